@@ -1,0 +1,241 @@
+// C-ABI batch driver around the UNMODIFIED reference sara-shield (TEST INFRASTRUCTURE, not product code).
+//
+// Compiled by oracle/Makefile together with the reference sources where they lie under /root/reference (nothing is
+// copied into this repository) into oracle/_ref/libsara_ref.so. It holds N independent reference `SafetyShield`
+// objects and drives them with the loop shape of SS/src/debug.cc:38-55
+// (humanMeasurement -> [newLongTermTrajectory] -> step), dumping everything the parity tests compare.
+// Built with -fno-access-control so private members of the reference classes can be read without touching its sources.
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "long_term_planner/long_term_planner.h"
+#include "reach_lib.hpp"
+#include "safety_shield/long_term_traj.h"
+#include "safety_shield/path.h"
+#include "safety_shield/safety_shield.h"
+#include "spdlog/spdlog.h"
+
+using safety_shield::Motion;
+using safety_shield::Path;
+using safety_shield::SafetyShield;
+using safety_shield::ShieldType;
+
+namespace {
+struct RefBatch {
+  int n = 0, J = 0, K = 0, threads = 1;
+  std::vector<std::unique_ptr<SafetyShield>> env;
+};
+
+template <class F>
+void par_for(const RefBatch* b, F f) {
+  int T = b->threads < 1 ? 1 : b->threads;
+  if (T > b->n) T = b->n;
+  if (T <= 1) {
+    for (int i = 0; i < b->n; ++i) f(i);
+    return;
+  }
+  std::vector<std::thread> th;
+  for (int t = 0; t < T; ++t) {
+    th.emplace_back([=]() {
+      int lo = static_cast<int>(static_cast<int64_t>(b->n) * t / T);
+      int hi = static_cast<int>(static_cast<int64_t>(b->n) * (t + 1) / T);
+      for (int i = lo; i < hi; ++i) f(i);
+    });
+  }
+  for (auto& x : th) x.join();
+}
+
+void put_capsule(const reach_lib::Capsule& c, double* o) {
+  o[0] = c.p1_.x; o[1] = c.p1_.y; o[2] = c.p1_.z;
+  o[3] = c.p2_.x; o[4] = c.p2_.y; o[5] = c.p2_.z;
+  o[6] = c.r_;
+}
+reach_lib::Capsule get_capsule(const double* c) {
+  return reach_lib::Capsule(reach_lib::Point(c[0], c[1], c[2]), reach_lib::Point(c[3], c[4], c[5]), c[6]);
+}
+void put_path(Path& p, double* o) {  // 11 doubles: phases[6], pos, vel, acc, jerk, is_current
+  for (int i = 0; i < 6; ++i) o[i] = p.phases_[i];
+  o[6] = p.pos_; o[7] = p.vel_; o[8] = p.acc_; o[9] = p.jerk_; o[10] = p.is_current_ ? 1.0 : 0.0;
+}
+}  // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------------------------------------------- batch of shields
+void* ref_create(int n, double sample_time, const char* traj_yaml, const char* robot_yaml, const char* mocap_yaml,
+                 const double* base_pose /*[n,6]*/, const double* init_q /*[n,J]*/, int J, int shield_type, int threads) {
+  spdlog::set_level(spdlog::level::off);
+  RefBatch* b = new RefBatch();
+  b->n = n;
+  b->J = J;
+  b->threads = threads;
+  b->env.resize(n);
+  for (int i = 0; i < n; ++i) {
+    std::vector<double> q(init_q + static_cast<size_t>(i) * J, init_q + static_cast<size_t>(i + 1) * J);
+    const double* p = base_pose + static_cast<size_t>(i) * 6;
+    b->env[i].reset(new SafetyShield(sample_time, traj_yaml, robot_yaml, mocap_yaml, p[0], p[1], p[2], p[3], p[4], p[5], q,
+                                     static_cast<ShieldType>(shield_type)));
+  }
+  b->K = static_cast<int>(b->env[0]->human_reach_->n_joints_meas_);
+  return b;
+}
+void ref_destroy(void* h) { delete static_cast<RefBatch*>(h); }
+void ref_set_threads(void* h, int threads) { static_cast<RefBatch*>(h)->threads = threads; }
+int ref_num_keypoints(void* h) { return static_cast<RefBatch*>(h)->K; }
+int ref_num_joints(void* h) { return static_cast<RefBatch*>(h)->env[0]->nb_joints_; }
+
+void ref_reset(void* h, const uint8_t* mask, const double* base_pose, const double* init_q, const double* t,
+               int shield_type) {
+  RefBatch* b = static_cast<RefBatch*>(h);
+  par_for(b, [=](int i) {
+    if (mask && !mask[i]) return;
+    const double* p = base_pose + static_cast<size_t>(i) * 6;
+    std::vector<double> q(init_q + static_cast<size_t>(i) * b->J, init_q + static_cast<size_t>(i + 1) * b->J);
+    b->env[i]->reset(p[0], p[1], p[2], p[3], p[4], p[5], q, t[i], static_cast<ShieldType>(shield_type));
+  });
+}
+
+void ref_human_measurement(void* h, const uint8_t* mask, const double* kp /*[n,K,3]*/, const double* t /*[n]*/) {
+  RefBatch* b = static_cast<RefBatch*>(h);
+  par_for(b, [=](int i) {
+    if (mask && !mask[i]) return;
+    std::vector<reach_lib::Point> pts(b->K);
+    const double* p = kp + static_cast<size_t>(i) * b->K * 3;
+    for (int k = 0; k < b->K; ++k) pts[k] = reach_lib::Point(p[3 * k], p[3 * k + 1], p[3 * k + 2]);
+    b->env[i]->humanMeasurement(pts, t[i]);
+  });
+}
+
+void ref_new_goal(void* h, const uint8_t* mask, const double* goal_q, const double* goal_dq) {
+  RefBatch* b = static_cast<RefBatch*>(h);
+  par_for(b, [=](int i) {
+    if (mask && !mask[i]) return;
+    std::vector<double> q(goal_q + static_cast<size_t>(i) * b->J, goal_q + static_cast<size_t>(i + 1) * b->J);
+    std::vector<double> dq(goal_dq + static_cast<size_t>(i) * b->J, goal_dq + static_cast<size_t>(i + 1) * b->J);
+    b->env[i]->newLongTermTrajectory(q, dq);
+  });
+}
+
+// One `step` for every env. Any output pointer may be NULL. branch: 0 recovery / 1 potential / 2 failsafe
+// (SS/src/safety_shield.cc:511-553); the paths that decide it are not modified by determineNextMotion, so the branch can
+// be read back after the call.
+void ref_step(void* h, const double* t, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
+              uint8_t* branch) {
+  RefBatch* b = static_cast<RefBatch*>(h);
+  const int J = b->J;
+  par_for(b, [=](int i) {
+    SafetyShield& s = *b->env[i];
+    Motion m = s.step(t[i]);
+    const size_t o = static_cast<size_t>(i) * J;
+    for (int j = 0; j < J; ++j) {
+      if (q) q[o + j] = m.q_[j];
+      if (dq) dq[o + j] = m.dq_[j];
+      if (ddq) ddq[o + j] = m.ddq_[j];
+      if (dddq) dddq[o + j] = m.dddq_[j];
+    }
+    if (is_safe) is_safe[i] = s.is_safe_ ? 1 : 0;
+    if (branch) branch[i] = s.is_safe_ ? (s.recovery_path_.pos_ >= s.failsafe_path_.pos_ ? 0 : 1) : 2;
+  });
+}
+
+// Capsules of the last step + per-model minimum capsule distance (min over robot x human of capsule_capsule_dist).
+void ref_get_capsules(void* h, double* robot /*[n,J,7]*/, double* human /*[n,H,7]*/, int H, double* min_dist /*[n,3]*/) {
+  RefBatch* b = static_cast<RefBatch*>(h);
+  const int J = b->J;
+  par_for(b, [=](int i) {
+    SafetyShield& s = *b->env[i];
+    if (robot)
+      for (size_t j = 0; j < s.robot_capsules_.size() && j < static_cast<size_t>(J); ++j)
+        put_capsule(s.robot_capsules_[j], robot + (static_cast<size_t>(i) * J + j) * 7);
+    int k = 0;
+    for (size_t m = 0; m < s.human_capsules_.size(); ++m) {
+      double md = INFINITY;
+      for (auto& hc : s.human_capsules_[m]) {
+        if (human && k < H) put_capsule(hc, human + (static_cast<size_t>(i) * H + k) * 7);
+        ++k;
+        for (auto& rc : s.robot_capsules_) {
+          double d = reach_lib::intersections::capsule_capsule_dist(rc, hc);
+          if (d < md) md = d;
+        }
+      }
+      if (min_dist && m < 3) min_dist[static_cast<size_t>(i) * 3 + m] = md;
+    }
+  });
+}
+
+// State dump for debugging divergences: 5 paths x 11 doubles + 8 scalars.
+void ref_get_state(void* h, int i, double* out /*[63]*/) {
+  SafetyShield& s = *static_cast<RefBatch*>(h)->env[i];
+  put_path(s.recovery_path_, out);
+  put_path(s.failsafe_path_, out + 11);
+  put_path(s.failsafe_path_2_, out + 22);
+  put_path(s.safe_path_, out + 33);
+  put_path(s.potential_path_, out + 44);
+  out[55] = s.path_s_;
+  out[56] = s.path_s_discrete_;
+  out[57] = s.new_ltt_;
+  out[58] = s.new_goal_;
+  out[59] = s.new_ltt_processed_;
+  out[60] = s.recovery_path_correct_;
+  out[61] = s.long_term_trajectory_.getLength();
+  out[62] = s.new_long_term_trajectory_.getLength();
+}
+
+// ------------------------------------------------------------------------------------------- per-stage entry points
+void ref_capsule_dist(int n, const double* c1 /*[n,7]*/, const double* c2 /*[n,7]*/, double* dist /*[n]*/) {
+  for (int i = 0; i < n; ++i)
+    dist[i] = reach_lib::intersections::capsule_capsule_dist(get_capsule(c1 + 7 * i), get_capsule(c2 + 7 * i));
+}
+
+// planSafetyShield on shield 0 of the batch (SS/src/safety_shield.cc:203-341) + Path::getFinalMotion.
+void ref_plan_safety_shield(void* h, int n, const double* in /*[n,6]: pos vel acc ve a_max j_max*/,
+                            uint8_t* ok /*[n]*/, double* phases /*[n,6]*/, double* fin /*[n,3]*/) {
+  SafetyShield& s = *static_cast<RefBatch*>(h)->env[0];
+  for (int i = 0; i < n; ++i) {
+    const double* a = in + 6 * i;
+    Path p;
+    ok[i] = s.planSafetyShield(a[0], a[1], a[2], a[3], a[4], a[5], p) ? 1 : 0;
+    for (int k = 0; k < 6; ++k) phases[6 * i + k] = p.phases_[k];
+    p.getFinalMotion(fin[3 * i], fin[3 * i + 1], fin[3 * i + 2]);
+  }
+}
+
+// LongTermPlanner::planTrajectory (LTP/src/long_term_planner.cc:7-63). Returns length (0 on failure);
+// traj layout [L][4][J] (q, v, a, j per sample), truncated to max_len samples.
+int ref_ltp_plan(int J, double ts, const double* q_min, const double* q_max, const double* v_max, const double* a_max,
+                 const double* j_max, const double* q_goal, const double* q0, const double* v0, const double* a0,
+                 double* traj, int max_len) {
+  auto vec = [J](const double* p) { return std::vector<double>(p, p + J); };
+  long_term_planner::LongTermPlanner ltp(J, ts, vec(q_min), vec(q_max), vec(v_max), vec(a_max), vec(j_max));
+  long_term_planner::Trajectory tr;
+  bool ok = ltp.planTrajectory(vec(q_goal), vec(q0), vec(v0), vec(a0), tr);
+  if (!ok) return 0;
+  int L = tr.length < max_len ? tr.length : max_len;
+  for (int i = 0; i < L; ++i)
+    for (int j = 0; j < J; ++j) {
+      double* o = traj + (static_cast<size_t>(i) * 4) * J;
+      o[0 * J + j] = tr.q[j][i];
+      o[1 * J + j] = tr.v[j][i];
+      o[2 * J + j] = tr.a[j][i];
+      o[3 * J + j] = tr.j[j][i];
+    }
+  return tr.length;
+}
+
+// roots() + getSmallestPositiveNonComplexRoot (LTP/include/long_term_planner/roots.h:22-50)
+double ref_poly_roots(int ncoef, const double* coef, double* re, double* im) {
+  Eigen::VectorXd pv(ncoef);
+  for (int i = 0; i < ncoef; ++i) pv(i) = coef[i];
+  auto r = long_term_planner::roots<double>(pv);
+  for (int i = 0; i < ncoef - 1; ++i) {
+    re[i] = r(i, 0).real();
+    im[i] = r(i, 0).imag();
+  }
+  return long_term_planner::getSmallestPositiveNonComplexRoot<double>(r);
+}
+
+}  // extern "C"
