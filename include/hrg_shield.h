@@ -1,0 +1,167 @@
+/* hrg_shield.h — C ABI of the batched B200 safety shield (libhrg_shield.so).
+ *
+ * Drop-in boundary for the sara-shield hot path of human-robot-gym. Each entry point replaces one method of the
+ * reference's pybind module `safety_shield_py` (SS/bindings/safety_shield_bindings.cpp:82-115, where
+ * SS = human_robot_gym/controllers/failsafe_controller/sara-shield/safety_shield), now over a batch of N independent
+ * shields held as structure-of-arrays FP64 device memory owned by an opaque handle.
+ *
+ * Conventions: plain C types only; every array argument is a DEVICE pointer to caller-owned memory unless the
+ * function name ends in `_host` (then it is a HOST pointer, pinned for best speed, and the call performs the
+ * host<->device copies on `stream`); nothing synchronises implicitly; every function returns 0 on success or a
+ * negative HRG_E* code (no exceptions cross the ABI). `stream` is a cudaStream_t passed as void*.
+ * There is no CPU fallback: without a CUDA device hrg_shield_create fails with HRG_ENODEVICE.
+ */
+#ifndef HRG_SHIELD_H
+#define HRG_SHIELD_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HRG_MAX_JOINTS 8     /* Schunk 6, Panda 7 */
+#define HRG_MAX_KEYPOINTS 64 /* mujoco_mocap.yaml 23, cmu_mocap*.yaml 21-31 */
+#define HRG_MAX_BODIES 24    /* shipped models 8; synthetic full body 16 */
+#define HRG_MAX_EXT 8        /* shipped models 2; synthetic full body 4 */
+
+#define HRG_OK 0
+#define HRG_EINVAL (-1)
+#define HRG_ENODEVICE (-2)
+#define HRG_ECUDA (-3)
+#define HRG_ENOMEM (-4)
+
+/* ShieldType (SS/include/safety_shield/safety_shield.h:55) */
+#define HRG_SHIELD_OFF 0
+#define HRG_SHIELD_SSM 1
+#define HRG_SHIELD_PFL 2
+
+/* Per-env status bits reported by hrg_shield_step (replace the reference's logged-and-swallowed exceptions). */
+#define HRG_ST_REPLANNED 0x1u        /* LongTermPlanner ran this tick (safety_shield.cc:589) */
+#define HRG_ST_REPLAN_FAILED 0x2u    /* planTrajectory returned false (safety_shield.cc:600) */
+#define HRG_ST_NOT_PLANNABLE 0x4u    /* |ddq| > a_max_ltt (safety_shield.cc:572,603) */
+#define HRG_ST_JOINT_LIMIT 0x8u      /* goal motion outside [q_min,q_max] (safety_shield.cc:619) */
+#define HRG_ST_LTT_TRUNCATED 0x10u   /* planned trajectory longer than ltt_capacity: replan rejected */
+#define HRG_ST_NEAR_THRESHOLD 0x20u  /* some capsule distance within 1e-6 m of 0 (excluded from flag parity) */
+
+/* Constant tables: the content of the reference's three YAML files (safety_shield.cc:61-131), already ordered the
+ * way the reference EVALUATES them (bodies/extremities in std::map order). Filled by the host layer. */
+typedef struct HrgConfig {
+  int32_t nb_joints;    /* robot_parameters_*.yaml nb_joints */
+  int32_t n_keypoints;  /* len(joint_names) of the mocap yaml */
+  int32_t n_bodies;     /* Vel and Accel capsules each */
+  int32_t n_ext;        /* Pos spheres */
+  int32_t ltt_capacity; /* samples per long-term-trajectory slot (two slots per env) */
+  int32_t reserved0;
+  double sample_time;
+  double max_s_stop, v_safe, alpha_i_max; /* trajectory_parameters_*.yaml */
+  double secure_radius;                   /* robot_parameters_*.yaml */
+  double meas_err_pos, meas_err_vel, delay; /* mocap yaml */
+  double q_min[HRG_MAX_JOINTS], q_max[HRG_MAX_JOINTS];
+  double v_max[HRG_MAX_JOINTS], a_max[HRG_MAX_JOINTS], j_max[HRG_MAX_JOINTS]; /* *_max_allowed */
+  double a_max_ltt[HRG_MAX_JOINTS], j_max_ltt[HRG_MAX_JOINTS];
+  double link_T[HRG_MAX_JOINTS][16];  /* transformation_matrices, row-major 4x4 per joint */
+  double link_caps[HRG_MAX_JOINTS][7]; /* enclosures: p1 p2 r in link frame */
+  int32_t body_prox[HRG_MAX_BODIES], body_dist[HRG_MAX_BODIES];
+  double body_thickness[HRG_MAX_BODIES];
+  double body_vmax[HRG_MAX_BODIES][2], body_amax[HRG_MAX_BODIES][2]; /* joint_v_max/joint_a_max of prox, dist */
+  int32_t ext_base[HRG_MAX_EXT];
+  int32_t reserved1[HRG_MAX_EXT];
+  double ext_thickness[HRG_MAX_EXT], ext_length[HRG_MAX_EXT], ext_vmax[HRG_MAX_EXT];
+} HrgConfig;
+
+/* Device-reduced per-step statistics (the only cross-GPU exchange: one tiny all_reduce of this struct). */
+typedef struct HrgStats {
+  int64_t n_steps;          /* env-steps accumulated */
+  int64_t n_unsafe;         /* steps with is_safe == false */
+  int64_t n_branch[3];      /* determineNextMotion branch histogram: recovery / potential / failsafe */
+  int64_t n_replan;         /* LongTermPlanner invocations */
+  int64_t n_replan_failed;
+  int64_t n_near_threshold; /* steps with a capsule distance within 1e-6 of 0 */
+  int64_t ltt_len_sum;      /* sum of planned LTT lengths (mean L = ltt_len_sum / (n_replan - n_replan_failed)) */
+  double min_dist;          /* smallest capsule distance seen */
+} HrgStats;
+
+typedef struct HrgShield HrgShield;
+
+/* SafetyShield(sample_time, trajectory_config_file, robot_config_file, mocap_config_file, init_x..init_yaw, init_qpos,
+ * shield_type) — safety_shield_bindings.cpp:84-96 / safety_shield.cc:55-162 — for n_envs shields on CUDA device `device`.
+ * base_pose [N,6] = (x,y,z,roll,pitch,yaw), init_q [N,J], shield_type [N] (or NULL: all SSM); HOST pointers here
+ * (construction is not on the hot path). The shields are primed exactly like the reference ctor. */
+int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double* base_pose_host,
+                      const double* init_q_host, const int32_t* shield_type_host, HrgShield** out);
+int hrg_shield_destroy(HrgShield* s);
+
+/* SafetyShield.reset(init_x.., init_qpos, current_time, shield_type) — bindings :97-106 / safety_shield.cc:164-201.
+ * env_mask [N] u8 or NULL (all). */
+int hrg_shield_reset(HrgShield* s, const uint8_t* env_mask, const double* base_pose, const double* init_q,
+                     const double* t, const int32_t* shield_type, void* stream);
+
+/* SafetyShield.humanMeasurement(human_measurement, time) — bindings :110 / safety_shield.h:521-539 /
+ * human_reach.cc:52-74. keypoints [N,K,3], t [N]. env_mask [N] u8 or NULL. */
+int hrg_shield_human_measurement(HrgShield* s, const uint8_t* env_mask, const double* keypoints, const double* t,
+                                 void* stream);
+
+/* SafetyShield.newLongTermTrajectory(goal_position, goal_velocity) — bindings :108 / safety_shield.cc:672-697.
+ * goal_q, goal_dq [N,J]; env_mask [N] u8 or NULL. */
+int hrg_shield_new_goal(HrgShield* s, const uint8_t* env_mask, const double* goal_q, const double* goal_dq,
+                        void* stream);
+
+/* SafetyShield.setLongTermTrajectory(traj) — bindings :109 / safety_shield.cc:699-730 — for ONE env.
+ * traj [L,4,J] (q,dq,ddq,dddq per sample), times of samples are not needed by the SSM path. Returns in *verdict:
+ * 0 installed, 1 RobotMovementException, 2 start position differs, 3 start velocity differs, 4 does not end stopped. */
+int hrg_shield_set_ltt(HrgShield* s, int env, const double* traj_host, int length, double sample_time,
+                       int32_t* verdict_host, void* stream);
+
+/* SafetyShield.step(cycle_begin_time) — bindings :107 / safety_shield.cc:555-647 — for every env.
+ * t [N]; outputs (any may be NULL): q,dq,ddq,dddq [N,J]; is_safe [N] u8 (getSafety, bindings :113);
+ * branch [N] u8 0 recovery / 1 potential / 2 failsafe (safety_shield.cc:511-553); status [N] HRG_ST_* bits. */
+int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double* ddq, double* dddq,
+                    uint8_t* is_safe, uint8_t* branch, uint32_t* status, void* stream);
+
+/* humanMeasurement + [newLongTermTrajectory for masked envs] + step with HOST buffers: one H2D of the inputs, the
+ * kernels, one D2H of the setpoints, all on `stream`; the caller synchronises the stream. goal_mask/goal_q may be NULL.
+ * out_host [N, 3J+1] doubles per env: q[J], dq[J], ddq[J], then is_safe + 2*branch packed as a double is NOT used —
+ * flags_host [N] u8 = is_safe | branch<<1. */
+int hrg_shield_tick_host(HrgShield* s, const double* keypoints_host, const double* t_host, const uint8_t* goal_mask_host,
+                         const double* goal_q_host, double* q_host, double* dq_host, double* ddq_host,
+                         uint8_t* flags_host, void* stream);
+
+/* getRobotReachCapsules / getHumanReachCapsules — bindings :111-112 / safety_shield.h:549-574 — of the last step.
+ * robot [N,J,7], human [N,H,7] with H = n_ext + 2*n_bodies ordered Pos, Vel, Accel; min_dist [N,3] = per human model
+ * the minimum capsule_capsule_dist over robot x human capsules (+inf where the step skipped verification).
+ * Any pointer may be NULL. */
+int hrg_shield_get_capsules(HrgShield* s, double* robot, double* human, double* min_dist, void* stream);
+
+/* Accumulated statistics since the last clear; `out` is a DEVICE pointer to one HrgStats. */
+int hrg_shield_stats(HrgShield* s, HrgStats* out, int clear, void* stream);
+
+int hrg_shield_num_envs(const HrgShield* s);
+int hrg_shield_num_human_capsules(const HrgShield* s);
+/* Number of kernels this library has launched on behalf of `s` since creation (bench.py's gpu_launches claim). */
+int64_t hrg_shield_launch_count(const HrgShield* s);
+const char* hrg_last_error(void);
+
+/* ---- per-stage entry points (parity tests + ncu); all DEVICE pointers --------------------------------------- */
+/* capsule_capsule_dist (RL/include/intersections.hpp:105-124) for n independent pairs: c1,c2 [n,7] -> dist [n]. */
+int hrg_stage_capsule_dist(int n, const double* c1, const double* c2, double* dist, void* stream);
+/* planSafetyShield + Path::getFinalMotion (safety_shield.cc:203-341, path.cc:41-53) for n cases:
+ * in [n,6] = pos vel acc ve a_max j_max -> ok [n] u8, phases [n,6], fin [n,3]. */
+int hrg_stage_plan_safety_shield(double sample_time, int n, const double* in, uint8_t* ok, double* phases, double* fin,
+                                 void* stream);
+/* LongTermPlanner::planTrajectory (LTP/src/long_term_planner.cc:7-63) for n independent problems with the limits of
+ * cfg: goal,q0,v0,a0 [n,J] -> traj [n,cap,4,J], length [n] i32 (0 = failed, -L = longer than cap). */
+int hrg_stage_ltp_plan(const HrgConfig* cfg, int n, const double* goal, const double* q0, const double* v0,
+                       const double* a0, double* traj, int32_t* length, int cap, void* stream);
+/* reach + verify only (robot_reach.cc:61-98, human_reach.cc:76-87, verify_iso.cc:19-33) on explicit inputs:
+ * base_pose [n,6], q_start,q_goal [n,J], s_diff,t_reach [n], alpha_i [n,J], kp_pos,kp_vel [n,K,3] ->
+ * robot [n,J,7], human [n,H,7], min_dist [n,3], is_safe [n]. */
+int hrg_stage_reach_verify(const HrgConfig* cfg, int n, const double* base_pose, const double* q_start,
+                           const double* q_goal, const double* s_diff, const double* t_reach, const double* alpha_i,
+                           const double* kp_pos, const double* kp_vel, double* robot, double* human, double* min_dist,
+                           uint8_t* is_safe, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HRG_SHIELD_H */
