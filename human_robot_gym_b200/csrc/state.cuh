@@ -1,0 +1,113 @@
+// Device-resident state of a batch of N shields: structure-of-arrays FP64 in HBM.
+//
+// Two access patterns shape the layout:
+//   * thread-per-env kernels (path planning in s, selection) touch the scalar state: stored field-major [field][N] so
+//     that consecutive threads read consecutive doubles (fully coalesced 8 B x 32 = 256 B per request);
+//   * warp-per-env kernels (measurement, reach + verify) and the per-env gathers (one LTT sample) touch small contiguous
+//     records: stored env-major [N][record] so a warp reads one 128 B-aligned record with consecutive lanes.
+// The reference holds the same data as one heap-allocated SafetyShield object per env
+// (SS/include/safety_shield/safety_shield.h:70-293).
+#pragma once
+#include "geom_math.cuh"
+
+namespace hrg {
+
+// flag word (one per env)
+enum : uint32_t {
+  F_IS_SAFE = 1u << 0,        // is_safe_
+  F_NEW_LTT = 1u << 1,        // new_ltt_
+  F_NEW_GOAL = 1u << 2,       // new_goal_
+  F_NEW_LTT_PROCESSED = 1u << 3,
+  F_REC_CORRECT = 1u << 4,    // recovery_path_correct_
+  F_UNDER_V_LIMIT = 1u << 5,  // is_under_v_limit_ (PFL)
+  F_REC_CURRENT = 1u << 6,    // recovery_path_.isCurrent()
+  F_LIVE_SLOT = 1u << 7,      // which LTT slot is long_term_trajectory_ (the other one is new_long_term_trajectory_)
+  F_VERIFY = 1u << 8,         // this step runs reach + verify
+  F_PENDING_REPLAN = 1u << 9, // this step waits for k_replan
+  F_TYPE_SHIFT = 10,          // 2 bits: ShieldType
+  F_TYPE_MASK = 3u << 10,
+  F_STEPPED = 1u << 12,       // at least one step() since reset (capsule getters)
+  F_BRANCH_SHIFT = 13,        // 2 bits: branch of the last determineNextMotion
+  F_BRANCH_MASK = 3u << 13,
+  F_STATUS_SHIFT = 16,        // HRG_ST_* bits of the last step live in the high half
+};
+
+enum { P_REC = 0, P_FS = 1, P_FS2 = 2, P_SAFE = 3, N_PATHS = 4, PATH_FIELDS = 10 };
+
+struct DevState {
+  int N, J, K, H, L;  // envs, joints, keypoints, human capsules, LTT capacity (samples per slot)
+  const HrgConfig* cfg;
+  // ---- field-major [..][N]
+  double* paths;      // [N_PATHS][PATH_FIELDS][N]
+  double* path_s;     // [N]
+  int32_t* path_sd;   // [N] path_s_discrete_
+  uint32_t* flags;    // [N]
+  double* prev_dq;    // [J][N]  next_motion_.getVelocity()
+  double* goal_q;     // [J][N]  new_goal_motion_
+  double* replan_q;   // [J][N]  last_replan_start_motion_
+  int32_t* ltt_len;   // [2][N]
+  int32_t* ltt_cur;   // [2][N]  current_pos_
+  int32_t* ltt_start; // [2][N]  starting_index_
+  double* ltt_t0;     // [2][N]  time of sample 0 (= path_s_ at planning; PFL scan)
+  double* ltt_alpha;  // [2][J][N] alpha_i_ (PFL; NULL when PFL is not enabled: SSM uses cfg->alpha_i_max)
+  // ---- env-major [N][..]
+  double* base_T;     // [N][12] rows 0..2 of the base pose matrix
+  double* kp_pos;     // [N][K*3]
+  double* kp_vel;     // [N][K*3]
+  double* last_meas;  // [N]
+  double* ltt;        // [N][2][L][4][J]  q, dq, ddq, dddq per sample
+  double* ltt_cart;   // [N][2][L] max Cartesian velocity per sample (PFL; NULL otherwise)
+  // ---- per-step hand-over between the kernels of one tick, env-major
+  double* cur;        // [N][4J+1]: q, dq, ddq, dddq of getCurrentMotion(), then its s
+  double* reach_in;   // [N][3J+2]: q_start[J], q_goal[J], alpha_i[J], s_diff, t_reach
+  double* min_dist;   // [N][3]
+  int32_t* replan_list;   // [N]
+  int32_t* replan_count;  // [1]
+  // optional per-step capsule dump (drop-in getters); NULL = not stored
+  double* robot_caps;  // [N][J][7]
+  double* human_caps;  // [N][H][7]
+  HrgStats* stats;
+};
+
+HRG_HD int cur_stride(int J) { return 4 * J + 1; }
+HRG_HD int reach_stride(int J) { return 3 * J + 2; }
+
+HRG_HD void path_load(const DevState& S, int which, int e, PathS& p) {
+  const double* b = S.paths + (size_t)which * PATH_FIELDS * S.N + e;
+  for (int i = 0; i < 6; ++i) p.ph[i] = b[(size_t)i * S.N];
+  p.pos = b[(size_t)6 * S.N];
+  p.vel = b[(size_t)7 * S.N];
+  p.acc = b[(size_t)8 * S.N];
+  p.jerk = b[(size_t)9 * S.N];
+}
+HRG_HD void path_store(const DevState& S, int which, int e, const PathS& p) {
+  double* b = S.paths + (size_t)which * PATH_FIELDS * S.N + e;
+  for (int i = 0; i < 6; ++i) b[(size_t)i * S.N] = p.ph[i];
+  b[(size_t)6 * S.N] = p.pos;
+  b[(size_t)7 * S.N] = p.vel;
+  b[(size_t)8 * S.N] = p.acc;
+  b[(size_t)9 * S.N] = p.jerk;
+}
+HRG_HD const double* ltt_sample(const DevState& S, int e, int slot, int i) {
+  return S.ltt + (((size_t)e * 2 + slot) * S.L + i) * 4 * S.J;
+}
+HRG_HD double* ltt_sample_w(const DevState& S, int e, int slot, int i) {
+  return S.ltt + (((size_t)e * 2 + slot) * S.L + i) * 4 * S.J;
+}
+
+// LongTermTraj::interpolate (SS/src/long_term_traj.cc:41-77) of slot `slot` of env e at (s, ds, dds, ddds).
+// out: q, dq, ddq, dddq with stride `os` between joints (so it can write env-major or registers).
+HRG_HD void ltt_interpolate(const DevState& S, const HrgConfig& c, int e, int slot, double s, double ds, double dds,
+                            double ddds, double* q, double* dq, double* ddq, double* dddq) {
+  int sample;
+  double dt;
+  ltt_locate(s, c.sample_time, S.ltt_start[(size_t)slot * S.N + e], S.ltt_len[(size_t)slot * S.N + e],
+             S.ltt_cur[(size_t)slot * S.N + e], sample, dt);
+  const double* m = ltt_sample(S, e, slot, sample);
+  const int J = S.J;
+  for (int j = 0; j < J; ++j)
+    ltt_interp_joint(m[j], m[J + j], m[2 * J + j], m[3 * J + j], dt, ds, dds, ddds, c.v_max[j], c.a_max[j], q[j],
+                     dq[j], ddq[j], dddq[j]);
+}
+
+}  // namespace hrg
