@@ -251,6 +251,15 @@ HRG_HD Cap human_capsule(const HrgConfig& c, int h, const double* kp, const doub
                              c.body_amax[b][1], c.body_thickness[b], t_reach, c.delay, c.meas_err_pos, c.meas_err_vel);
 }
 
+// Rows 0..2 of the base pose matrix from (x, y, z, roll, pitch, yaw) — RobotReach ctor / reset
+// (SS/src/robot_reach.cc:5-17,41-52). out[12] row-major 3x4.
+HRG_HD void base_pose_matrix(double x, double y, double z, double roll, double pitch, double yaw, double* out) {
+  double cr = cos(roll), sr = sin(roll), cp = cos(pitch), sp = sin(pitch), cy = cos(yaw), sy = sin(yaw);
+  out[0] = cr * cp; out[1] = cr * sp * sy - sr * cy; out[2] = cr * sp * cy + sr * sy; out[3] = x;
+  out[4] = sr * cp; out[5] = sr * sp * sy + cr * cy; out[6] = sr * sp * cy - cr * sy; out[7] = y;
+  out[8] = -sp;     out[9] = cp * sy;                out[10] = cp * cy;               out[11] = z;
+}
+
 // model index (0 Pos, 1 Vel, 2 Accel) of human capsule h
 HRG_HD int human_model_of(const HrgConfig& c, int h) { return h < c.n_ext ? 0 : ((h - c.n_ext) < c.n_bodies ? 1 : 2); }
 

@@ -1,0 +1,312 @@
+// libhrg_shield.so — C ABI of the batched B200 safety shield (see include/hrg_shield.h).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (see __graft_entry__.build()).
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "kernels_reach.cuh"
+#include "kernels_tick.cuh"
+
+using namespace hrg;
+
+namespace {
+thread_local std::string g_err;
+
+int fail(int code, const char* what, cudaError_t ce = cudaSuccess) {
+  g_err = what;
+  if (ce != cudaSuccess) {
+    g_err += ": ";
+    g_err += cudaGetErrorString(ce);
+  }
+  return code;
+}
+#define CK(call)                                        \
+  do {                                                  \
+    cudaError_t _e = (call);                            \
+    if (_e != cudaSuccess) return fail(HRG_ECUDA, #call, _e); \
+  } while (0)
+
+int cfg_check(const HrgConfig* c) {
+  if (!c) return fail(HRG_EINVAL, "cfg is NULL");
+  if (c->nb_joints < 1 || c->nb_joints > HRG_MAX_JOINTS) return fail(HRG_EINVAL, "nb_joints out of range");
+  if (c->n_keypoints < 1 || c->n_keypoints > HRG_MAX_KEYPOINTS) return fail(HRG_EINVAL, "n_keypoints out of range");
+  if (c->n_bodies < 0 || c->n_bodies > HRG_MAX_BODIES) return fail(HRG_EINVAL, "n_bodies out of range");
+  if (c->n_ext < 0 || c->n_ext > HRG_MAX_EXT) return fail(HRG_EINVAL, "n_ext out of range");
+  if (!(c->sample_time > 0)) return fail(HRG_EINVAL, "sample_time must be > 0");
+  for (int b = 0; b < c->n_bodies; ++b)
+    if (c->body_prox[b] < 0 || c->body_prox[b] >= c->n_keypoints || c->body_dist[b] < 0 ||
+        c->body_dist[b] >= c->n_keypoints)
+      return fail(HRG_EINVAL, "body keypoint index out of range");
+  for (int x = 0; x < c->n_ext; ++x)
+    if (c->ext_base[x] < 0 || c->ext_base[x] >= c->n_keypoints) return fail(HRG_EINVAL, "extremity index out of range");
+  return HRG_OK;
+}
+}  // namespace
+
+struct HrgShield {
+  DevState S;
+  HrgConfig cfg;
+  int device = 0;
+  int sm_count = 148;
+  bool pfl = false;
+  long long launches = 0;
+  std::vector<void*> allocs;
+  // staging for the *_host tick
+  double* d_kp = nullptr;
+  double* d_t = nullptr;
+  double* d_goal = nullptr;
+  uint8_t* d_goal_mask = nullptr;
+  double* d_q = nullptr;
+  double* d_dq = nullptr;
+  double* d_ddq = nullptr;
+  uint8_t* d_safe = nullptr;
+  uint8_t* d_branch = nullptr;
+  uint8_t* d_flags8 = nullptr;
+  size_t reach_smem = 0;
+
+  template <class T>
+  int alloc(T** p, size_t n) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, n * sizeof(T) + 16);
+    if (e != cudaSuccess) return fail(HRG_ENOMEM, "cudaMalloc", e);
+    e = cudaMemset(q, 0, n * sizeof(T) + 16);
+    if (e != cudaSuccess) return fail(HRG_ECUDA, "cudaMemset", e);
+    allocs.push_back(q);
+    *p = static_cast<T*>(q);
+    return HRG_OK;
+  }
+};
+
+namespace {
+inline int grid_for(int n, int block) { return (n + block - 1) / block; }
+inline int reach_grid(const HrgShield* s, int n) {
+  int need = (n + kWarpsPerBlock - 1) / kWarpsPerBlock;
+  int cap = s->sm_count * 8;  // a multiple of the SM count; warps stride over the remaining envs
+  return need < cap ? (need > 0 ? need : 1) : cap;
+}
+
+__global__ void k_pack_flags(int n, const uint8_t* __restrict__ safe, const uint8_t* __restrict__ branch,
+                             uint8_t* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (uint8_t)(safe[i] | (branch[i] << 1));
+}
+}  // namespace
+
+extern "C" {
+
+const char* hrg_last_error(void) { return g_err.c_str(); }
+
+int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double* base_pose_host,
+                      const double* init_q_host, const int32_t* shield_type_host, HrgShield** out) {
+  if (!out) return fail(HRG_EINVAL, "out is NULL");
+  *out = nullptr;
+  int rc = cfg_check(cfg);
+  if (rc) return rc;
+  if (n_envs < 1) return fail(HRG_EINVAL, "n_envs must be >= 1");
+  if (cfg->ltt_capacity < 2) return fail(HRG_EINVAL, "ltt_capacity must be >= 2");
+  if (!base_pose_host || !init_q_host) return fail(HRG_EINVAL, "base_pose/init_q is NULL");
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev < 1) return fail(HRG_ENODEVICE, "no CUDA device (this library has no CPU fallback)", ce);
+  if (device < 0 || device >= ndev) return fail(HRG_EINVAL, "device index out of range");
+  CK(cudaSetDevice(device));
+  HrgShield* h = new (std::nothrow) HrgShield();
+  if (!h) return fail(HRG_ENOMEM, "host allocation failed");
+  h->cfg = *cfg;
+  h->device = device;
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  h->sm_count = prop.multiProcessorCount;
+  DevState& S = h->S;
+  const size_t N = n_envs;
+  const int J = cfg->nb_joints, K = cfg->n_keypoints, H = cfg->n_ext + 2 * cfg->n_bodies, L = cfg->ltt_capacity;
+  S.N = n_envs; S.J = J; S.K = K; S.H = H; S.L = L;
+  h->pfl = false;
+  if (shield_type_host)
+    for (size_t i = 0; i < N; ++i) h->pfl |= (shield_type_host[i] == HRG_SHIELD_PFL);
+  HrgConfig* dcfg = nullptr;
+#define AL(ptr, count)                         \
+  do {                                         \
+    rc = h->alloc(&(ptr), (size_t)(count));    \
+    if (rc) {                                  \
+      hrg_shield_destroy(h);                   \
+      return rc;                               \
+    }                                          \
+  } while (0)
+  AL(dcfg, 1);
+  S.cfg = dcfg;
+  AL(S.paths, (size_t)N_PATHS * PATH_FIELDS * N);
+  AL(S.path_s, N);
+  AL(S.path_sd, N);
+  AL(S.flags, N);
+  AL(S.prev_dq, (size_t)J * N);
+  AL(S.goal_q, (size_t)J * N);
+  AL(S.replan_q, (size_t)J * N);
+  AL(S.ltt_len, 2 * N);
+  AL(S.ltt_cur, 2 * N);
+  AL(S.ltt_start, 2 * N);
+  AL(S.ltt_t0, 2 * N);
+  AL(S.ltt_ts, 2 * N);
+  AL(S.ltt_alpha, (size_t)2 * J * N);
+  AL(S.base_T, 12 * N);
+  AL(S.kp_pos, (size_t)K * 3 * N);
+  AL(S.kp_vel, (size_t)K * 3 * N);
+  AL(S.last_meas, N);
+  AL(S.ltt, (size_t)N * 2 * L * 4 * J);
+  AL(S.cur, (size_t)N * cur_stride(J));
+  AL(S.reach_in, (size_t)N * reach_stride(J));
+  AL(S.min_dist, 3 * N);
+  AL(S.replan_list, N);
+  AL(S.replan_count, 1);
+  AL(S.stats, 1);
+  S.ltt_cart = nullptr;
+  S.robot_caps = nullptr;
+  S.human_caps = nullptr;
+  if (h->pfl) {
+    AL(S.ltt_cart, (size_t)N * 2 * L);
+  }
+  // staging buffers of hrg_shield_tick_host
+  AL(h->d_kp, (size_t)K * 3 * N);
+  AL(h->d_t, N);
+  AL(h->d_goal, (size_t)J * N);
+  AL(h->d_goal_mask, N);
+  AL(h->d_q, (size_t)J * N);
+  AL(h->d_dq, (size_t)J * N);
+  AL(h->d_ddq, (size_t)J * N);
+  AL(h->d_safe, N);
+  AL(h->d_branch, N);
+  AL(h->d_flags8, N);
+#undef AL
+  h->reach_smem = (size_t)kWarpsPerBlock * reach_smem_doubles(K, H) * sizeof(double);
+  cudaFuncSetAttribute(k_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
+  cudaFuncSetAttribute(k_stage_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
+  ce = cudaMemcpy(dcfg, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice);
+  HrgStats st0;
+  memset(&st0, 0, sizeof(st0));
+  st0.min_dist = INFINITY;
+  if (ce == cudaSuccess) ce = cudaMemcpy(S.stats, &st0, sizeof(st0), cudaMemcpyHostToDevice);
+  // prime every shield like the reference constructor
+  double *d_pose = nullptr, *d_q0 = nullptr;
+  int32_t* d_type = nullptr;
+  if (ce == cudaSuccess) ce = cudaMalloc(&d_pose, 6 * N * sizeof(double));
+  if (ce == cudaSuccess) ce = cudaMalloc(&d_q0, (size_t)J * N * sizeof(double));
+  if (ce == cudaSuccess) ce = cudaMemcpy(d_pose, base_pose_host, 6 * N * sizeof(double), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) ce = cudaMemcpy(d_q0, init_q_host, (size_t)J * N * sizeof(double), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess && shield_type_host) {
+    ce = cudaMalloc(&d_type, N * sizeof(int32_t));
+    if (ce == cudaSuccess) ce = cudaMemcpy(d_type, shield_type_host, N * sizeof(int32_t), cudaMemcpyHostToDevice);
+  }
+  if (ce == cudaSuccess) {
+    k_reset<<<grid_for(n_envs, 128), 128>>>(S, nullptr, d_pose, d_q0, d_type);
+    h->launches++;
+    ce = cudaDeviceSynchronize();
+  }
+  cudaFree(d_pose);
+  cudaFree(d_q0);
+  cudaFree(d_type);
+  if (ce != cudaSuccess) {
+    hrg_shield_destroy(h);
+    return fail(HRG_ECUDA, "shield initialisation", ce);
+  }
+  *out = h;
+  return HRG_OK;
+}
+
+int hrg_shield_destroy(HrgShield* s) {
+  if (!s) return HRG_OK;
+  cudaSetDevice(s->device);
+  for (void* p : s->allocs) cudaFree(p);
+  delete s;
+  return HRG_OK;
+}
+
+int hrg_shield_num_envs(const HrgShield* s) { return s ? s->S.N : 0; }
+int hrg_shield_num_human_capsules(const HrgShield* s) { return s ? s->S.H : 0; }
+int64_t hrg_shield_launch_count(const HrgShield* s) { return s ? s->launches : 0; }
+
+int hrg_shield_reset(HrgShield* s, const uint8_t* env_mask, const double* base_pose, const double* init_q,
+                     const double* t, const int32_t* shield_type, void* stream) {
+  if (!s || !base_pose || !init_q) return fail(HRG_EINVAL, "hrg_shield_reset: NULL argument");
+  (void)t;  // cycle_begin_time_ is only stored by the reference (safety_shield.cc:185)
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  k_reset<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S, env_mask, base_pose, init_q, shield_type);
+  s->launches++;
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_shield_human_measurement(HrgShield* s, const uint8_t* env_mask, const double* keypoints, const double* t,
+                                 void* stream) {
+  if (!s || !keypoints || !t) return fail(HRG_EINVAL, "hrg_shield_human_measurement: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  k_measure<<<reach_grid(s, s->S.N), kWarpsPerBlock * 32, 0, st>>>(s->S, env_mask, keypoints, t);
+  s->launches++;
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_shield_new_goal(HrgShield* s, const uint8_t* env_mask, const double* goal_q, const double* goal_dq,
+                        void* stream) {
+  if (!s || !goal_q) return fail(HRG_EINVAL, "hrg_shield_new_goal: NULL argument");
+  (void)goal_dq;  // clamped and stored by the reference, never read on the step path (safety_shield.cc:682-684)
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  k_new_goal<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S, env_mask, goal_q);
+  s->launches++;
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
+                    uint8_t* branch, uint32_t* status, void* stream) {
+  if (!s || !t) return fail(HRG_EINVAL, "hrg_shield_step: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int N = s->S.N;
+  k_pre_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
+  {
+    int groups_per_block = 128 / 8;
+    int need = grid_for(N, groups_per_block);
+    int cap = s->sm_count * 4;
+    k_replan<<<need < cap ? need : cap, 128, 0, st>>>(s->S, t);
+  }
+  k_reach_verify<<<reach_grid(s, N), kWarpsPerBlock * 32, s->reach_smem, st>>>(s->S);
+  k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
+  s->launches += 4;
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_shield_tick_host(HrgShield* s, const double* keypoints_host, const double* t_host,
+                         const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
+                         double* ddq_host, uint8_t* flags_host, void* stream) {
+  if (!s || !keypoints_host || !t_host) return fail(HRG_EINVAL, "hrg_shield_tick_host: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t N = s->S.N, J = s->S.J, K3 = (size_t)s->S.K * 3;
+  CK(cudaMemcpyAsync(s->d_kp, keypoints_host, N * K3 * sizeof(double), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(s->d_t, t_host, N * sizeof(double), cudaMemcpyHostToDevice, st));
+  int rc = hrg_shield_human_measurement(s, nullptr, s->d_kp, s->d_t, stream);
+  if (rc) return rc;
+  if (goal_mask_host && goal_q_host) {
+    CK(cudaMemcpyAsync(s->d_goal_mask, goal_mask_host, N, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(s->d_goal, goal_q_host, N * J * sizeof(double), cudaMemcpyHostToDevice, st));
+    rc = hrg_shield_new_goal(s, s->d_goal_mask, s->d_goal, nullptr, stream);
+    if (rc) return rc;
+  }
+  rc = hrg_shield_step(s, s->d_t, s->d_q, s->d_dq, s->d_ddq, nullptr, s->d_safe, s->d_branch, nullptr, stream);
+  if (rc) return rc;
+  if (q_host) CK(cudaMemcpyAsync(q_host, s->d_q, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (dq_host) CK(cudaMemcpyAsync(dq_host, s->d_dq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (ddq_host) CK(cudaMemcpyAsync(ddq_host, s->d_ddq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (flags_host) {
+    k_pack_flags<<<grid_for((int)N, 256), 256, 0, st>>>((int)N, s->d_safe, s->d_branch, s->d_flags8);
+    s->launches++;
+    CK(cudaMemcpyAsync(flags_host, s->d_flags8, N, cudaMemcpyDeviceToHost, st));
+  }
+  return HRG_OK;
+}
+
+}  // extern "C"
+#include "hrg_shield_extra.cuh"

@@ -1,0 +1,194 @@
+// Second half of the C ABI (included at the end of hrg_shield.cu): getters, statistics, user-supplied LTT and the
+// per-stage entry points used by the parity tests and by ncu.
+#pragma once
+
+namespace {
+
+__global__ void k_copy_stats(HrgStats* dst, HrgStats* src, int clear) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    *dst = *src;
+    if (clear) {
+      HrgStats z;
+      z.n_steps = 0; z.n_unsafe = 0; z.n_branch[0] = z.n_branch[1] = z.n_branch[2] = 0;
+      z.n_replan = 0; z.n_replan_failed = 0; z.n_near_threshold = 0; z.ltt_len_sum = 0;
+      z.min_dist = INFINITY;
+      *src = z;
+    }
+  }
+}
+
+// SafetyShield::setLongTermTrajectory (SS/src/safety_shield.cc:699-730) for one env; traj already on the device.
+__global__ void k_set_ltt(DevState S, int e, const double* __restrict__ traj, int length, double sample_time,
+                          int starting_index, const double* __restrict__ alpha, int32_t* verdict) {
+  __shared__ int s_verdict;
+  const HrgConfig& c = *S.cfg;
+  const int J = S.J, N = S.N;
+  if (threadIdx.x == 0) {
+    uint32_t f = S.flags[e];
+    const int live = (f & F_LIVE_SLOT) ? 1 : 0;
+    PathS p;
+    path_load(S, (f & F_REC_CURRENT) ? P_REC : P_FS, e, p);
+    double q[HRG_MAX_JOINTS], dq[HRG_MAX_JOINTS], ddq[HRG_MAX_JOINTS], dddq[HRG_MAX_JOINTS];
+    ltt_interpolate(S, c, e, live, p.pos, p.vel, p.acc, p.jerk, q, dq, ddq, dddq);
+    int v = 0;
+    for (int j = 0; j < J && v == 0; ++j)
+      if (fabs(dq[j]) > 1e-4 || fabs(ddq[j]) > 1e-4 || fabs(dddq[j]) > 1e-4) v = 1;  // RobotMovementException
+    const double* first = traj + (size_t)ltt_index(0, starting_index, length, 0) * 4 * J;
+    const double* last = traj + (size_t)ltt_index(length - 1, starting_index, length, 0) * 4 * J;
+    for (int j = 0; j < J && v == 0; ++j)
+      if (fabs(q[j] - first[j]) > 1e-3) v = 2;  // hasSamePos (motion.h:151-160)
+    for (int j = 0; j < J && v == 0; ++j)
+      if (fabs(dq[j] - first[J + j]) > 1e-4) v = 3;  // hasSameVel
+    for (int j = 0; j < J && v == 0; ++j)
+      if (fabs(last[J + j]) > 1e-4 || fabs(last[2 * J + j]) > 1e-4 || fabs(last[3 * J + j]) > 1e-4) v = 4;
+    if (v == 0) {
+      const int pend = 1 - live;
+      S.ltt_len[(size_t)pend * N + e] = length;
+      S.ltt_cur[(size_t)pend * N + e] = 0;
+      S.ltt_start[(size_t)pend * N + e] = starting_index;
+      S.ltt_t0[(size_t)pend * N + e] = 0.0;
+      S.ltt_ts[(size_t)pend * N + e] = sample_time;
+      for (int j = 0; j < J; ++j) S.ltt_alpha[((size_t)pend * J + j) * N + e] = alpha[j];
+      f |= F_NEW_LTT | F_NEW_LTT_PROCESSED;
+      S.flags[e] = f;
+    }
+    s_verdict = v;
+    *verdict = v;
+  }
+  __syncthreads();
+  if (s_verdict == 0) {
+    const int pend = (S.flags[e] & F_LIVE_SLOT) ? 0 : 1;
+    double* dst = ltt_sample_w(S, e, pend, 0);
+    for (int i = threadIdx.x; i < length * 4 * J; i += blockDim.x) dst[i] = traj[i];
+  }
+}
+}  // namespace
+
+extern "C" {
+
+int hrg_shield_store_capsules(HrgShield* s, int on) {
+  if (!s) return fail(HRG_EINVAL, "hrg_shield_store_capsules: NULL handle");
+  CK(cudaSetDevice(s->device));
+  if (on && !s->S.robot_caps) {
+    int rc = s->alloc(&s->S.robot_caps, (size_t)s->S.N * s->S.J * 7);
+    if (rc) return rc;
+    rc = s->alloc(&s->S.human_caps, (size_t)s->S.N * s->S.H * 7);
+    if (rc) return rc;
+  }
+  return HRG_OK;
+}
+
+int hrg_shield_get_capsules(HrgShield* s, double* robot, double* human, double* min_dist, void* stream) {
+  if (!s) return fail(HRG_EINVAL, "hrg_shield_get_capsules: NULL handle");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if ((robot || human) && !s->S.robot_caps)
+    return fail(HRG_EINVAL, "capsules are not stored: call hrg_shield_store_capsules(s, 1) before stepping");
+  const size_t N = s->S.N;
+  if (robot) CK(cudaMemcpyAsync(robot, s->S.robot_caps, N * s->S.J * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  if (human) CK(cudaMemcpyAsync(human, s->S.human_caps, N * s->S.H * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  if (min_dist) CK(cudaMemcpyAsync(min_dist, s->S.min_dist, N * 3 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  return HRG_OK;
+}
+
+int hrg_shield_stats(HrgShield* s, HrgStats* out, int clear, void* stream) {
+  if (!s || !out) return fail(HRG_EINVAL, "hrg_shield_stats: NULL argument");
+  k_copy_stats<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(out, s->S.stats, clear);
+  s->launches++;
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_shield_set_ltt(HrgShield* s, int env, const double* traj_host, int length, double sample_time,
+                       int starting_index, const double* alpha_i_host, int32_t* verdict_host) {
+  if (!s || !traj_host || !alpha_i_host || !verdict_host) return fail(HRG_EINVAL, "hrg_shield_set_ltt: NULL argument");
+  if (env < 0 || env >= s->S.N) return fail(HRG_EINVAL, "hrg_shield_set_ltt: env out of range");
+  if (length < 1 || length > s->S.L) return fail(HRG_EINVAL, "hrg_shield_set_ltt: length exceeds ltt_capacity");
+  if (!(sample_time > 0)) return fail(HRG_EINVAL, "hrg_shield_set_ltt: sample_time must be > 0");
+  CK(cudaSetDevice(s->device));
+  const int J = s->S.J;
+  double* d = nullptr;
+  const size_t nb = ((size_t)length * 4 * J + J) * sizeof(double);
+  CK(cudaMalloc(&d, nb + sizeof(int32_t) * 2));
+  cudaError_t ce = cudaMemcpy(d, traj_host, (size_t)length * 4 * J * sizeof(double), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess)
+    ce = cudaMemcpy(d + (size_t)length * 4 * J, alpha_i_host, J * sizeof(double), cudaMemcpyHostToDevice);
+  int32_t* dv = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(d) + nb);
+  if (ce == cudaSuccess) {
+    k_set_ltt<<<1, 128>>>(s->S, env, d, length, sample_time, starting_index, d + (size_t)length * 4 * J, dv);
+    s->launches++;
+    ce = cudaMemcpy(verdict_host, dv, sizeof(int32_t), cudaMemcpyDeviceToHost);
+  }
+  cudaFree(d);
+  if (ce != cudaSuccess) return fail(HRG_ECUDA, "hrg_shield_set_ltt", ce);
+  return HRG_OK;
+}
+
+// ---- per-stage entry points ------------------------------------------------------------------------------------
+int hrg_stage_capsule_dist(int n, const double* c1, const double* c2, double* dist, void* stream) {
+  if (n < 0 || !c1 || !c2 || !dist) return fail(HRG_EINVAL, "hrg_stage_capsule_dist: bad argument");
+  if (n == 0) return HRG_OK;
+  k_stage_capsule_dist<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(n, c1, c2, dist);
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_stage_plan_safety_shield(double sample_time, int n, const double* in, uint8_t* ok, double* phases, double* fin,
+                                 void* stream) {
+  if (n < 0 || !in || !ok || !phases || !fin) return fail(HRG_EINVAL, "hrg_stage_plan_safety_shield: bad argument");
+  if (n == 0) return HRG_OK;
+  k_stage_plan_safety_shield<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(sample_time, n, in, ok,
+                                                                                               phases, fin);
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_stage_ltp_plan(const HrgConfig* cfg, int n, const double* goal, const double* q0, const double* v0,
+                       const double* a0, double* traj, int32_t* length, int cap, void* stream) {
+  int rc = cfg_check(cfg);
+  if (rc) return rc;
+  if (n < 0 || !goal || !q0 || !v0 || !a0 || !traj || !length || cap < 1)
+    return fail(HRG_EINVAL, "hrg_stage_ltp_plan: bad argument");
+  if (n == 0) return HRG_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  HrgConfig* d = nullptr;
+  CK(cudaMalloc(&d, sizeof(HrgConfig)));
+  cudaError_t ce = cudaMemcpyAsync(d, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice, st);
+  if (ce == cudaSuccess) {
+    k_stage_ltp_plan<<<grid_for(n, 64), 64, 0, st>>>(d, n, goal, q0, v0, a0, traj, length, cap);
+    ce = cudaStreamSynchronize(st);
+  }
+  cudaFree(d);
+  if (ce != cudaSuccess) return fail(HRG_ECUDA, "hrg_stage_ltp_plan", ce);
+  return HRG_OK;
+}
+
+int hrg_stage_reach_verify(const HrgConfig* cfg, int n, const double* base_pose, const double* q_start,
+                           const double* q_goal, const double* s_diff, const double* t_reach, const double* alpha_i,
+                           const double* kp_pos, const double* kp_vel, double* robot, double* human, double* min_dist,
+                           uint8_t* is_safe, void* stream) {
+  int rc = cfg_check(cfg);
+  if (rc) return rc;
+  if (n < 0 || !base_pose || !q_start || !q_goal || !s_diff || !t_reach || !alpha_i || !kp_pos || !kp_vel)
+    return fail(HRG_EINVAL, "hrg_stage_reach_verify: bad argument");
+  if (n == 0) return HRG_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  HrgConfig* d = nullptr;
+  CK(cudaMalloc(&d, sizeof(HrgConfig)));
+  cudaError_t ce = cudaMemcpyAsync(d, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice, st);
+  if (ce == cudaSuccess) {
+    const int H = cfg->n_ext + 2 * cfg->n_bodies;
+    const size_t smem = (size_t)kWarpsPerBlock * reach_smem_doubles(cfg->n_keypoints, H) * sizeof(double);
+    cudaFuncSetAttribute(k_stage_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int need = (n + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    int grid = need < 148 * 8 ? need : 148 * 8;
+    k_stage_reach_verify<<<grid, kWarpsPerBlock * 32, smem, st>>>(d, n, base_pose, q_start, q_goal, s_diff, t_reach,
+                                                                  alpha_i, kp_pos, kp_vel, robot, human, min_dist,
+                                                                  is_safe);
+    ce = cudaStreamSynchronize(st);
+  }
+  cudaFree(d);
+  if (ce != cudaSuccess) return fail(HRG_ECUDA, "hrg_stage_reach_verify", ce);
+  return HRG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,288 @@
+// Thread-per-env kernels of one shield tick (scalar path logic; coalesced field-major state) and the replan kernel
+// (one lane per (env, joint), 8-lane groups).
+#pragma once
+#include "ltp_math.cuh"
+#include "step_logic.cuh"
+
+namespace hrg {
+
+constexpr int kTickBlock = 128;
+
+__global__ void k_new_goal(DevState S, const uint8_t* __restrict__ mask, const double* __restrict__ goal_q) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= S.N) return;
+  if (mask && !mask[e]) return;
+  new_goal_env(S, *S.cfg, e, goal_q + (size_t)e * S.J);
+}
+
+// step() up to the replan decision; envs that do not replan go straight on to the potential trajectory.
+__global__ void __launch_bounds__(kTickBlock) k_pre_plan(DevState S, const double* __restrict__ t) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= S.N) return;
+  const HrgConfig& c = *S.cfg;
+  uint32_t f = S.flags[e];
+  if (pre_env(S, c, e, f)) {
+    const int slot = atomicAdd(S.replan_count, 1);
+    S.replan_list[slot] = e;
+  } else {
+    plan_env(S, c, e, t[e], f);
+  }
+  S.flags[e] = f;
+}
+
+// calculateLongTermTrajectory (SS/src/safety_shield.cc:732-760) -> LongTermPlanner::planTrajectory
+// (LTP/src/long_term_planner.cc:7-63) for the envs on the replan list: lane j of an 8-lane group plans joint j
+// (lanes >= J shadow joint J-1 and never write); group-wide decisions go through width-8 shuffles / ballots.
+// Lane 0 then finishes the env's step up to the reach/verify hand-over.
+__global__ void __launch_bounds__(128) k_replan(DevState S, const double* __restrict__ t) {
+  const HrgConfig& c = *S.cfg;
+  const int lane = threadIdx.x & 31;
+  const int gl = lane & 7;                       // lane in group
+  const unsigned gmask = 0xFFu << (lane & 24);   // the 8 lanes of this group
+  const int group = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const int ngroups = (gridDim.x * blockDim.x) >> 3;
+  const int count = *S.replan_count;
+  const int J = S.J, N = S.N;
+  const int j = gl < J ? gl : J - 1;
+  const bool writer = gl < J;
+  LtpLimits L;
+  L.v_max = c.v_max[j]; L.a_max = c.a_max_ltt[j]; L.j_max = c.j_max_ltt[j]; L.t_sample = c.sample_time;
+  for (int idx = group; idx < count; idx += ngroups) {
+    const int e = S.replan_list[idx];
+    uint32_t f = S.flags[e];
+    const int pend = (f & F_LIVE_SLOT) ? 0 : 1;
+    const double* cur = S.cur + (size_t)e * cur_stride(J);
+    const double q_0 = cur[j], v_0 = cur[J + j], a_0 = cur[2 * J + j];
+    const double q_goal = S.goal_q[(size_t)j * N + e];
+    uint32_t status = HRG_ST_REPLANNED;
+    int len = 0;
+    bool ok = ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0);
+    ok = (__ballot_sync(gmask, ok) & gmask) == gmask;
+    JointPlan opt, sc;
+    if (ok) {
+      ltp_zero7(opt.T);
+      ok = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, opt.T, opt.dir, opt.mod);
+      ok = (__ballot_sync(gmask, ok) & gmask) == gmask;
+    }
+    if (ok) {
+      double t_required = -1;
+      int slowest = -1;
+      for (int k = 0; k < J; ++k) {
+        double tk = __shfl_sync(gmask, opt.T[6], k, 8);
+        if (tk > t_required) {
+          t_required = tk;
+          slowest = k;
+        }
+      }
+      ok = slowest != -1;
+      if (ok) {
+        sc = opt;
+        sc.v_drive = L.v_max;
+        ltp_zero7(sc.T);
+        if (j != slowest)
+          ltp_time_scaling(L, q_goal, q_0, v_0, a_0, opt.dir, t_required, sc.T, sc.v_drive, sc.mod);
+        double mx = sc.T[0];
+        for (int k = 1; k < 7; ++k) mx = (mx < sc.T[k]) ? sc.T[k] : mx;
+        if (mx <= 0.0)
+          for (int k = 0; k < 7; ++k) sc.T[k] = opt.T[k];
+        len = ltp_joint_len(L, sc);
+        for (int o = 4; o > 0; o >>= 1) {
+          int other = __shfl_xor_sync(gmask, len, o, 8);
+          len = other > len ? other : len;
+        }
+        if (len > S.L) {
+          status |= HRG_ST_LTT_TRUNCATED;
+          ok = false;
+        } else if (len < 1) {
+          ok = false;
+        }
+      }
+    }
+    if (ok) {
+      double qf = c.q_min[j];
+      if (writer) qf = ltp_sample_joint(L, sc, q_0, v_0, a_0, len, ltt_sample_w(S, e, pend, 0) + j, J, (size_t)4 * J);
+      bool in = !(qf < c.q_min[j] || qf > c.q_max[j]);
+      ok = (__ballot_sync(gmask, in) & gmask) == gmask;
+    }
+    if (ok && writer) {
+      S.replan_q[(size_t)j * N + e] = q_0;  // last_replan_start_motion_ = current_motion (:593)
+      // SSM/OFF: alpha_i_ = alpha_i_max (long_term_traj.h:108-116)
+      S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
+    }
+    __syncwarp(gmask);
+    if (gl == 0) {
+      if (ok) {
+        S.ltt_len[(size_t)pend * N + e] = len;
+        S.ltt_cur[(size_t)pend * N + e] = 0;
+        S.ltt_start[(size_t)pend * N + e] = S.path_sd[e];
+        S.ltt_t0[(size_t)pend * N + e] = S.path_s[e];
+        S.ltt_ts[(size_t)pend * N + e] = c.sample_time;
+        f |= F_NEW_LTT;
+        f &= ~F_NEW_LTT_PROCESSED;
+      } else {
+        f &= ~F_NEW_LTT;
+        status |= HRG_ST_REPLAN_FAILED;
+      }
+      f &= ~F_PENDING_REPLAN;
+      f |= status << F_STATUS_SHIFT;
+      plan_env(S, c, e, t[e], f);
+      S.flags[e] = f;
+    }
+    __syncwarp(gmask);
+  }
+}
+
+// determineNextMotion + setpoint write-out + statistics. Also re-arms the replan list for the next tick.
+__global__ void __launch_bounds__(kTickBlock)
+    k_select(DevState S, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe, uint8_t* branch,
+             uint32_t* status) {
+  __shared__ unsigned long long s_cnt[8];
+  __shared__ double s_min;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0ull;
+  if (threadIdx.x == 0) s_min = INFINITY;
+  __syncthreads();
+  if (e == 0) *S.replan_count = 0;
+  unsigned long long my[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum
+  double my_min = INFINITY;
+  if (e < S.N) {
+    const HrgConfig& c = *S.cfg;
+    uint32_t f = S.flags[e];
+    select_env(S, c, e, f, q, dq, ddq, dddq);
+    f |= F_NEW_LTT_PROCESSED | F_STEPPED;  // safety_shield.cc:641
+    S.flags[e] = f;
+    const uint32_t st = f >> F_STATUS_SHIFT;
+    const int br = (f & F_BRANCH_MASK) >> F_BRANCH_SHIFT;
+    if (is_safe) is_safe[e] = (f & F_IS_SAFE) ? 1 : 0;
+    if (branch) branch[e] = (uint8_t)br;
+    if (status) status[e] = st;
+    if (S.stats) {
+      my[0] = (f & F_IS_SAFE) ? 0 : 1;
+      my[1 + br] = 1;
+      my[4] = (st & HRG_ST_REPLANNED) ? 1 : 0;
+      my[5] = (st & HRG_ST_REPLAN_FAILED) ? 1 : 0;
+      my[6] = (st & HRG_ST_NEAR_THRESHOLD) ? 1 : 0;
+      if ((st & HRG_ST_REPLANNED) && !(st & HRG_ST_REPLAN_FAILED))
+        my[7] = (unsigned long long)S.ltt_len[(size_t)((f & F_LIVE_SLOT) ? 0 : 1) * S.N + e];
+      if (f & F_VERIFY) {
+        const double* md = S.min_dist + (size_t)e * 3;
+        my_min = fmin(md[0], fmin(md[1], md[2]));
+      }
+    }
+  }
+  if (S.stats) {
+    for (int k = 0; k < 8; ++k) {
+      unsigned long long v = my[k];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_cnt[k], v);
+    }
+    for (int o = 16; o > 0; o >>= 1) my_min = fmin(my_min, __shfl_xor_sync(0xffffffffu, my_min, o));
+    if ((threadIdx.x & 31) == 0 && my_min < INFINITY) {
+      // monotone CAS min on the bit pattern (values may be negative => compare as doubles)
+      unsigned long long* a = reinterpret_cast<unsigned long long*>(&s_min);
+      unsigned long long old = *a;
+      while (__longlong_as_double((long long)old) > my_min) {
+        unsigned long long prev = atomicCAS(a, old, (unsigned long long)__double_as_longlong(my_min));
+        if (prev == old) break;
+        old = prev;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int n_here = S.N - blockIdx.x * blockDim.x;
+      if (n_here > (int)blockDim.x) n_here = blockDim.x;
+      unsigned long long* g = reinterpret_cast<unsigned long long*>(S.stats);
+      atomicAdd(&g[0], (unsigned long long)n_here);
+      for (int k = 0; k < 8; ++k)
+        if (s_cnt[k]) atomicAdd(&g[1 + k], s_cnt[k]);
+      if (s_min < INFINITY) {
+        unsigned long long* a = reinterpret_cast<unsigned long long*>(&S.stats->min_dist);
+        unsigned long long old = *a;
+        while (__longlong_as_double((long long)old) > s_min) {
+          unsigned long long prev = atomicCAS(a, old, (unsigned long long)__double_as_longlong(s_min));
+          if (prev == old) break;
+          old = prev;
+        }
+      }
+    }
+  }
+}
+
+// SafetyShield ctor tail / reset (SS/src/safety_shield.cc:147-160,164-201): clear flags and paths, seat the base pose,
+// install the 1-sample LTT at init_qpos, prime the paths with computesPotentialTrajectory(is_safe_, 0) +
+// determineNextMotion(is_safe_). The human keypoint buffers are deliberately left alone: HumanReach::reset only sets
+// last_meas_timestep_ = -1 (human_reach.cc:44-50), so the old velocity survives until two new measurements arrived.
+__global__ void k_reset(DevState S, const uint8_t* __restrict__ mask, const double* __restrict__ base_pose,
+                        const double* __restrict__ init_q, const int32_t* __restrict__ shield_type) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= S.N) return;
+  if (mask && !mask[e]) return;
+  const HrgConfig& c = *S.cfg;
+  const int J = S.J, N = S.N;
+  const uint32_t type = shield_type ? (uint32_t)shield_type[e] : (uint32_t)HRG_SHIELD_SSM;
+  uint32_t f = S.flags[e] & F_UNDER_V_LIMIT;  // is_under_v_limit_ is not touched by reset()
+  f |= (type << F_TYPE_SHIFT) & F_TYPE_MASK;
+  if (type == HRG_SHIELD_OFF) f |= F_IS_SAFE;
+  const double* p = base_pose + (size_t)e * 6;
+  base_pose_matrix(p[0], p[1], p[2], p[3], p[4], p[5], S.base_T + (size_t)e * 12);
+  S.last_meas[e] = -1;
+  PathS z;
+  path_clear(z);
+  for (int w = 0; w < N_PATHS; ++w) path_store(S, w, e, z);
+  S.path_s[e] = 0;
+  S.path_sd[e] = 0;
+  // live slot 0 = {Motion(0.0, init_qpos)}
+  double* m = ltt_sample_w(S, e, 0, 0);
+  for (int j = 0; j < J; ++j) {
+    m[j] = init_q[(size_t)e * J + j];
+    m[J + j] = 0.0; m[2 * J + j] = 0.0; m[3 * J + j] = 0.0;
+    S.prev_dq[(size_t)j * N + e] = 0.0;
+    S.ltt_alpha[((size_t)0 * J + j) * N + e] = (type == HRG_SHIELD_PFL) ? 0.0 : c.alpha_i_max;
+  }
+  if (S.ltt_cart) S.ltt_cart[((size_t)e * 2 + 0) * S.L] = 0.0;
+  for (int s = 0; s < 2; ++s) {
+    S.ltt_len[(size_t)s * N + e] = 1;
+    S.ltt_cur[(size_t)s * N + e] = 0;
+    S.ltt_start[(size_t)s * N + e] = 0;
+    S.ltt_t0[(size_t)s * N + e] = 0.0;
+    S.ltt_ts[(size_t)s * N + e] = c.sample_time;
+  }
+  double gq[HRG_MAX_JOINTS], s_d, t_brake;
+  int gslot;
+  potential_env(S, c, e, f, gq, s_d, t_brake, gslot);
+  select_env(S, c, e, f, nullptr, nullptr, nullptr, nullptr);
+  S.flags[e] = f;
+  for (int k = 0; k < 3; ++k) S.min_dist[(size_t)e * 3 + k] = INFINITY;
+}
+
+// ---- stage entry points ----------------------------------------------------------------------------------------
+__global__ void k_stage_capsule_dist(int n, const double* __restrict__ c1, const double* __restrict__ c2,
+                                     double* __restrict__ dist) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  dist[i] = capsule_capsule_dist(cap_load(c1 + (size_t)i * 7), cap_load(c2 + (size_t)i * 7));
+}
+
+__global__ void k_stage_plan_safety_shield(double ts, int n, const double* __restrict__ in, uint8_t* ok,
+                                           double* phases, double* fin) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double* a = in + (size_t)i * 6;
+  PathS p;
+  path_clear(p);
+  bool touched;
+  ok[i] = plan_safety_shield(a[0], a[1], a[2], a[3], a[4], a[5], ts, p, touched) ? 1 : 0;
+  for (int k = 0; k < 6; ++k) phases[(size_t)i * 6 + k] = p.ph[k];
+  path_final(p, fin[(size_t)i * 3], fin[(size_t)i * 3 + 1], fin[(size_t)i * 3 + 2]);
+}
+
+__global__ void k_stage_ltp_plan(const HrgConfig* __restrict__ cfg, int n, const double* goal, const double* q0,
+                                 const double* v0, const double* a0, double* traj, int32_t* length, int cap) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int J = cfg->nb_joints;
+  length[i] = ltp_plan_env_seq(*cfg, goal + (size_t)i * J, q0 + (size_t)i * J, v0 + (size_t)i * J, a0 + (size_t)i * J,
+                               traj + (size_t)i * cap * 4 * J, cap);
+}
+
+}  // namespace hrg

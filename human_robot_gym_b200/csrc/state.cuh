@@ -49,7 +49,8 @@ struct DevState {
   int32_t* ltt_cur;   // [2][N]  current_pos_
   int32_t* ltt_start; // [2][N]  starting_index_
   double* ltt_t0;     // [2][N]  time of sample 0 (= path_s_ at planning; PFL scan)
-  double* ltt_alpha;  // [2][J][N] alpha_i_ (PFL; NULL when PFL is not enabled: SSM uses cfg->alpha_i_max)
+  double* ltt_ts;     // [2][N]  sample_time_ of the LTT (differs from the shield's only for user-supplied LTTs)
+  double* ltt_alpha;  // [2][J][N] alpha_i_ of the LTT
   // ---- env-major [N][..]
   double* base_T;     // [N][12] rows 0..2 of the base pose matrix
   double* kp_pos;     // [N][K*3]
@@ -101,7 +102,7 @@ HRG_HD void ltt_interpolate(const DevState& S, const HrgConfig& c, int e, int sl
                             double ddds, double* q, double* dq, double* ddq, double* dddq) {
   int sample;
   double dt;
-  ltt_locate(s, c.sample_time, S.ltt_start[(size_t)slot * S.N + e], S.ltt_len[(size_t)slot * S.N + e],
+  ltt_locate(s, S.ltt_ts[(size_t)slot * S.N + e], S.ltt_start[(size_t)slot * S.N + e], S.ltt_len[(size_t)slot * S.N + e],
              S.ltt_cur[(size_t)slot * S.N + e], sample, dt);
   const double* m = ltt_sample(S, e, slot, sample);
   const int J = S.J;

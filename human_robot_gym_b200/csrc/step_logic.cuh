@@ -18,15 +18,15 @@ HRG_HD void new_goal_env(const DevState& S, const HrgConfig& c, int e, const dou
   S.flags[e] = f;
 }
 
-// computesPotentialTrajectory (:367-456) + joint-limit check (:617-621) + hand-over to reach/verify.
-// `f` is the env's flag word (updated in place, caller stores it).
-HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uint32_t& f) {
+// computesPotentialTrajectory(is_safe_, next_motion_.getVelocity()) (:367-456). `f` is the env's flag word (updated in
+// place, caller stores it). Outputs the goal motion's angles, its path position s_d, the slot it was interpolated from
+// and t_brake (= potential_path_.getPhase(3)).
+HRG_HD void potential_env(const DevState& S, const HrgConfig& c, int e, uint32_t& f, double* gq, double& s_goal,
+                          double& t_brake_out, int& gslot_out) {
   const int J = S.J, N = S.N;
   const double ts = c.sample_time;
   const int live = (f & F_LIVE_SLOT) ? 1 : 0, pend = 1 - live;
   const uint32_t type = (f & F_TYPE_MASK) >> F_TYPE_SHIFT;
-  // :612-614
-  if ((f & F_NEW_LTT) && !(f & F_NEW_LTT_PROCESSED)) f &= ~F_IS_SAFE;
   const bool v = (f & F_IS_SAFE) != 0;
   // :370-376 advance the LTT cursors to the travelled path position
   double path_s = S.path_s[e];
@@ -107,10 +107,23 @@ HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uin
   double s_d, ds_d, dds_d;
   path_final(pot, s_d, ds_d, dds_d);
   const double ddds_d = fs.jerk;
-  const double t_brake = pot.ph[2];
-  double gq[HRG_MAX_JOINTS], gdq[HRG_MAX_JOINTS], gddq[HRG_MAX_JOINTS], gdddq[HRG_MAX_JOINTS];
+  double gdq[HRG_MAX_JOINTS], gddq[HRG_MAX_JOINTS], gdddq[HRG_MAX_JOINTS];
   const int gslot = (f & F_NEW_LTT) ? pend : live;
   ltt_interpolate(S, c, e, gslot, s_d, ds_d, dds_d, ddds_d, gq, gdq, gddq, gdddq);
+  s_goal = s_d;
+  t_brake_out = pot.ph[2];
+  gslot_out = gslot;
+}
+
+// Middle part of step() (:606-637): potential trajectory, joint-limit check, hand-over to reach + verify.
+HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uint32_t& f) {
+  const int J = S.J, N = S.N;
+  const uint32_t type = (f & F_TYPE_MASK) >> F_TYPE_SHIFT;
+  // :612-614
+  if ((f & F_NEW_LTT) && !(f & F_NEW_LTT_PROCESSED)) f &= ~F_IS_SAFE;
+  double gq[HRG_MAX_JOINTS], s_d, t_brake;
+  int gslot;
+  potential_env(S, c, e, f, gq, s_d, t_brake, gslot);
   // :617-637
   f &= ~F_VERIFY;
   if (type != HRG_SHIELD_OFF) {
@@ -127,8 +140,7 @@ HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uin
       for (int j = 0; j < J; ++j) {
         ri[j] = cur[j];
         ri[J + j] = gq[j];
-        ri[2 * J + j] = (S.ltt_alpha && type == HRG_SHIELD_PFL) ? S.ltt_alpha[((size_t)gslot * J + j) * N + e]
-                                                               : c.alpha_i_max;
+        ri[2 * J + j] = S.ltt_alpha[((size_t)gslot * J + j) * N + e];  // getAlphaI() (:606-610)
       }
       ri[3 * J] = s_d - cur[4 * J];                      // goal_motion.getS() - current_motion.getS()
       ri[3 * J + 1] = t - S.last_meas[e] + t_brake;      // human_reach.cc:79
@@ -190,7 +202,7 @@ HRG_HD bool pre_env(const DevState& S, const HrgConfig& c, int e, uint32_t& f) {
   return false;
 }
 
-// determineNextMotion (:511-553) + :639-641. Writes the setpoints (env-major [N][J], any pointer may be NULL).
+// determineNextMotion (:511-553); the caller sets new_ltt_processed_ (:641). Writes the setpoints (env-major [N][J], any pointer may be NULL).
 HRG_HD void select_env(const DevState& S, const HrgConfig& c, int e, uint32_t& f, double* q_out, double* dq_out,
                        double* ddq_out, double* dddq_out) {
   const int J = S.J, N = S.N;
@@ -234,7 +246,6 @@ HRG_HD void select_env(const DevState& S, const HrgConfig& c, int e, uint32_t& f
     if (ddq_out) ddq_out[(size_t)e * J + j] = ddq[j];
     if (dddq_out) dddq_out[(size_t)e * J + j] = dddq[j];
   }
-  f |= F_NEW_LTT_PROCESSED | F_STEPPED;
   f = (f & ~F_BRANCH_MASK) | ((uint32_t)branch << F_BRANCH_SHIFT);
 }
 

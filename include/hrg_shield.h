@@ -108,10 +108,15 @@ int hrg_shield_new_goal(HrgShield* s, const uint8_t* env_mask, const double* goa
                         void* stream);
 
 /* SafetyShield.setLongTermTrajectory(traj) — bindings :109 / safety_shield.cc:699-730 — for ONE env.
- * traj [L,4,J] (q,dq,ddq,dddq per sample), times of samples are not needed by the SSM path. Returns in *verdict:
+ * traj [L,4,J] (q,dq,ddq,dddq per sample) HOST pointer; sample_time/starting_index/alpha_i [J] are the LongTermTraj's
+ * own (long_term_traj.h:108-116). Synchronous. Returns in *verdict:
  * 0 installed, 1 RobotMovementException, 2 start position differs, 3 start velocity differs, 4 does not end stopped. */
 int hrg_shield_set_ltt(HrgShield* s, int env, const double* traj_host, int length, double sample_time,
-                       int32_t* verdict_host, void* stream);
+                       int starting_index, const double* alpha_i_host, int32_t* verdict_host);
+
+/* Keep the robot/human capsules of every step for hrg_shield_get_capsules (off by default: it adds 56(J+H) bytes of
+ * writes per env-step that only the visualisation getters need). Takes effect from the next step. */
+int hrg_shield_store_capsules(HrgShield* s, int on);
 
 /* SafetyShield.step(cycle_begin_time) — bindings :107 / safety_shield.cc:555-647 — for every env.
  * t [N]; outputs (any may be NULL): q,dq,ddq,dddq [N,J]; is_safe [N] u8 (getSafety, bindings :113);
