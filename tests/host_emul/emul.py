@@ -1,0 +1,127 @@
+"""ctypes view of the TEST-ONLY host emulation (tests/host_emul/emul.cc). Never imported by the product."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from human_robot_gym_b200.cabi import HrgConfig
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "libhrg_emul.so")
+_lib = None
+_p = C.c_void_p
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        src = os.path.join(_HERE, "emul.cc")
+        if not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(src):
+            subprocess.check_call([os.path.join(_HERE, "build.sh")])
+        L = C.CDLL(_LIB)
+        L.emul_create.restype = C.c_void_p
+        L.emul_create.argtypes = [C.POINTER(HrgConfig), C.c_int, _p, _p, _p]
+        L.emul_destroy.argtypes = [_p]
+        L.emul_reset.argtypes = [_p] * 5
+        L.emul_human_measurement.argtypes = [_p] * 4
+        L.emul_new_goal.argtypes = [_p] * 3
+        L.emul_step.argtypes = [_p] * 9
+        L.emul_get_capsules.argtypes = [_p] * 4
+        L.emul_get_state.argtypes = [_p, C.c_int, _p]
+        L.emul_capsule_dist.argtypes = [C.c_int, _p, _p, _p]
+        L.emul_plan_safety_shield.argtypes = [C.c_double, C.c_int, _p, _p, _p, _p]
+        L.emul_ltp_plan.restype = C.c_int
+        L.emul_ltp_plan.argtypes = [C.POINTER(HrgConfig), _p, _p, _p, _p, _p, C.c_int]
+        L.emul_poly_root.restype = C.c_double
+        L.emul_poly_root.argtypes = [_p, C.c_int]
+        _lib = L
+    return _lib
+
+
+def _a(x, dt=np.float64):
+    return np.ascontiguousarray(x, dtype=dt)
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+class EmulBatch:
+    def __init__(self, cfg: HrgConfig, n, base_pose, init_q, shield_type=1):
+        self.cfg, self.n, self.J, self.K = cfg, n, cfg.nb_joints, cfg.n_keypoints
+        self.H = cfg.n_ext + 2 * cfg.n_bodies
+        bp = _a(np.broadcast_to(_a(base_pose), (n, 6)))
+        q0 = _a(np.broadcast_to(_a(init_q), (n, self.J)))
+        ty = _a(np.broadcast_to(np.asarray(shield_type), (n,)), np.int32)
+        self.h = lib().emul_create(C.byref(cfg), n, _ptr(bp), _ptr(q0), _ptr(ty))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().emul_destroy(self.h)
+            self.h = None
+
+    def reset(self, base_pose, init_q, shield_type=1, mask=None):
+        bp = _a(np.broadcast_to(_a(base_pose), (self.n, 6)))
+        q0 = _a(np.broadcast_to(_a(init_q), (self.n, self.J)))
+        ty = _a(np.broadcast_to(np.asarray(shield_type), (self.n,)), np.int32)
+        m = None if mask is None else _a(mask, np.uint8)
+        lib().emul_reset(self.h, _ptr(m), _ptr(bp), _ptr(q0), _ptr(ty))
+
+    def human_measurement(self, kp, t, mask=None):
+        kp = _a(kp).reshape(self.n, self.K, 3)
+        tt = _a(np.broadcast_to(t, (self.n,)))
+        m = None if mask is None else _a(mask, np.uint8)
+        lib().emul_human_measurement(self.h, _ptr(m), _ptr(kp), _ptr(tt))
+
+    def new_goal(self, goal_q, mask=None):
+        g = _a(goal_q).reshape(self.n, self.J)
+        m = None if mask is None else _a(mask, np.uint8)
+        lib().emul_new_goal(self.h, _ptr(m), _ptr(g))
+
+    def step(self, t):
+        tt = _a(np.broadcast_to(t, (self.n,)))
+        o = {k: np.zeros((self.n, self.J)) for k in ("q", "dq", "ddq", "dddq")}
+        o["is_safe"] = np.zeros(self.n, np.uint8)
+        o["branch"] = np.zeros(self.n, np.uint8)
+        o["status"] = np.zeros(self.n, np.uint32)
+        lib().emul_step(self.h, _ptr(tt), _ptr(o["q"]), _ptr(o["dq"]), _ptr(o["ddq"]), _ptr(o["dddq"]),
+                        _ptr(o["is_safe"]), _ptr(o["branch"]), _ptr(o["status"]))
+        return o
+
+    def capsules(self):
+        r, h, md = np.zeros((self.n, self.J, 7)), np.zeros((self.n, self.H, 7)), np.zeros((self.n, 3))
+        lib().emul_get_capsules(self.h, _ptr(r), _ptr(h), _ptr(md))
+        return r, h, md
+
+    def state(self, e):
+        o = np.zeros(52)
+        lib().emul_get_state(self.h, e, _ptr(o))
+        return o
+
+
+def capsule_dist(c1, c2):
+    c1, c2 = _a(c1).reshape(-1, 7), _a(c2).reshape(-1, 7)
+    d = np.zeros(c1.shape[0])
+    lib().emul_capsule_dist(c1.shape[0], _ptr(c1), _ptr(c2), _ptr(d))
+    return d
+
+
+def plan_safety_shield(ts, cases):
+    cases = _a(cases).reshape(-1, 6)
+    n = cases.shape[0]
+    ok, ph, fin = np.zeros(n, np.uint8), np.zeros((n, 6)), np.zeros((n, 3))
+    lib().emul_plan_safety_shield(ts, n, _ptr(cases), _ptr(ok), _ptr(ph), _ptr(fin))
+    return ok, ph, fin
+
+
+def ltp_plan(cfg, goal, q0, v0, a0, cap=4096):
+    J = cfg.nb_joints
+    traj = np.zeros((cap, 4, J))
+    L = lib().emul_ltp_plan(C.byref(cfg), _ptr(_a(goal)), _ptr(_a(q0)), _ptr(_a(v0)), _ptr(_a(a0)), _ptr(traj), cap)
+    return L, traj[: max(L, 0)]
+
+
+def poly_root(coef):
+    c = _a(coef)
+    return lib().emul_poly_root(_ptr(c), c.shape[0])
