@@ -1,0 +1,166 @@
+"""BatchedSafetyShield — N independent sara-shield instances stepped together on one B200.
+
+Same verbs as the reference `safety_shield_py.SafetyShield` (SS/bindings/safety_shield_bindings.cpp:82-115) over
+`[N, ...]` FP64 CUDA tensors. PyTorch is only plumbing here (device memory, streams); the arithmetic runs in the
+hand-written sm_100a kernels of libhrg_shield.so behind the C ABI of include/hrg_shield.h. No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import cabi
+from .config import ShieldConfig
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+class BatchedSafetyShield:
+    def __init__(self, n_envs: int, sample_time: float, trajectory_config_file: str, robot_config_file: str,
+                 mocap_config_file: str, base_pose=None, init_qpos=None, shield_type=cabi.SHIELD_SSM,
+                 device: Optional[torch.device] = None, ltt_capacity: int = 1024, store_capsules: bool = False,
+                 config: Optional[ShieldConfig] = None):
+        self.lib = cabi.load_library()  # raises if the CUDA extension is missing
+        if not torch.cuda.is_available():
+            raise cabi.ShieldLibraryError("BatchedSafetyShield needs a CUDA device; there is no CPU fallback")
+        self.config = config or ShieldConfig.from_files(sample_time, trajectory_config_file, robot_config_file,
+                                                        mocap_config_file)
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.n_envs = int(n_envs)
+        self.cfg = cabi.make_cfg(self.config, ltt_capacity)
+        self.J, self.K = self.cfg.nb_joints, self.cfg.n_keypoints
+        self.H = self.cfg.n_ext + 2 * self.cfg.n_bodies
+        N, J = self.n_envs, self.J
+        pose = np.zeros((N, 6)) if base_pose is None else np.broadcast_to(np.asarray(base_pose, np.float64), (N, 6))
+        q0 = np.zeros((N, J)) if init_qpos is None else np.broadcast_to(np.asarray(init_qpos, np.float64), (N, J))
+        ty = np.broadcast_to(np.asarray(shield_type, np.int32), (N,))
+        pose, q0, ty = np.ascontiguousarray(pose), np.ascontiguousarray(q0), np.ascontiguousarray(ty)
+        h = C.c_void_p()
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        cabi.check(self.lib.hrg_shield_create(C.byref(self.cfg), N, dev_index, pose.ctypes.data, q0.ctypes.data,
+                                              ty.ctypes.data, C.byref(h)), "hrg_shield_create")
+        self._h = h
+        f64 = dict(dtype=torch.float64, device=self.device)
+        self.q = torch.zeros(N, J, **f64)
+        self.dq = torch.zeros(N, J, **f64)
+        self.ddq = torch.zeros(N, J, **f64)
+        self.dddq = torch.zeros(N, J, **f64)
+        self.is_safe = torch.zeros(N, dtype=torch.uint8, device=self.device)
+        self.branch = torch.zeros(N, dtype=torch.uint8, device=self.device)
+        self.status = torch.zeros(N, dtype=torch.int32, device=self.device)
+        self._stats = torch.zeros(10, dtype=torch.int64, device=self.device)
+        self._store = False
+        if store_capsules:
+            self.store_capsules(True)
+
+    # ------------------------------------------------------------------------------------------------ helpers
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _f64(self, x, shape):
+        t = torch.as_tensor(x, dtype=torch.float64, device=self.device)
+        return t.expand(shape).contiguous() if t.shape != torch.Size(shape) else t.contiguous()
+
+    def _mask(self, m):
+        if m is None:
+            return None
+        return torch.as_tensor(m, device=self.device).to(torch.uint8).contiguous()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            torch.cuda.synchronize(self.device)
+            self.lib.hrg_shield_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---------------------------------------------------------------------------------------------------- verbs
+    def reset(self, base_pose, init_qpos, current_time=0.0, shield_type=cabi.SHIELD_SSM, env_mask=None):
+        N, J = self.n_envs, self.J
+        pose, q0 = self._f64(base_pose, (N, 6)), self._f64(init_qpos, (N, J))
+        t = self._f64(current_time, (N,))
+        ty = torch.as_tensor(shield_type, dtype=torch.int32, device=self.device).expand(N).contiguous()
+        m = self._mask(env_mask)
+        cabi.check(self.lib.hrg_shield_reset(self._h, _ptr(m), _ptr(pose), _ptr(q0), _ptr(t), _ptr(ty), self._stream()),
+                   "hrg_shield_reset")
+
+    def humanMeasurement(self, keypoints, time, env_mask=None):
+        kp = self._f64(keypoints, (self.n_envs, self.K, 3))
+        t = self._f64(time, (self.n_envs,))
+        m = self._mask(env_mask)
+        cabi.check(self.lib.hrg_shield_human_measurement(self._h, _ptr(m), _ptr(kp), _ptr(t), self._stream()),
+                   "hrg_shield_human_measurement")
+
+    def newLongTermTrajectory(self, goal_position, goal_velocity=None, env_mask=None):
+        gq = self._f64(goal_position, (self.n_envs, self.J))
+        gd = None if goal_velocity is None else self._f64(goal_velocity, (self.n_envs, self.J))
+        m = self._mask(env_mask)
+        cabi.check(self.lib.hrg_shield_new_goal(self._h, _ptr(m), _ptr(gq), _ptr(gd), self._stream()),
+                   "hrg_shield_new_goal")
+
+    def step(self, cycle_begin_time):
+        """One shield tick for every env. Returns (q, dq, ddq, dddq) views of the output tensors [N, J]."""
+        t = self._f64(cycle_begin_time, (self.n_envs,))
+        cabi.check(self.lib.hrg_shield_step(self._h, _ptr(t), _ptr(self.q), _ptr(self.dq), _ptr(self.ddq),
+                                            _ptr(self.dddq), _ptr(self.is_safe), _ptr(self.branch), _ptr(self.status),
+                                            self._stream()), "hrg_shield_step")
+        return self.q, self.dq, self.ddq, self.dddq
+
+    def getSafety(self):
+        return self.is_safe.bool()
+
+    def store_capsules(self, on=True):
+        cabi.check(self.lib.hrg_shield_store_capsules(self._h, int(bool(on))), "hrg_shield_store_capsules")
+        self._store = bool(on)
+
+    def capsules(self):
+        """(robot [N,J,7], human [N,H,7], min_dist [N,3]) of the last step; needs store_capsules(True) beforehand."""
+        f64 = dict(dtype=torch.float64, device=self.device)
+        robot = torch.zeros(self.n_envs, self.J, 7, **f64) if self._store else None
+        human = torch.zeros(self.n_envs, self.H, 7, **f64) if self._store else None
+        md = torch.zeros(self.n_envs, 3, **f64)
+        cabi.check(self.lib.hrg_shield_get_capsules(self._h, _ptr(robot), _ptr(human), _ptr(md), self._stream()),
+                   "hrg_shield_get_capsules")
+        return robot, human, md
+
+    def set_ltt(self, env: int, traj: np.ndarray, sample_time: float, starting_index: int, alpha_i) -> int:
+        traj = np.ascontiguousarray(traj, dtype=np.float64).reshape(-1, 4, self.J)
+        alpha = np.ascontiguousarray(np.broadcast_to(np.asarray(alpha_i, np.float64), (self.J,)))
+        verdict = C.c_int32(-1)
+        torch.cuda.synchronize(self.device)
+        cabi.check(self.lib.hrg_shield_set_ltt(self._h, int(env), traj.ctypes.data, traj.shape[0], float(sample_time),
+                                               int(starting_index), alpha.ctypes.data, C.addressof(verdict)),
+                   "hrg_shield_set_ltt")
+        return verdict.value
+
+    def stats(self, clear=False) -> dict:
+        cabi.check(self.lib.hrg_shield_stats(self._h, _ptr(self._stats), int(clear), self._stream()), "hrg_shield_stats")
+        v = self._stats.cpu()
+        md = v[9:10].view(torch.float64).item()
+        return {"n_steps": int(v[0]), "n_unsafe": int(v[1]), "n_branch": [int(v[2]), int(v[3]), int(v[4])],
+                "n_replan": int(v[5]), "n_replan_failed": int(v[6]), "n_near_threshold": int(v[7]),
+                "ltt_len_sum": int(v[8]), "min_dist": md}
+
+    def stats_tensor(self, clear=False) -> torch.Tensor:
+        """Raw [10] int64 device tensor (last word = min_dist bits) for the cross-GPU all_reduce."""
+        cabi.check(self.lib.hrg_shield_stats(self._h, _ptr(self._stats), int(clear), self._stream()), "hrg_shield_stats")
+        return self._stats
+
+    def launch_count(self) -> int:
+        return int(self.lib.hrg_shield_launch_count(self._h))
+
+    def tick_host(self, kp_host: torch.Tensor, t_host: torch.Tensor, goal_mask_host, goal_q_host, q_host, dq_host,
+                  ddq_host, flags_host):
+        """humanMeasurement + [newLongTermTrajectory] + step with pinned HOST tensors (copies on the current stream)."""
+        cabi.check(self.lib.hrg_shield_tick_host(self._h, kp_host.data_ptr(), t_host.data_ptr(), _ptr(goal_mask_host),
+                                                 _ptr(goal_q_host), _ptr(q_host), _ptr(dq_host), _ptr(ddq_host),
+                                                 _ptr(flags_host), self._stream()), "hrg_shield_tick_host")
