@@ -155,6 +155,16 @@ class BatchedSafetyShield:
         cabi.check(self.lib.hrg_shield_stats(self._h, _ptr(self._stats), int(clear), self._stream()), "hrg_shield_stats")
         return self._stats
 
+    def profile(self, max_steps: int):
+        cabi.check(self.lib.hrg_shield_profile(self._h, int(max_steps)), "hrg_shield_profile")
+
+    def profile_read(self):
+        """({kernel: total ms}, steps) of the profiled steps since profile(max_steps)."""
+        ms = (C.c_double * 4)()
+        n = C.c_int(0)
+        cabi.check(self.lib.hrg_shield_profile_read(self._h, C.addressof(ms), C.addressof(n)), "hrg_shield_profile_read")
+        return dict(zip(("k_pre_plan", "k_replan", "k_reach_verify", "k_select"), list(ms))), n.value
+
     def launch_count(self) -> int:
         return int(self.lib.hrg_shield_launch_count(self._h))
 

@@ -101,6 +101,8 @@ SYMBOLS = {
     "hrg_shield_tick_host": (C.c_int, [C.c_void_p] + [C.c_void_p] * 8 + [_vp]),
     "hrg_shield_get_capsules": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _vp]),
     "hrg_shield_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _vp]),
+    "hrg_shield_profile": (C.c_int, [C.c_void_p, C.c_int]),
+    "hrg_shield_profile_read": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "hrg_shield_num_envs": (C.c_int, [C.c_void_p]),
     "hrg_shield_num_human_capsules": (C.c_int, [C.c_void_p]),
     "hrg_shield_launch_count": (C.c_int64, [C.c_void_p]),

@@ -67,6 +67,10 @@ struct HrgShield {
   uint8_t* d_branch = nullptr;
   uint8_t* d_flags8 = nullptr;
   size_t reach_smem = 0;
+  // optional per-kernel timing of hrg_shield_step (bench.py's roofline leg): 5 boundary events per step
+  bool prof = false;
+  std::vector<cudaEvent_t> ev;
+  size_t ev_used = 0;
 
   template <class T>
   int alloc(T** p, size_t n) {
@@ -220,6 +224,7 @@ int hrg_shield_destroy(HrgShield* s) {
   if (!s) return HRG_OK;
   cudaSetDevice(s->device);
   for (void* p : s->allocs) cudaFree(p);
+  for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
   delete s;
   return HRG_OK;
 }
@@ -265,15 +270,25 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   if (!s || !t) return fail(HRG_EINVAL, "hrg_shield_step: NULL argument");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int N = s->S.N;
+  const bool prof = s->prof && s->ev_used + 5 <= s->ev.size();
+  cudaEvent_t* ev = prof ? &s->ev[s->ev_used] : nullptr;
+  if (prof) {
+    s->ev_used += 5;
+    cudaEventRecord(ev[0], st);
+  }
   k_pre_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
+  if (prof) cudaEventRecord(ev[1], st);
   {
     int groups_per_block = 128 / 8;
     int need = grid_for(N, groups_per_block);
     int cap = s->sm_count * 4;
     k_replan<<<need < cap ? need : cap, 128, 0, st>>>(s->S, t);
   }
+  if (prof) cudaEventRecord(ev[2], st);
   k_reach_verify<<<reach_grid(s, N), kWarpsPerBlock * 32, s->reach_smem, st>>>(s->S);
+  if (prof) cudaEventRecord(ev[3], st);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
+  if (prof) cudaEventRecord(ev[4], st);
   s->launches += 4;
   CK(cudaGetLastError());
   return HRG_OK;

@@ -123,6 +123,36 @@ int hrg_shield_set_ltt(HrgShield* s, int env, const double* traj_host, int lengt
   return HRG_OK;
 }
 
+int hrg_shield_profile(HrgShield* s, int max_steps) {
+  if (!s || max_steps < 0) return fail(HRG_EINVAL, "hrg_shield_profile: bad argument");
+  CK(cudaSetDevice(s->device));
+  while (s->ev.size() < (size_t)max_steps * 5) {
+    cudaEvent_t e;
+    CK(cudaEventCreate(&e));
+    s->ev.push_back(e);
+  }
+  s->prof = max_steps > 0;
+  s->ev_used = 0;
+  return HRG_OK;
+}
+
+int hrg_shield_profile_read(HrgShield* s, double* ms_host, int* steps_host) {
+  if (!s || !ms_host || !steps_host) return fail(HRG_EINVAL, "hrg_shield_profile_read: NULL argument");
+  CK(cudaSetDevice(s->device));
+  for (int k = 0; k < 4; ++k) ms_host[k] = 0.0;
+  const size_t steps = s->ev_used / 5;
+  if (steps) CK(cudaEventSynchronize(s->ev[s->ev_used - 1]));
+  for (size_t i = 0; i < steps; ++i)
+    for (int k = 0; k < 4; ++k) {
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, s->ev[i * 5 + k], s->ev[i * 5 + k + 1]));
+      ms_host[k] += ms;
+    }
+  *steps_host = (int)steps;
+  s->ev_used = 0;
+  return HRG_OK;
+}
+
 // ---- per-stage entry points ------------------------------------------------------------------------------------
 int hrg_stage_capsule_dist(int n, const double* c1, const double* c2, double* dist, void* stream) {
   if (n < 0 || !c1 || !c2 || !dist) return fail(HRG_EINVAL, "hrg_stage_capsule_dist: bad argument");

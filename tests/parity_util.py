@@ -1,0 +1,141 @@
+"""Shared helpers of the parity tests, smoke() and bench.py's checker legs (test infrastructure)."""
+from __future__ import annotations
+
+import json
+import os
+import tempfile
+
+import numpy as np
+import yaml
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_CFG_DIR = None
+
+
+def configs() -> dict:
+    with open(os.path.join(ROOT, "tests", "golden", "configs.json")) as f:
+        return json.load(f)
+
+
+def config_dir() -> str:
+    """The golden configs written back out as YAML files in the reference schema (once per process)."""
+    global _CFG_DIR
+    if _CFG_DIR is None:
+        d = tempfile.mkdtemp(prefix="shield_cfg_")
+        for name, content in configs().items():
+            with open(os.path.join(d, name + ".yaml"), "w") as f:
+                yaml.safe_dump(content, f, default_flow_style=None)
+        # builder-supplied "full body, long horizon" variants for BASELINE config 4
+        full = full_body_mocap(configs()["mujoco_mocap"])
+        with open(os.path.join(d, "mujoco_mocap_full_body.yaml"), "w") as f:
+            yaml.safe_dump(full, f, default_flow_style=None)
+        long_h = dict(configs()["trajectory_parameters_schunk"])
+        long_h["max_s_stop"] = 0.5
+        with open(os.path.join(d, "trajectory_parameters_schunk_long.yaml"), "w") as f:
+            yaml.safe_dump(long_h, f, default_flow_style=None)
+        _CFG_DIR = d
+    return _CFG_DIR
+
+
+def full_body_mocap(base: dict) -> dict:
+    """mujoco_mocap.yaml + legs, pelvis and spine: 16 bodies, 4 extremities -> H = 4 + 16 + 16 = 36 capsules."""
+    m = json.loads(json.dumps(base))
+    extra = [("L_UpperLeg", "L_Hip", "L_Knee", 0.2), ("R_UpperLeg", "R_Hip", "R_Knee", 0.2),
+             ("L_LowerLeg", "L_Knee", "L_Ankle", 0.132), ("R_LowerLeg", "R_Knee", "R_Ankle", 0.132),
+             ("L_Foot", "L_Ankle", "L_Toe", 0.1), ("R_Foot", "R_Ankle", "R_Toe", 0.1),
+             ("Pelvis", "L_Hip", "R_Hip", 0.3), ("Spine", "Torso", "Chest", 0.434)]
+    for name, p, d, th in extra:
+        m["bodies"].append({"name": name, "proximal": p, "distal": d, "thickness": th})
+    m["extremities"].append({"name": "L_Leg", "base": "L_Hip", "end": "L_Toe", "length": 1.0, "thickness": 0.0})
+    m["extremities"].append({"name": "R_Leg", "base": "R_Hip", "end": "R_Toe", "length": 1.0, "thickness": 0.0})
+    return m
+
+
+def default_files(robot="schunk", mocap="mujoco_mocap", traj=None):
+    d = config_dir()
+    traj = traj or f"trajectory_parameters_{robot}"
+    return (os.path.join(d, traj + ".yaml"), os.path.join(d, f"robot_parameters_{robot}.yaml"),
+            os.path.join(d, mocap + ".yaml"))
+
+
+def mocap_joint_names(mocap_file: str):
+    from human_robot_gym_b200.config import load_yaml
+    return load_yaml(mocap_file)["joint_names"]
+
+
+def make_checker(files, n, base_pose, init_q, sample_time=0.004, shield_type=1, threads=8):
+    """The CPU checker for a batch: the reference build (oracle/_ref) when present, else the C restatement."""
+    from oracle import ref
+    if ref.available():
+        return ref.RefBatch(n, sample_time, files[0], files[1], files[2], base_pose, init_q, shield_type=shield_type,
+                            threads=threads), "reference"
+    from oracle import port
+    return port.PortBatch(n, sample_time, files, base_pose, init_q, shield_type=shield_type), "port"
+
+
+def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0", sample_time=0.004, shield_type=1,
+                        goal_period=25, stagger=True, ltt_capacity=1024, base_pose=None, collect=None):
+    """Drives BatchedSafetyShield (CUDA) and the CPU checker in lockstep on identical synthetic inputs.
+
+    Decisions (is_safe, branch) must match exactly; an env whose FIRST mismatch happens on a tick where either side
+    reports a capsule distance within 1e-6 m of 0 is counted as near-threshold and excluded (north_star). Envs are
+    dropped from the comparison after their first mismatch (their closed loops have diverged).
+    """
+    import torch
+
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    from human_robot_gym_b200.config import ShieldConfig
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+
+    sc = ShieldConfig.from_files(sample_time, *files)
+    scen = SyntheticScenario(n_envs, mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, seed)
+    pose = np.zeros((n_envs, 6)) if base_pose is None else np.broadcast_to(np.asarray(base_pose, float), (n_envs, 6))
+    pose = np.ascontiguousarray(pose)
+    chk, kind = make_checker(files, n_envs, pose, scen.init_q, sample_time, shield_type)
+    gpu = BatchedSafetyShield(n_envs, sample_time, *files, base_pose=pose, init_qpos=scen.init_q,
+                              shield_type=shield_type, device=device, ltt_capacity=ltt_capacity, store_capsules=True)
+    H = gpu.H
+    alive = np.ones(n_envs, bool)
+    n_mis, n_near, max_sp, max_md, max_caps = 0, 0, 0.0, 0.0, 0.0
+    hist = np.zeros(3, np.int64)
+    unsafe = 0
+    phase = (np.arange(n_envs) % goal_period) if stagger else np.zeros(n_envs, int)
+    for k in range(ticks):
+        t = k * sample_time
+        kp = scen.keypoints(t)
+        chk.human_measurement(kp, t)
+        gpu.humanMeasurement(torch.from_numpy(kp), t)
+        gmask = (phase == (k % goal_period))
+        if gmask.any():
+            g = scen.next_goal(gmask)
+            chk.new_goal(g, mask=gmask)
+            gpu.newLongTermTrajectory(torch.from_numpy(g), env_mask=torch.from_numpy(gmask))
+        a = chk.step(t)
+        gpu.step(t)
+        b = {"q": gpu.q.cpu().numpy(), "dq": gpu.dq.cpu().numpy(), "ddq": gpu.ddq.cpu().numpy(),
+             "dddq": gpu.dddq.cpu().numpy(), "is_safe": gpu.is_safe.cpu().numpy(), "branch": gpu.branch.cpu().numpy(),
+             "status": gpu.status.cpu().numpy()}
+        r_g, h_g, md_g = [x.cpu().numpy() for x in gpu.capsules()]
+        r_c, h_c, md_c = chk.capsules(H)
+        bad = ((a["is_safe"] != b["is_safe"]) | (a["branch"] != b["branch"])) & alive
+        if bad.any():
+            near = ((b["status"] & 32) != 0) | (np.abs(np.where(np.isfinite(md_c), md_c, 1.0)).min(axis=1) < 1e-6)
+            n_near += int((bad & near).sum())
+            n_mis += int((bad & ~near).sum())
+            alive &= ~bad
+        if alive.any():
+            for key in ("q", "dq", "ddq", "dddq"):
+                max_sp = max(max_sp, float(np.abs(a[key][alive] - b[key][alive]).max()))
+            ver = alive & np.isfinite(md_g).all(axis=1) & np.isfinite(md_c).all(axis=1)
+            if ver.any():
+                max_md = max(max_md, float(np.abs(md_g[ver] - md_c[ver]).max()))
+                max_caps = max(max_caps, float(np.abs(r_g[ver] - r_c[ver]).max()), float(np.abs(h_g[ver] - h_c[ver]).max()))
+            hist += np.bincount(a["branch"][alive], minlength=3)[:3]
+            unsafe += int((a["is_safe"][alive] == 0).sum())
+        if collect is not None:
+            collect(k, a, b)
+    stats = gpu.stats()
+    gpu.close()
+    return {"checker": kind, "n_envs": n_envs, "ticks": ticks, "mismatch_excl_near": n_mis, "near_threshold_excluded": n_near,
+            "max_setpoint_diff": max_sp, "max_min_dist_diff": max_md, "max_capsule_diff": max_caps,
+            "branch_hist": hist.tolist(), "unsafe_frac": unsafe / max(1, int(hist.sum())), "gpu_stats": stats}

@@ -1,0 +1,155 @@
+"""-m gpu: the CUDA path, called through the C ABI, against the CPU checker on identical seeded inputs."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests import parity_util as pu
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def _lib():
+    from human_robot_gym_b200 import cabi
+    return cabi, cabi.load_library()
+
+
+def _dev(a, dtype=None):
+    return torch.as_tensor(np.ascontiguousarray(a), device="cuda:0") if dtype is None else torch.as_tensor(
+        np.ascontiguousarray(a), dtype=dtype, device="cuda:0")
+
+
+def random_capsules(rng, n):
+    c = np.zeros((n, 7))
+    c[:, :3] = rng.uniform(-1, 1, (n, 3))
+    c[:, 3:6] = c[:, :3] + rng.uniform(-0.6, 0.6, (n, 3))
+    c[:, 6] = rng.uniform(0.02, 0.3, n)
+    return c
+
+
+def capsule_cases(seed=7, n=200000):
+    rng = np.random.default_rng(seed)
+    c1, c2 = random_capsules(rng, n), random_capsules(rng, n)
+    k = n // 10
+    c1[:k, 3:6] = c1[:k, :3]                      # sphere vs capsule
+    c2[k:2 * k, 3:6] = c2[k:2 * k, :3]            # capsule vs sphere
+    c1[2 * k:3 * k, 3:6] = c1[2 * k:3 * k, :3]    # sphere vs sphere
+    c2[2 * k:3 * k, 3:6] = c2[2 * k:3 * k, :3]
+    # exactly parallel, axis aligned (denom == 0 branch incl. the chained comparisons)
+    s = slice(3 * k, 4 * k)
+    ax = rng.integers(0, 3, k)
+    for c in (c1, c2):
+        p = np.round(rng.uniform(-1, 1, (k, 3)), 2)
+        c[s, :3] = p
+        c[s, 3:6] = p
+        c[s, 3 + 0] += np.where(ax == 0, np.round(rng.uniform(0.1, 1, k), 2), 0)
+        c[s, 3 + 1] += np.where(ax == 1, np.round(rng.uniform(0.1, 1, k), 2), 0)
+        c[s, 3 + 2] += np.where(ax == 2, np.round(rng.uniform(0.1, 1, k), 2), 0)
+    # touching: distance within ~1e-7 of the threshold
+    s = slice(4 * k, 5 * k)
+    c2[s, 6] = 0.0
+    return c1, c2
+
+
+def test_capsule_distance_matches_reference():
+    from oracle import ref
+    cabi, L = _lib()
+    c1, c2 = capsule_cases()
+    want = ref.capsule_dist(c1, c2) if ref.available() else __import__("oracle.port", fromlist=["x"]).capsule_dist(c1, c2)
+    d1, d2 = _dev(c1), _dev(c2)
+    out = torch.zeros(c1.shape[0], dtype=torch.float64, device="cuda:0")
+    cabi.check(L.hrg_stage_capsule_dist(c1.shape[0], d1.data_ptr(), d2.data_ptr(), out.data_ptr(), None))
+    got = out.cpu().numpy()
+    both_nan = np.isnan(want) & np.isnan(got)
+    assert np.array_equal(np.isnan(want), np.isnan(got))
+    diff = np.abs(np.where(both_nan, 0, want - got))
+    assert diff.max() <= 1e-12, diff.max()  # tolerance of north_star is 1e-5; IEEE-identical arithmetic gives ~0
+    flips = ((want < 0) != (got < 0)) & ~both_nan
+    assert flips.sum() == 0
+
+
+def test_plan_safety_shield_grid():
+    """The reference's own 21 x 80 x 101 grid (SS/tests/src/safety_shield_tests.cc:29-53): a_max 10, j_max 100."""
+    cabi, L = _lib()
+    vel = np.arange(21) * 0.05
+    acc = -10 + np.arange(80) * 0.25
+    ve = np.arange(101) * 0.01
+    V, A, E = np.meshgrid(vel, acc, ve, indexing="ij")
+    cases = np.stack([np.zeros(V.size), V.ravel(), A.ravel(), E.ravel(), np.full(V.size, 10.0), np.full(V.size, 100.0)], 1)
+    n = cases.shape[0]
+    ok = torch.zeros(n, dtype=torch.uint8, device="cuda:0")
+    ph = torch.zeros(n, 6, dtype=torch.float64, device="cuda:0")
+    fin = torch.zeros(n, 3, dtype=torch.float64, device="cuda:0")
+    cabi.check(L.hrg_stage_plan_safety_shield(0.001, n, _dev(cases).data_ptr(), ok.data_ptr(), ph.data_ptr(),
+                                              fin.data_ptr(), None))
+    ok, fin = ok.cpu().numpy(), fin.cpu().numpy()
+    assert ok.all()
+    assert np.abs(fin[:, 1] - cases[:, 3]).max() < 1e-6   # final_vel ~ ve
+    assert np.abs(fin[:, 2]).max() < 1e-6                  # final_acc ~ 0
+    from oracle import ref
+    if ref.available():
+        files = pu.default_files("schunk", "cmu_mocap_no_hand")
+        rb = ref.RefBatch(1, 0.001, *files, np.zeros(6), np.zeros(6))
+        ok_r, ph_r, fin_r = rb.plan_safety_shield(cases)
+        assert np.array_equal(ok_r, ok)
+        assert np.abs(ph_r - ph.cpu().numpy()).max() < 1e-12
+        assert np.abs(fin_r - fin).max() < 1e-12
+
+
+def test_long_term_planner_matches_reference():
+    from oracle import ref
+    if not ref.available():
+        pytest.skip("needs oracle/_ref")
+    from human_robot_gym_b200.cabi import make_cfg
+    from human_robot_gym_b200.config import ShieldConfig
+    cabi, L = _lib()
+    files = pu.default_files("schunk")
+    sc = ShieldConfig.from_files(0.004, *files)
+    cap = 1024
+    cfg = make_cfg(sc, cap)
+    J = cfg.nb_joints
+    rng = np.random.default_rng(11)
+    n = 512
+    q0 = rng.uniform(-1.5, 1.5, (n, J))
+    v0 = rng.uniform(-0.6, 0.6, (n, J)) * (rng.random((n, 1)) < 0.7)
+    a0 = rng.uniform(-1.5, 1.5, (n, J)) * (rng.random((n, 1)) < 0.7)
+    goal = np.clip(q0 + rng.uniform(-1.0, 1.0, (n, J)) * rng.choice([0.05, 0.3, 1.0], (n, 1)), sc.traj.q_min_allowed,
+                   sc.traj.q_max_allowed)
+    traj = torch.zeros(n, cap, 4, J, dtype=torch.float64, device="cuda:0")
+    length = torch.zeros(n, dtype=torch.int32, device="cuda:0")
+    cabi.check(L.hrg_stage_ltp_plan(C.byref(cfg), n, _dev(goal).data_ptr(), _dev(q0).data_ptr(), _dev(v0).data_ptr(),
+                                    _dev(a0).data_ptr(), traj.data_ptr(), length.data_ptr(), cap, None))
+    length, traj = length.cpu().numpy(), traj.cpu().numpy()
+    t = sc.traj
+    n_ok, worst = 0, 0.0
+    for i in range(n):
+        Lr, tr = ref.ltp_plan(0.004, t.q_min_allowed, t.q_max_allowed, t.v_max_allowed, t.a_max_ltt, t.j_max_ltt, goal[i],
+                              q0[i], v0[i], a0[i], cap)
+        assert (Lr if Lr <= cap else -Lr) == length[i], (i, Lr, length[i])
+        if Lr > 0 and Lr <= cap:
+            n_ok += 1
+            worst = max(worst, float(np.abs(tr - traj[i, :Lr]).max()))
+    assert n_ok > n // 4
+    assert worst < 1e-5, worst
+
+
+@pytest.mark.parametrize("robot,n_envs,ticks,seed", [("schunk", 512, 150, 1001), ("panda", 512, 150, 1002)])
+def test_closed_loop_matches_checker(robot, n_envs, ticks, seed):
+    res = pu.closed_loop_compare(pu.default_files(robot), n_envs=n_envs, ticks=ticks, seed=seed)
+    print(res)
+    assert res["mismatch_excl_near"] == 0, res
+    assert res["max_setpoint_diff"] < 1e-5, res      # (rad, rad/s, ...) north_star tolerance
+    assert res["max_min_dist_diff"] < 1e-5, res      # metres
+    assert res["max_capsule_diff"] < 1e-5, res
+    assert res["near_threshold_excluded"] <= n_envs // 100
+    assert res["gpu_stats"]["n_steps"] == n_envs * ticks
+    assert res["branch_hist"][0] > 0 and res["branch_hist"][2] > 0
+
+
+def test_full_body_long_horizon():
+    files = pu.default_files("schunk", "mujoco_mocap_full_body", "trajectory_parameters_schunk_long")
+    res = pu.closed_loop_compare(files, n_envs=256, ticks=100, seed=1004)
+    print(res)
+    assert res["mismatch_excl_near"] == 0, res
+    assert res["max_setpoint_diff"] < 1e-5 and res["max_min_dist_diff"] < 1e-5, res
