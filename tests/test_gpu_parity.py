@@ -72,16 +72,17 @@ def test_capsule_distance_matches_reference():
 def test_plan_safety_shield_grid():
     """The reference's own 21 x 80 x 101 grid (SS/tests/src/safety_shield_tests.cc:29-53): a_max 10, j_max 100."""
     cabi, L = _lib()
-    vel = np.arange(21) * 0.05
-    acc = -10 + np.arange(80) * 0.25
-    ve = np.arange(101) * 0.01
+    vel = np.arange(-10, 11) / 10.0
+    acc = np.arange(-40, 40) / 5.0
+    ve = np.arange(101) / 100.0
     V, A, E = np.meshgrid(vel, acc, ve, indexing="ij")
     cases = np.stack([np.zeros(V.size), V.ravel(), A.ravel(), E.ravel(), np.full(V.size, 10.0), np.full(V.size, 100.0)], 1)
     n = cases.shape[0]
     ok = torch.zeros(n, dtype=torch.uint8, device="cuda:0")
     ph = torch.zeros(n, 6, dtype=torch.float64, device="cuda:0")
     fin = torch.zeros(n, 3, dtype=torch.float64, device="cuda:0")
-    cabi.check(L.hrg_stage_plan_safety_shield(0.001, n, _dev(cases).data_ptr(), ok.data_ptr(), ph.data_ptr(),
+    d_cases = _dev(cases)
+    cabi.check(L.hrg_stage_plan_safety_shield(0.001, n, d_cases.data_ptr(), ok.data_ptr(), ph.data_ptr(),
                                               fin.data_ptr(), None))
     ok, fin = ok.cpu().numpy(), fin.cpu().numpy()
     assert ok.all()
@@ -118,8 +119,9 @@ def test_long_term_planner_matches_reference():
                    sc.traj.q_max_allowed)
     traj = torch.zeros(n, cap, 4, J, dtype=torch.float64, device="cuda:0")
     length = torch.zeros(n, dtype=torch.int32, device="cuda:0")
-    cabi.check(L.hrg_stage_ltp_plan(C.byref(cfg), n, _dev(goal).data_ptr(), _dev(q0).data_ptr(), _dev(v0).data_ptr(),
-                                    _dev(a0).data_ptr(), traj.data_ptr(), length.data_ptr(), cap, None))
+    d_goal, d_q0, d_v0, d_a0 = _dev(goal), _dev(q0), _dev(v0), _dev(a0)  # keep the device copies alive over the call
+    cabi.check(L.hrg_stage_ltp_plan(C.byref(cfg), n, d_goal.data_ptr(), d_q0.data_ptr(), d_v0.data_ptr(),
+                                    d_a0.data_ptr(), traj.data_ptr(), length.data_ptr(), cap, None))
     length, traj = length.cpu().numpy(), traj.cpu().numpy()
     t = sc.traj
     n_ok, worst = 0, 0.0
