@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""Shield-steps/sec of the batched B200 safety shield (BASELINE.json metric), with roofline and CPU baseline.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--envs E] [--robot schunk|panda]
+
+One "step" = one shield tick over the whole batch: humanMeasurement + (newLongTermTrajectory for the 1/25 of the envs
+whose policy period starts on this tick) + step. Workload at N=1: the configuration the metric is quoted on —
+Schunk 6-DoF, SSM, mujoco_mocap human (K=23 keypoints, H=18 capsules), 65,536 shields on ONE B200 — and the same
+65,536 shields on EVERY GPU for N>1 (weak scaling, envs are independent; the only collective is one tiny all_reduce of
+the verify statistics after the timed region). Synthetic keypoints/goals (human_robot_gym_b200/synthetic.py).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+SAMPLE_TIME = 0.004
+GOAL_PERIOD = 25  # shield ticks per policy step (human_env.yaml:21,35)
+METRIC = "shield-steps/sec"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=25)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs", type=int, default=65536, help="shields per GPU")
+    ap.add_argument("--robot", default="schunk")
+    ap.add_argument("--mocap", default="mujoco_mocap")
+    ap.add_argument("--traj", default=None)
+    ap.add_argument("--ring", type=int, default=32, help="distinct keypoint frames kept resident (ping-pong replay)")
+    ap.add_argument("--ltt-capacity", type=int, default=512)
+    ap.add_argument("--cpu-envs", type=int, default=4096)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--seed", type=int, default=1003)
+    return ap.parse_args()
+
+
+def workload_name(args, sc):
+    h = sc.human
+    return (f"{args.robot} {sc.robot.nb_joints}-DoF SSM, {args.mocap} human (K={h.n_keypoints}, H={h.n_capsules}), "
+            f"{args.envs} shields per GPU, synthetic keypoints+goals, replans staggered over {GOAL_PERIOD} ticks")
+
+
+def ring_index(k, R):
+    """Ping-pong replay of R frames: continuous positions, velocity flips at the ends."""
+    if R <= 1:
+        return 0
+    p = k % (2 * (R - 1))
+    return p if p < R else 2 * (R - 1) - p
+
+
+def make_inputs(args, sc, n, seed, names):
+    """Host-side synthetic inputs: keypoint ring [R,n,K,3], goal ring [G,n,J], phase masks [25,n]."""
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+    scen = SyntheticScenario(n, names, sc.traj.q_min_allowed, sc.traj.q_max_allowed, seed)
+    kp = np.stack([scen.keypoints(i * SAMPLE_TIME) for i in range(args.ring)])
+    goals = np.stack([scen.next_goal() for _ in range(8)])
+    phase = np.arange(n) % GOAL_PERIOD
+    masks = np.stack([(phase == p) for p in range(GOAL_PERIOD)]).astype(np.uint8)
+    return scen, kp, goals, masks
+
+
+def cpu_loop(args, files, sc, names, n_cpu, warmup, steps, threads, budget_s=25.0):
+    """The reference's own per-env CPU shield loop (SS/src/debug.cc:38-55 shape) on `threads` host threads."""
+    from tests.parity_util import make_checker
+    scen, kp, goals, masks = make_inputs(args, sc, n_cpu, args.seed + 7919, names)
+    chk, kind = make_checker(files, n_cpu, np.zeros((n_cpu, 6)), scen.init_q, SAMPLE_TIME, 1, threads)
+    mb = masks.astype(bool)
+
+    def tick(k):
+        t = k * SAMPLE_TIME
+        chk.human_measurement(kp[ring_index(k, args.ring)], t)
+        chk.new_goal(goals[(k // GOAL_PERIOD) % goals.shape[0]], mask=mb[k % GOAL_PERIOD])
+        chk.step(t)
+
+    for k in range(warmup):
+        tick(k)
+    t0 = time.perf_counter()
+    done = 0
+    for k in range(warmup, warmup + steps):
+        tick(k)
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": n_cpu * done / dt, "unit": METRIC, "cores": threads,
+            "kind": "reference" if kind == "reference" else "port",
+            "sample": f"{n_cpu} envs x {done} ticks of the same workload ({warmup} warm-up ticks), "
+                      f"{threads} std::thread workers over a static env partition"}, dt / max(done, 1) * 1e3, done
+
+
+class ClockSampler:
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0]))
+                mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        os.unlink(self.f.name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        return out
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traffic_per_launch(kernel):
+    """dram bytes per launch of `kernel` from the committed ncu --set full summary, if one exists."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get(kernel)
+    return None
+
+
+def run_reference(args, files, sc, names, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    cb, ms, done = cpu_loop(args, files, sc, names, args.cpu_envs, args.warmup, args.steps, threads, budget_s=120.0)
+    line = {"metric": METRIC, "value": cb["value"], "unit": METRIC, "n_gpus": args.gpus, "steps": done,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "impl": "reference",
+            "config": {"workload": workload_name(args, sc), "cpu_sample_envs": args.cpu_envs,
+                       "note": "reference C++ (oracle/_ref) on the host cores; a step here is one tick of the CPU sample"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    from human_robot_gym_b200.config import ShieldConfig
+    from tests.parity_util import default_files, mocap_joint_names
+    files = default_files(args.robot, args.mocap, args.traj)
+    sc = ShieldConfig.from_files(SAMPLE_TIME, *files)
+    names = mocap_joint_names(files[2])
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, files, sc, names, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback for the product path)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    N, J, K = args.envs, sc.robot.nb_joints, sc.human.n_keypoints
+    W, S = args.warmup, args.steps
+    scen, kp_h, goals_h, masks_h = make_inputs(args, sc, N, args.seed + rank, names)
+    shield = BatchedSafetyShield(N, SAMPLE_TIME, *files, init_qpos=scen.init_q, device=dev,
+                                 ltt_capacity=args.ltt_capacity, config=sc)
+    kp_d = torch.from_numpy(kp_h).to(dev)            # [R,N,K,3]
+    goals_d = torch.from_numpy(goals_h).to(dev)      # [G,N,J]
+    masks_d = torch.from_numpy(masks_h).to(dev)      # [25,N]
+    total = W + 3 * S + 8
+    t_d = (torch.arange(total, dtype=torch.float64, device=dev) * SAMPLE_TIME)[:, None].expand(total, N).contiguous()
+
+    def tick(k):
+        shield.tick_device(kp_d[ring_index(k, args.ring)], t_d[k], masks_d[k % GOAL_PERIOD],
+                           goals_d[(k // GOAL_PERIOD) % goals_d.shape[0]])
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    k = 0
+    for _ in range(W):
+        tick(k)
+        k += 1
+    sync_all()
+    shield.stats(clear=True)
+    launches0 = shield.launch_count()
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    e0.record()
+    for _ in range(S):
+        tick(k)
+        k += 1
+    e1.record()
+    sync_all()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    launches = shield.launch_count() - launches0
+    clk = clocks.stop() if clocks else None
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    # verify statistics of the timed region: the one collective of the path (SUM of counts, MIN of min_dist)
+    st = shield.stats_tensor().clone()
+    counts, mind = st[:9].clone(), st[9:10].view(torch.float64).clone()
+    if world > 1:
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mind, op=dist.ReduceOp.MIN)
+    counts = counts.cpu().tolist()
+
+    # ---- per-kernel device time (separate pass so the events do not perturb `value`) ---------------------------
+    shield.profile(S)
+    for _ in range(S):
+        tick(k)
+        k += 1
+    kms, ksteps = shield.profile_read()
+    shield.profile(0)
+
+    # ---- end to end through the C ABI with HOST buffers -----------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        pin = dict(pin_memory=True)
+        kp_p = torch.from_numpy(kp_h).pin_memory()
+        goals_p = torch.from_numpy(goals_h).pin_memory()
+        masks_p = torch.from_numpy(masks_h).pin_memory()
+        t_p = torch.zeros(N, dtype=torch.float64, **pin)
+        q_p, dq_p, ddq_p = (torch.zeros(N, J, dtype=torch.float64, **pin) for _ in range(3))
+        fl_p = torch.zeros(N, dtype=torch.uint8, **pin)
+
+        def tick_host(kk):
+            t_p.fill_(kk * SAMPLE_TIME)
+            shield.tick_host(kp_p[ring_index(kk, args.ring)], t_p, masks_p[kk % GOAL_PERIOD],
+                             goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], q_p, dq_p, ddq_p, fl_p)
+            torch.cuda.current_stream(dev).synchronize()  # the caller consumes the setpoints before the next tick
+
+        for _ in range(max(3, min(W, 10))):
+            tick_host(k)
+            k += 1
+        sync_all()
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(S):
+            tick_host(k)
+            k += 1
+        e1.record()
+        sync_all()
+        ms_e = torch.tensor([max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms_e, op=dist.ReduceOp.MAX)
+        e2e = {"value": N * world * S / (float(ms_e.item()) / 1e3), "unit": METRIC,
+               "h2d_bytes_per_step": N * (K * 3 * 8 + 8 + 1 + J * 8), "d2h_bytes_per_step": N * (3 * J * 8 + 1),
+               "ms_per_step": float(ms_e.item()) / S}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        H = sc.human.n_capsules
+        # algorithmic bytes per env of the dominant kernel (fused K1+K2+K3): reads keypoint positions
+        # and velocities 48K, start/goal angles + alpha 24J, s_diff + t_reach 16; writes is_safe 1 + min_dist 24
+        b_reach = 48 * K + 24 * J + 41
+        dom = max(kms, key=kms.get)
+        dom_ms = kms[dom] / max(ksteps, 1)
+        alg = {"k_reach_verify": b_reach}.get(dom, b_reach)
+        achieved = alg * N / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
+        n_ok = max(1, counts[5] - counts[6])
+        L_mean = counts[8] / n_ok
+        b_tick = 48 * K + 770 + 136 * J
+        b_step = b_tick + (32 * J * L_mean + 16 * J) / GOAL_PERIOD
+        value = N * world * S / (ms_total / 1e3)
+        line = {
+            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": S, "warmup": W,
+            "ms_per_step": ms_total / S, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args, sc), "envs_total": N * world, "sample_time": SAMPLE_TIME,
+                       "l2_note": f"per-step working set {N * b_tick / 1e6:.0f} MB of state + {N * K * 24 / 1e6:.0f} MB "
+                                  "of new keypoints exceeds the 126 MB L2; no explicit flush",
+                       "ltt_capacity": args.ltt_capacity, "mean_ltt_len": L_mean},
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic_per_launch(dom), "peak_source": peak_src,
+                         "algorithmic_bytes_per_env": alg, "kernel_ms": dom_ms},
+            "kernel_ms_per_step": {kk: v / max(ksteps, 1) for kk, v in kms.items()},
+            "roofline_tick": {"algorithmic_bytes_per_step": b_step, "achieved": b_step * N / (ms_total / S / 1e3) / 1e9,
+                              "unit": "GB/s", "frac": b_step * N / (ms_total / S / 1e3) / 1e9 / peak},
+            "verify_stats": {"n_steps": counts[0], "unsafe_frac": counts[1] / max(1, counts[0]),
+                             "branch_hist": counts[2:5], "n_replan": counts[5], "n_replan_failed": counts[6],
+                             "n_near_threshold": counts[7], "min_dist": float(mind.item())},
+            "clocks": clk, "gpu_launches": int(launches),
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if world == 1 and not args.no_cpu:
+            threads = os.cpu_count() or 1
+            cb, _, _ = cpu_loop(args, files, sc, names, min(args.cpu_envs, N), 25, 100, threads)
+            line["cpu_baseline"] = cb
+        print(json.dumps(line), flush=True)
+    shield.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
