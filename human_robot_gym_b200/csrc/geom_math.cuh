@@ -229,26 +229,26 @@ HRG_HD Cap human_accel_capsule(const V3& p1, const V3& p2, const V3& v1, const V
 }
 
 // Human capsule h of the set {Pos[E], Vel[B], Accel[B]} (HumanReach::getAllCapsules, SS/include/safety_shield/
-// human_reach.h:203-205) from the measured keypoints kp/kv [K*3]; t_reach as in human_reach.cc:76-80.
-HRG_HD Cap human_capsule(const HrgConfig& c, int h, const double* kp, const double* kv, double t_reach) {
+// human_reach.h:203-205) from the measured keypoints; t_reach as in human_reach.cc:76-80. Coordinate `comp` of keypoint
+// `k` is kp[(3 * k + comp) * ks]: ks = 1 for one env's contiguous [K*3] record, ks = N (with kp pointing at the env's
+// column) for the field-major device state.
+HRG_HD V3 kp_point(const double* kp, int k, size_t ks) {
+  return v3(kp[(size_t)(3 * k) * ks], kp[(size_t)(3 * k + 1) * ks], kp[(size_t)(3 * k + 2) * ks]);
+}
+HRG_HD Cap human_capsule(const HrgConfig& c, int h, const double* kp, const double* kv, size_t ks, double t_reach) {
   const int E = c.n_ext, B = c.n_bodies;
-  if (h < E) {
-    const double* p = kp + 3 * c.ext_base[h];
-    return human_pos_capsule(v3(p[0], p[1], p[2]), c.ext_vmax[h], c.ext_length[h], c.ext_thickness[h], t_reach,
-                             c.delay, c.meas_err_pos);
-  }
+  if (h < E)
+    return human_pos_capsule(kp_point(kp, c.ext_base[h], ks), c.ext_vmax[h], c.ext_length[h], c.ext_thickness[h],
+                             t_reach, c.delay, c.meas_err_pos);
   const int b = (h - E) % B;
   const bool accel = (h - E) >= B;
-  const double* a = kp + 3 * c.body_prox[b];
-  const double* d = kp + 3 * c.body_dist[b];
-  V3 p1 = v3(a[0], a[1], a[2]), p2 = v3(d[0], d[1], d[2]);
+  const V3 p1 = kp_point(kp, c.body_prox[b], ks), p2 = kp_point(kp, c.body_dist[b], ks);
   if (!accel)
     return human_vel_capsule(p1, p2, c.body_vmax[b][0], c.body_vmax[b][1], c.body_thickness[b], t_reach, c.delay,
                              c.meas_err_pos);
-  const double* va = kv + 3 * c.body_prox[b];
-  const double* vd = kv + 3 * c.body_dist[b];
-  return human_accel_capsule(p1, p2, v3(va[0], va[1], va[2]), v3(vd[0], vd[1], vd[2]), c.body_amax[b][0],
-                             c.body_amax[b][1], c.body_thickness[b], t_reach, c.delay, c.meas_err_pos, c.meas_err_vel);
+  return human_accel_capsule(p1, p2, kp_point(kv, c.body_prox[b], ks), kp_point(kv, c.body_dist[b], ks),
+                             c.body_amax[b][0], c.body_amax[b][1], c.body_thickness[b], t_reach, c.delay,
+                             c.meas_err_pos, c.meas_err_vel);
 }
 
 // Rows 0..2 of the base pose matrix from (x, y, z, roll, pitch, yaw) — RobotReach ctor / reset

@@ -67,6 +67,11 @@ struct HrgShield {
   uint8_t* d_branch = nullptr;
   uint8_t* d_flags8 = nullptr;
   size_t reach_smem = 0;
+  size_t measure_smem = 0;
+  // k_replan runs on its own stream, concurrently with the first reach + verify pass (envs that do not replan)
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool overlap = true;
   // optional per-kernel timing of hrg_shield_step (bench.py's roofline leg): 5 boundary events per step
   bool prof = false;
   std::vector<cudaEvent_t> ev;
@@ -87,11 +92,7 @@ struct HrgShield {
 
 namespace {
 inline int grid_for(int n, int block) { return (n + block - 1) / block; }
-inline int reach_grid(const HrgShield* s, int n) {
-  int need = (n + kWarpsPerBlock - 1) / kWarpsPerBlock;
-  int cap = s->sm_count * 8;  // a multiple of the SM count; warps stride over the remaining envs
-  return need < cap ? (need > 0 ? need : 1) : cap;
-}
+inline int tile_grid(int n) { return (n + kTileEnvs - 1) / kTileEnvs; }
 
 __global__ void k_pack_flags(int n, const uint8_t* __restrict__ safe, const uint8_t* __restrict__ branch,
                              uint8_t* __restrict__ out) {
@@ -161,11 +162,13 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   AL(S.kp_vel, (size_t)K * 3 * N);
   AL(S.last_meas, N);
   AL(S.ltt, (size_t)N * 2 * L * 4 * J);
-  AL(S.cur, (size_t)N * cur_stride(J));
-  AL(S.reach_in, (size_t)N * reach_stride(J));
+  AL(S.cur, (size_t)N * cur_fields(J));
+  AL(S.reach_in, (size_t)N * reach_fields(J));
   AL(S.min_dist, 3 * N);
   AL(S.replan_list, N);
   AL(S.replan_count, 1);
+  AL(S.replan_next, 1);
+  AL(S.replan_mark, N);
   AL(S.stats, 1);
   S.ltt_cart = nullptr;
   S.robot_caps = nullptr;
@@ -185,10 +188,14 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   AL(h->d_branch, N);
   AL(h->d_flags8, N);
 #undef AL
-  h->reach_smem = (size_t)kWarpsPerBlock * reach_smem_doubles(K, H) * sizeof(double);
+  h->reach_smem = (size_t)reach_smem_doubles(J, H) * sizeof(double);
+  h->measure_smem = (size_t)kTileEnvs * ((K * 3) | 1) * sizeof(double);
   cudaFuncSetAttribute(k_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
-  cudaFuncSetAttribute(k_stage_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
-  ce = cudaMemcpy(dcfg, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice);
+  cudaFuncSetAttribute(k_measure, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->measure_smem);
+  ce = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
+  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
+  if (ce == cudaSuccess) ce = cudaMemcpy(dcfg, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice);
   HrgStats st0;
   memset(&st0, 0, sizeof(st0));
   st0.min_dist = INFINITY;
@@ -225,6 +232,9 @@ int hrg_shield_destroy(HrgShield* s) {
   cudaSetDevice(s->device);
   for (void* p : s->allocs) cudaFree(p);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
+  if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+  if (s->ev_join) cudaEventDestroy(s->ev_join);
+  if (s->side) cudaStreamDestroy(s->side);
   delete s;
   return HRG_OK;
 }
@@ -248,7 +258,7 @@ int hrg_shield_human_measurement(HrgShield* s, const uint8_t* env_mask, const do
                                  void* stream) {
   if (!s || !keypoints || !t) return fail(HRG_EINVAL, "hrg_shield_human_measurement: NULL argument");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  k_measure<<<reach_grid(s, s->S.N), kWarpsPerBlock * 32, 0, st>>>(s->S, env_mask, keypoints, t);
+  k_measure<<<tile_grid(s->S.N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, env_mask, keypoints, t);
   s->launches++;
   CK(cudaGetLastError());
   return HRG_OK;
@@ -278,18 +288,29 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   }
   k_pre_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
   if (prof) cudaEventRecord(ev[1], st);
-  {
-    int groups_per_block = 128 / 8;
-    int need = grid_for(N, groups_per_block);
-    int cap = s->sm_count * 4;
-    k_replan<<<need < cap ? need : cap, 128, 0, st>>>(s->S, t);
+  // one warp per replanning env, work fetched from a device counter; the grid only bounds the resident warps
+  const int warps_per_block = kReplanBlock / 32;
+  int rgrid = grid_for(N, warps_per_block);
+  if (rgrid > s->sm_count * 10) rgrid = s->sm_count * 10;
+  const bool fork = s->overlap && !prof;
+  if (fork) {
+    // replan || reach + verify of the envs that do not replan, then the replanned envs
+    CK(cudaEventRecord(s->ev_fork, st));
+    CK(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
+    k_replan<<<rgrid, kReplanBlock, 0, s->side>>>(s->S, t);
+    CK(cudaEventRecord(s->ev_join, s->side));
+    k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 0);
+    CK(cudaStreamWaitEvent(st, s->ev_join, 0));
+  } else {
+    k_replan<<<rgrid, kReplanBlock, 0, st>>>(s->S, t);
+    if (prof) cudaEventRecord(ev[2], st);
+    k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 0);
   }
-  if (prof) cudaEventRecord(ev[2], st);
-  k_reach_verify<<<reach_grid(s, N), kWarpsPerBlock * 32, s->reach_smem, st>>>(s->S);
+  k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 1);
   if (prof) cudaEventRecord(ev[3], st);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
   if (prof) cudaEventRecord(ev[4], st);
-  s->launches += 4;
+  s->launches += 5;
   CK(cudaGetLastError());
   return HRG_OK;
 }

@@ -86,7 +86,11 @@ int hrg_shield_get_capsules(HrgShield* s, double* robot, double* human, double* 
   const size_t N = s->S.N;
   if (robot) CK(cudaMemcpyAsync(robot, s->S.robot_caps, N * s->S.J * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
   if (human) CK(cudaMemcpyAsync(human, s->S.human_caps, N * s->S.H * 7 * sizeof(double), cudaMemcpyDeviceToDevice, st));
-  if (min_dist) CK(cudaMemcpyAsync(min_dist, s->S.min_dist, N * 3 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  if (min_dist) {
+    k_min_dist_out<<<grid_for((int)N, 256), 256, 0, st>>>(s->S, min_dist);
+    s->launches++;
+    CK(cudaGetLastError());
+  }
   return HRG_OK;
 }
 
@@ -202,18 +206,32 @@ int hrg_stage_reach_verify(const HrgConfig* cfg, int n, const double* base_pose,
     return fail(HRG_EINVAL, "hrg_stage_reach_verify: bad argument");
   if (n == 0) return HRG_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  HrgConfig* d = nullptr;
-  CK(cudaMalloc(&d, sizeof(HrgConfig)));
+  // scratch field-major state for this call: [cfg | base_T 12 | reach_in 3J+2 | kp 2*K3 | min_dist 3] x n doubles + flags
+  const int J = cfg->nb_joints, K3 = cfg->n_keypoints * 3, H = cfg->n_ext + 2 * cfg->n_bodies;
+  const size_t per_env = 12 + reach_fields(J) + 2 * (size_t)K3 + 3;
+  const size_t cfg_doubles = (sizeof(HrgConfig) + 7) / 8;
+  double* d = nullptr;
+  CK(cudaMalloc(&d, (cfg_doubles + per_env * n) * sizeof(double) + (size_t)n * sizeof(uint32_t) + 16));
+  DevState S;
+  memset(&S, 0, sizeof(S));
+  S.N = n; S.J = J; S.K = cfg->n_keypoints; S.H = H; S.L = 0;
+  S.cfg = reinterpret_cast<const HrgConfig*>(d);
+  double* p = d + cfg_doubles;
+  S.base_T = p; p += (size_t)12 * n;
+  S.reach_in = p; p += (size_t)reach_fields(J) * n;
+  S.kp_pos = p; p += (size_t)K3 * n;
+  S.kp_vel = p; p += (size_t)K3 * n;
+  S.min_dist = p; p += (size_t)3 * n;
+  S.flags = reinterpret_cast<uint32_t*>(p);
+  S.robot_caps = robot;
+  S.human_caps = human;
   cudaError_t ce = cudaMemcpyAsync(d, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice, st);
   if (ce == cudaSuccess) {
-    const int H = cfg->n_ext + 2 * cfg->n_bodies;
-    const size_t smem = (size_t)kWarpsPerBlock * reach_smem_doubles(cfg->n_keypoints, H) * sizeof(double);
-    cudaFuncSetAttribute(k_stage_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    int need = (n + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    int grid = need < 148 * 8 ? need : 148 * 8;
-    k_stage_reach_verify<<<grid, kWarpsPerBlock * 32, smem, st>>>(d, n, base_pose, q_start, q_goal, s_diff, t_reach,
-                                                                  alpha_i, kp_pos, kp_vel, robot, human, min_dist,
-                                                                  is_safe);
+    const size_t smem = (size_t)reach_smem_doubles(J, H) * sizeof(double);
+    cudaFuncSetAttribute(k_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_stage_pack<<<grid_for(n, 128), 128, 0, st>>>(S, base_pose, q_start, q_goal, s_diff, t_reach, alpha_i, kp_pos, kp_vel);
+    k_reach_verify<<<tile_grid(n), 32 * J, smem, st>>>(S, 0);
+    k_stage_unpack<<<grid_for(n, 128), 128, 0, st>>>(S, min_dist, is_safe);
     ce = cudaStreamSynchronize(st);
   }
   cudaFree(d);

@@ -1,265 +1,256 @@
-// Warp-per-env kernels: human measurement, and robot reach + human reach + ISO verification.
-// One warp owns one env at a time (grid-stride over envs); the env's keypoints, the two FK chains, the robot and the
-// human capsule sets live in that warp's slice of shared memory; the J x H capsule distances are spread over the 32
-// lanes and reduced with ballots / shuffles. FP64 throughout, no tensor cores (nothing here is a contraction).
+// Lane-per-env kernels: human measurement, and robot reach + human reach + ISO verification.
+//
+// k_reach_verify works on tiles of 32 envs: lane = env, warp = robot link. Because every lane of a warp evaluates the
+// SAME link against the SAME human capsule index (for 32 different envs), the sphere / capsule dispatch of ReachLib's
+// capsule_capsule_dist and the Pos / Vel / Accel model dispatch are warp-uniform, so the FP64 pipe sees full warps
+// (the first version spread the J x H pairs of ONE env over the lanes and ran at 10 of 32 lanes, profiles/r01_*).
+// All state is field-major [field][N], so every global access of a warp is one contiguous 256 B run.
+// FP64 throughout, no tensor cores (nothing here is a contraction).
 #pragma once
 #include "state.cuh"
 
 namespace hrg {
 
-constexpr int kWarpsPerBlock = 8;
+constexpr int kTileEnvs = 32;
+constexpr int kMeasureWarps = 8;
 
 // HumanReach::measurement (SS/src/human_reach.cc:52-74): vel = (new - old) * (1 / dt) when a previous measurement
-// exists and dt >= 1e-7; pos = new; last_meas = t. kp_in/kp_pos/kp_vel are env-major [N][K*3] (coalesced rows).
-__global__ void k_measure(DevState S, const uint8_t* __restrict__ mask, const double* __restrict__ kp_in,
-                          const double* __restrict__ t) {
-  const int lane = threadIdx.x & 31;
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int nwarps = (gridDim.x * blockDim.x) >> 5;
-  const int K3 = S.K * 3;
-  for (int e = warp; e < S.N; e += nwarps) {
-    if (mask && !mask[e]) continue;
+// exists and dt >= 1e-7; pos = new; last_meas = t. kp_in is the caller's [N][K][3] array; one block transposes a tile
+// of 32 envs through shared memory into the field-major state.
+__global__ void __launch_bounds__(kMeasureWarps * 32)
+    k_measure(DevState S, const uint8_t* __restrict__ mask, const double* __restrict__ kp_in,
+              const double* __restrict__ t) {
+  extern __shared__ double tile[];  // [32][K3 | 1]
+  const int K3 = S.K * 3, ld = K3 | 1, N = S.N;
+  const int e0 = blockIdx.x * kTileEnvs;
+  const int ne = (N - e0) < kTileEnvs ? (N - e0) : kTileEnvs;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int e = e0 + lane;
+  const bool act = lane < ne && (!mask || mask[e]);
+  bool diff = false;
+  double inv = 0.0, now = 0.0;
+  if (act) {
     const double last = S.last_meas[e];
-    const double now = t[e];
-    __syncwarp();
-    const double* in = kp_in + (size_t)e * K3;
-    double* pos = S.kp_pos + (size_t)e * K3;
-    double* vel = S.kp_vel + (size_t)e * K3;
-    bool diff = false;
-    double inv = 0.0;
+    now = t[e];
     if (last != -1) {
-      double dt = now - last;
+      const double dt = now - last;
       if (!(dt < 1e-7)) {
         diff = true;
         inv = 1 / dt;
       }
     }
-    for (int i = lane; i < K3; i += 32) {
-      double p = in[i];
-      if (diff) vel[i] = (p - pos[i]) * inv;
-      pos[i] = p;
+  }
+  const double* src = kp_in + (size_t)e0 * K3;
+  for (int i = threadIdx.x; i < ne * K3; i += blockDim.x) {
+    const int le = i / K3;
+    tile[le * ld + (i - le * K3)] = src[i];
+  }
+  __syncthreads();
+  if (act) {
+    for (int k = w; k < K3; k += kMeasureWarps) {
+      const double p = tile[lane * ld + k];
+      const size_t o = (size_t)k * N + e;
+      if (diff) S.kp_vel[o] = (p - S.kp_pos[o]) * inv;
+      S.kp_pos[o] = p;
     }
-    if (lane == 0) S.last_meas[e] = now;
+    if (w == 0) S.last_meas[e] = now;
   }
 }
 
-struct ReachSmem {  // per-warp slice, sizes for the configured K / H
-  double* kp;   // [K*3] positions
-  double* kv;   // [K*3] velocities
-  double* Tm;   // [2][16] FK chains: 0 = start config, 1 = goal config
-  double* sc;   // [2][8][2] cos, sin per chain and joint
-  double* P;    // [2][8][2][3] transformed capsule end points per chain and link
-  double* rob;  // [8][7]
-  double* hum;  // [H][7]
-};
-__host__ __device__ inline int reach_smem_doubles(int K, int H) { return 2 * K * 3 + 32 + 32 + 96 + 56 + H * 7; }
+// Shared-memory footprint of one 32-env tile, in doubles: sin/cos [2][J][2], link end points [2][J][2][3], human
+// capsules [H][7], each x 32 lanes. The per-link partial results of the final reduction reuse the sin/cos region.
+__host__ __device__ inline int reach_smem_doubles(int J, int H) { return (4 * J + 12 * J + 7 * H) * kTileEnvs; }
 
-// Explicit-input form used by both the tick kernel and the stage entry point.
-// base [12] rows 0..2 of the base matrix, ri = {q_start[J], q_goal[J], alpha[J], s_diff, t_reach}.
-// Returns (all lanes): bit m of `coll` set iff human model m collides; md[3] per-model minimum distance; near flag.
-__device__ __forceinline__ void reach_verify_warp(const HrgConfig& c, const ReachSmem& W, int lane,
-                                                  const double* __restrict__ base, const double* __restrict__ ri,
-                                                  const double* __restrict__ kp_g, const double* __restrict__ kv_g,
-                                                  unsigned& coll, double* md, bool& near) {
-  const int J = c.nb_joints, K3 = c.n_keypoints * 3, H = c.n_ext + 2 * c.n_bodies;
-  // ---- stage inputs -------------------------------------------------------------------------------------------
-  for (int i = lane; i < K3; i += 32) {
-    W.kp[i] = kp_g[i];
-    W.kv[i] = kv_g[i];
-  }
-  const int ch = lane >> 4, r = (lane >> 2) & 3, k = lane & 3;  // FK role: chain, row, column
-  W.Tm[ch * 16 + r * 4 + k] = (r < 3) ? base[r * 4 + k] : (k == 3 ? 1.0 : 0.0);
-  if (lane < 2 * J) {
-    const int cc = lane / J, jj = lane - cc * J;
-    double sn, cs;
-    sincos(ri[cc * J + jj], &sn, &cs);
-    W.sc[(cc * 8 + jj) * 2] = cs;
-    W.sc[(cc * 8 + jj) * 2 + 1] = sn;
-  }
-  const double s_diff = ri[3 * J], t_reach = ri[3 * J + 1];
-  __syncwarp();
-  // ---- human capsules: one lane per capsule (HumanReach::humanReachabilityAnalysis, human_reach.cc:76-87) --------
-  for (int h = lane; h < H; h += 32) {
-    Cap hc = human_capsule(c, h, W.kp, W.kv, t_reach);
-    cap_store(hc, W.hum + h * 7);
-  }
-  // ---- forward kinematics of both chains, 16 lanes per chain, one matrix element per lane -----------------------
-  // RobotReach::forwardKinematic (robot_reach.h:136-142): T = T * T_fixed[i] * Rz(q_i); transformCapsule (robot_reach.cc:54-59)
-  double* Tc = W.Tm + ch * 16;
-  for (int i = 0; i < J; ++i) {
-    const double* F = c.link_T[i];
-    double t0 = Tc[r * 4 + 0] * F[0 * 4 + k] + Tc[r * 4 + 1] * F[1 * 4 + k] + Tc[r * 4 + 2] * F[2 * 4 + k] +
-                Tc[r * 4 + 3] * F[3 * 4 + k];
-    __syncwarp();
-    Tc[r * 4 + k] = t0;
-    __syncwarp();
-    const double cs = W.sc[(ch * 8 + i) * 2], sn = W.sc[(ch * 8 + i) * 2 + 1];
-    const double a = Tc[r * 4 + 0], b = Tc[r * 4 + 1];
-    double t1 = (k == 0) ? a * cs + b * sn : ((k == 1) ? b * cs - a * sn : t0);
-    __syncwarp();
-    Tc[r * 4 + k] = t1;
-    __syncwarp();
-    if (r < 3 && k < 2) {  // k = 0: end point p1 of link i, k = 1: p2 (identical op sequence => spheres stay spheres)
-      const double* lp = c.link_caps[i] + 3 * k;
-      W.P[((ch * 8 + i) * 2 + k) * 3 + r] = Tc[r * 4 + 0] * lp[0] + Tc[r * 4 + 1] * lp[1] + Tc[r * 4 + 2] * lp[2] + Tc[r * 4 + 3];
-    }
-  }
-  __syncwarp();
-  // ---- swept link capsules: one lane per link (RobotReach::reach, robot_reach.cc:61-98) -------------------------
-  if (lane < J) {
-    const double* b1 = W.P + ((0 * 8 + lane) * 2 + 0) * 3;  // before p1
-    const double* b2 = b1 + 3;                              // before p2
-    const double* a1 = W.P + ((1 * 8 + lane) * 2 + 0) * 3;  // after p1
-    const double* a2 = a1 + 3;
-    const double rl = c.link_caps[lane][6];
-    const double grow = ri[2 * J + lane] * s_diff * s_diff / 8.0;
-    V3 d1 = v3(b1[0] - a1[0], b1[1] - a1[1], b1[2] - a1[2]);
-    V3 d2 = v3(b2[0] - a2[0], b2[1] - a2[1], b2[2] - a2[2]);
-    double r_1 = vnorm(d1) / 2.0 + grow + rl;
-    double r_2 = vnorm(d2) / 2.0 + grow + rl;
-    double* o = W.rob + lane * 7;
-    o[0] = (b1[0] + a1[0]) * 0.5; o[1] = (b1[1] + a1[1]) * 0.5; o[2] = (b1[2] + a1[2]) * 0.5;
-    o[3] = (b2[0] + a2[0]) * 0.5; o[4] = (b2[1] + a2[1]) * 0.5; o[5] = (b2[2] + a2[2]) * 0.5;
-    o[6] = fmax(r_1, r_2) + c.secure_radius;
-  }
-  __syncwarp();
-  // ---- verification: J x H capsule pairs over the lanes (VerifyISO::verify_human_reach, verify_iso.cc:5-33) ------
-  unsigned my_coll = 0;
-  double m0 = INFINITY, m1 = INFINITY, m2 = INFINITY;
-  bool my_near = false;
-  const int npairs = J * H;
-  for (int p = lane; p < npairs; p += 32) {
-    const int h = p / J, rr = p - h * J;
-    Cap rc = cap_load(W.rob + rr * 7);
-    Cap hc = cap_load(W.hum + h * 7);
-    double d = capsule_capsule_dist(rc, hc);
-    const int m = human_model_of(c, h);
-    if (d < 0.0) my_coll |= 1u << m;
-    if (fabs(d) < 1e-6) my_near = true;
-    if (m == 0) m0 = fmin(m0, d);
-    else if (m == 1) m1 = fmin(m1, d);
-    else m2 = fmin(m2, d);
-  }
-  coll = 0;
-  for (int m = 0; m < 3; ++m)
-    if (__ballot_sync(0xffffffffu, (my_coll >> m) & 1u)) coll |= 1u << m;
-  near = __ballot_sync(0xffffffffu, my_near) != 0;
-  for (int o = 16; o > 0; o >>= 1) {
-    m0 = fmin(m0, __shfl_xor_sync(0xffffffffu, m0, o));
-    m1 = fmin(m1, __shfl_xor_sync(0xffffffffu, m1, o));
-    m2 = fmin(m2, __shfl_xor_sync(0xffffffffu, m2, o));
-  }
-  md[0] = m0; md[1] = m1; md[2] = m2;
-}
-
-__device__ __forceinline__ ReachSmem reach_smem_slice(double* base, int warp_in_block, int K, int H) {
-  double* p = base + (size_t)warp_in_block * reach_smem_doubles(K, H);
-  ReachSmem W;
-  W.kp = p; p += K * 3;
-  W.kv = p; p += K * 3;
-  W.Tm = p; p += 32;
-  W.sc = p; p += 32;
-  W.P = p; p += 96;
-  W.rob = p; p += 56;
-  W.hum = p;
-  return W;
-}
-
-// Tick kernel: reach + verify for every env whose plan step asked for it (F_VERIFY); writes is_safe_ into the flag
-// word, the per-model minimum distances, and (optionally) the capsules for the drop-in getters.
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_reach_verify(DevState S) {
+// pass 0: every env of the batch except those marked for the second pass; pass 1: the envs on this tick's replan list
+// (their goal motion only exists once k_replan has run). Grid = ceil(N / 32) tiles, block = J warps.
+__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32) k_reach_verify(DevState S, int pass) {
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
+  __shared__ unsigned bits_s[HRG_MAX_JOINTS][kTileEnvs];
+  const int J = S.J, H = S.H, N = S.N;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NW = blockDim.x >> 5;
+  int e = blockIdx.x * kTileEnvs + lane;
+  bool in_tile;
+  if (pass == 0) {
+    in_tile = e < N;
+    if (in_tile && S.replan_mark && S.replan_mark[e]) in_tile = false;
+  } else {
+    const int cnt = *S.replan_count;
+    if (blockIdx.x * kTileEnvs >= cnt) return;
+    in_tile = e < cnt;
+    e = in_tile ? S.replan_list[e] : 0;
+  }
   {
     const int nw = sizeof(HrgConfig) / 8;
     const double* src = reinterpret_cast<const double*>(S.cfg);
     double* dst = reinterpret_cast<double*>(&cfg_s);
     for (int i = threadIdx.x; i < nw; i += blockDim.x) dst[i] = src[i];
   }
-  __syncthreads();
   const HrgConfig& c = cfg_s;
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int warp = blockIdx.x * kWarpsPerBlock + wib, nwarps = gridDim.x * kWarpsPerBlock;
-  const ReachSmem W = reach_smem_slice(smem, wib, S.K, S.H);
-  const int J = S.J, K3 = S.K * 3, H = S.H;
-  for (int e = warp; e < S.N; e += nwarps) {
-    uint32_t f = S.flags[e];
-    if (!(f & F_VERIFY)) {
-      if (lane < 3) S.min_dist[(size_t)e * 3 + lane] = INFINITY;
-      continue;
+  const uint32_t f = in_tile ? S.flags[e] : 0u;
+  const bool act = in_tile && (f & F_VERIFY);
+  double* sc = smem;                          // [(ch * J + j) * 2 + {cos, sin}][32]
+  double* P = sc + 4 * J * kTileEnvs;         // [((ch * J + i) * 2 + k) * 3 + r][32]
+  double* hum = P + 12 * J * kTileEnvs;       // [h * 7 + k][32]
+  // ---- phase 0: sin / cos of joint w for the start and the goal configuration -------------------------------------
+  if (w < J) {
+    double sn, cs;
+    sincos(act ? ri_at(S, w, e) : 0.0, &sn, &cs);
+    sc[((0 * J + w) * 2 + 0) * kTileEnvs + lane] = cs;
+    sc[((0 * J + w) * 2 + 1) * kTileEnvs + lane] = sn;
+    sincos(act ? ri_at(S, J + w, e) : 0.0, &sn, &cs);
+    sc[((1 * J + w) * 2 + 0) * kTileEnvs + lane] = cs;
+    sc[((1 * J + w) * 2 + 1) * kTileEnvs + lane] = sn;
+  }
+  __syncthreads();
+  const double t_reach = act ? ri_at(S, 3 * J + 1, e) : 0.0;
+  // ---- phase 1: forward kinematics, one (chain, row) per thread ------------------------------------------------------
+  // RobotReach::forwardKinematic (robot_reach.h:136-142): T = T * T_fixed[i] * Rz(q_i); row r of the product only needs
+  // row r of T, so the three rows of a chain run in three warps without any exchange. transformCapsule
+  // (robot_reach.cc:54-59) of both end points of link i follows from the same row.
+  for (int it = w; it < 6; it += NW) {
+    const int ch = it / 3, r = it - ch * 3;
+    double r0 = 0.0, r1 = 0.0, r2 = 0.0, r3 = 0.0;
+    if (act) {
+      r0 = S.base_T[(size_t)(r * 4 + 0) * N + e];
+      r1 = S.base_T[(size_t)(r * 4 + 1) * N + e];
+      r2 = S.base_T[(size_t)(r * 4 + 2) * N + e];
+      r3 = S.base_T[(size_t)(r * 4 + 3) * N + e];
     }
-    unsigned coll;
-    double md[3];
-    bool near;
-    __syncwarp();
-    reach_verify_warp(c, W, lane, S.base_T + (size_t)e * 12, S.reach_in + (size_t)e * reach_stride(J),
-                      S.kp_pos + (size_t)e * K3, S.kp_vel + (size_t)e * K3, coll, md, near);
-    // safe iff ANY human model is collision-free (verify_iso.cc:22-27)
-    const bool safe = (coll != 7u);
-    if (lane == 0) {
-      f = safe ? (f | F_IS_SAFE) : (f & ~F_IS_SAFE);
-      if (near) f |= (uint32_t)HRG_ST_NEAR_THRESHOLD << F_STATUS_SHIFT;
-      S.flags[e] = f;
+    for (int i = 0; i < J; ++i) {
+      const double* F = c.link_T[i];
+      const double t0 = r0 * F[0] + r1 * F[4] + r2 * F[8] + r3 * F[12];
+      const double t1 = r0 * F[1] + r1 * F[5] + r2 * F[9] + r3 * F[13];
+      const double t2 = r0 * F[2] + r1 * F[6] + r2 * F[10] + r3 * F[14];
+      const double t3 = r0 * F[3] + r1 * F[7] + r2 * F[11] + r3 * F[15];
+      const double cs = sc[((ch * J + i) * 2 + 0) * kTileEnvs + lane], sn = sc[((ch * J + i) * 2 + 1) * kTileEnvs + lane];
+      r0 = t0 * cs + t1 * sn;
+      r1 = t1 * cs - t0 * sn;
+      r2 = t2;
+      r3 = t3;
+      const double* lp = c.link_caps[i];
+      P[(((ch * J + i) * 2 + 0) * 3 + r) * kTileEnvs + lane] = r0 * lp[0] + r1 * lp[1] + r2 * lp[2] + r3;
+      P[(((ch * J + i) * 2 + 1) * 3 + r) * kTileEnvs + lane] = r0 * lp[3] + r1 * lp[4] + r2 * lp[5] + r3;
     }
-    if (lane < 3) S.min_dist[(size_t)e * 3 + lane] = md[lane];
-    if (S.robot_caps)
-      for (int i = lane; i < J * 7; i += 32) S.robot_caps[(size_t)e * J * 7 + i] = W.rob[i];
-    if (S.human_caps)
-      for (int i = lane; i < H * 7; i += 32) S.human_caps[(size_t)e * H * 7 + i] = W.hum[i];
-    __syncwarp();
+  }
+  // ---- phase 2: human capsules, capsule index h uniform per warp (HumanReach::humanReachabilityAnalysis) ------------
+  for (int h = w; h < H; h += NW) {
+    Cap hc;
+    hc.p1 = v3(0, 0, 0); hc.p2 = v3(0, 0, 1); hc.r = 0;
+    if (act) hc = human_capsule(c, h, S.kp_pos + e, S.kp_vel + e, (size_t)N, t_reach);
+    double* o = hum + (size_t)h * 7 * kTileEnvs + lane;
+    o[0 * kTileEnvs] = hc.p1.x; o[1 * kTileEnvs] = hc.p1.y; o[2 * kTileEnvs] = hc.p1.z;
+    o[3 * kTileEnvs] = hc.p2.x; o[4 * kTileEnvs] = hc.p2.y; o[5 * kTileEnvs] = hc.p2.z;
+    o[6 * kTileEnvs] = hc.r;
+    if (act && S.human_caps) cap_store(hc, S.human_caps + ((size_t)e * H + h) * 7);
+  }
+  __syncthreads();
+  // ---- phase 3: swept capsule of link w (RobotReach::reach, robot_reach.cc:61-98) -----------------------------------
+  unsigned my_bits = 0;
+  double m0 = INFINITY, m1 = INFINITY, m2 = INFINITY;
+  if (w < J) {
+    const double* b = P + ((0 * J + w) * 2) * 3 * kTileEnvs + lane;  // before: p1 xyz, p2 xyz
+    const double* a = P + ((1 * J + w) * 2) * 3 * kTileEnvs + lane;  // after
+    double bp[6], ap[6];
+    for (int k = 0; k < 6; ++k) {
+      bp[k] = b[k * kTileEnvs];
+      ap[k] = a[k * kTileEnvs];
+    }
+    const double s_diff = act ? ri_at(S, 3 * J, e) : 0.0;
+    const double alpha = act ? ri_at(S, 2 * J + w, e) : 0.0;
+    const double rl = c.link_caps[w][6];
+    const double grow = alpha * s_diff * s_diff / 8.0;
+    const double r_1 = vnorm(v3(bp[0] - ap[0], bp[1] - ap[1], bp[2] - ap[2])) / 2.0 + grow + rl;
+    const double r_2 = vnorm(v3(bp[3] - ap[3], bp[4] - ap[4], bp[5] - ap[5])) / 2.0 + grow + rl;
+    Cap rc;
+    rc.p1 = v3((bp[0] + ap[0]) * 0.5, (bp[1] + ap[1]) * 0.5, (bp[2] + ap[2]) * 0.5);
+    rc.p2 = v3((bp[3] + ap[3]) * 0.5, (bp[4] + ap[4]) * 0.5, (bp[5] + ap[5]) * 0.5);
+    rc.r = fmax(r_1, r_2) + c.secure_radius;
+    if (act && S.robot_caps) cap_store(rc, S.robot_caps + ((size_t)e * J + w) * 7);
+    // ---- phase 4: link w against every human capsule (VerifyISO::verify_human_reach, verify_iso.cc:5-33) -----------
+    const int E = c.n_ext, B = c.n_bodies;
+    for (int h = 0; h < H; ++h) {
+      const double* hp = hum + (size_t)h * 7 * kTileEnvs + lane;
+      Cap hc;
+      hc.p1 = v3(hp[0 * kTileEnvs], hp[1 * kTileEnvs], hp[2 * kTileEnvs]);
+      hc.p2 = v3(hp[3 * kTileEnvs], hp[4 * kTileEnvs], hp[5 * kTileEnvs]);
+      hc.r = hp[6 * kTileEnvs];
+      const double d = capsule_capsule_dist(rc, hc);
+      const int m = h < E ? 0 : (h - E < B ? 1 : 2);  // warp-uniform
+      if (d < 0.0) my_bits |= 1u << m;
+      if (fabs(d) < 1e-6) my_bits |= 8u;
+      if (m == 0) m0 = fmin(m0, d);
+      else if (m == 1) m1 = fmin(m1, d);
+      else m2 = fmin(m2, d);
+    }
+  }
+  __syncthreads();  // sc / P are dead from here on: reuse sc for the per-link partial minima
+  if (w < J) {
+    sc[(w * 3 + 0) * kTileEnvs + lane] = m0;
+    sc[(w * 3 + 1) * kTileEnvs + lane] = m1;
+    sc[(w * 3 + 2) * kTileEnvs + lane] = m2;
+    bits_s[w][lane] = my_bits;
+  }
+  __syncthreads();
+  // ---- phase 5: combine the links; safe iff ANY human model is collision-free (verify_iso.cc:22-27) -----------------
+  if (w == 0 && in_tile) {
+    if (!act) {
+      for (int m = 0; m < 3; ++m) S.min_dist[(size_t)m * N + e] = INFINITY;
+    } else {
+      unsigned bits = 0;
+      double md[3] = {INFINITY, INFINITY, INFINITY};
+      for (int l = 0; l < J; ++l) {
+        bits |= bits_s[l][lane];
+        for (int m = 0; m < 3; ++m) md[m] = fmin(md[m], sc[(l * 3 + m) * kTileEnvs + lane]);
+      }
+      uint32_t g = ((bits & 7u) != 7u) ? (f | F_IS_SAFE) : (f & ~F_IS_SAFE);
+      if (bits & 8u) g |= (uint32_t)HRG_ST_NEAR_THRESHOLD << F_STATUS_SHIFT;
+      S.flags[e] = g;
+      for (int m = 0; m < 3; ++m) S.min_dist[(size_t)m * N + e] = md[m];
+    }
   }
 }
 
-// Stage entry point on explicit inputs (parity tests, ncu).
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
-    k_stage_reach_verify(const HrgConfig* __restrict__ cfg, int n, const double* base_pose, const double* q_start,
-                         const double* q_goal, const double* s_diff, const double* t_reach, const double* alpha,
-                         const double* kp_pos, const double* kp_vel, double* robot, double* human, double* min_dist,
-                         uint8_t* is_safe) {
-  extern __shared__ double smem[];
-  __shared__ HrgConfig cfg_s;
-  __shared__ double in_s[kWarpsPerBlock][12 + 3 * HRG_MAX_JOINTS + 2];
-  {
-    const int nw = sizeof(HrgConfig) / 8;
-    const double* src = reinterpret_cast<const double*>(cfg);
-    double* dst = reinterpret_cast<double*>(&cfg_s);
-    for (int i = threadIdx.x; i < nw; i += blockDim.x) dst[i] = src[i];
+// ---- stage entry point (parity tests, ncu): explicit env-major inputs are packed into a scratch field-major state, the
+// tick kernel runs on it unchanged, and the results are unpacked again.
+__global__ void k_stage_pack(DevState S, const double* __restrict__ base_pose, const double* __restrict__ q_start,
+                             const double* __restrict__ q_goal, const double* __restrict__ s_diff,
+                             const double* __restrict__ t_reach, const double* __restrict__ alpha,
+                             const double* __restrict__ kp_pos, const double* __restrict__ kp_vel) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= S.N) return;
+  const int J = S.J, K3 = S.K * 3, N = S.N;
+  double B[12];
+  const double* p = base_pose + (size_t)e * 6;
+  base_pose_matrix(p[0], p[1], p[2], p[3], p[4], p[5], B);
+  for (int k = 0; k < 12; ++k) S.base_T[(size_t)k * N + e] = B[k];
+  for (int j = 0; j < J; ++j) {
+    ri_at(S, j, e) = q_start[(size_t)e * J + j];
+    ri_at(S, J + j, e) = q_goal[(size_t)e * J + j];
+    ri_at(S, 2 * J + j, e) = alpha[(size_t)e * J + j];
   }
-  __syncthreads();
-  const HrgConfig& c = cfg_s;
-  const int J = c.nb_joints, K = c.n_keypoints, H = c.n_ext + 2 * c.n_bodies;
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int warp = blockIdx.x * kWarpsPerBlock + wib, nwarps = gridDim.x * kWarpsPerBlock;
-  const ReachSmem W = reach_smem_slice(smem, wib, K, H);
-  for (int e = warp; e < n; e += nwarps) {
-    double* in = in_s[wib];
-    __syncwarp();
-    if (lane == 0) {
-      const double* p = base_pose + (size_t)e * 6;
-      base_pose_matrix(p[0], p[1], p[2], p[3], p[4], p[5], in);
-    }
-    if (lane < J) {
-      in[12 + lane] = q_start[(size_t)e * J + lane];
-      in[12 + J + lane] = q_goal[(size_t)e * J + lane];
-      in[12 + 2 * J + lane] = alpha[(size_t)e * J + lane];
-    }
-    if (lane == 0) {
-      in[12 + 3 * J] = s_diff[e];
-      in[12 + 3 * J + 1] = t_reach[e];
-    }
-    __syncwarp();
-    unsigned coll;
-    double md[3];
-    bool near;
-    reach_verify_warp(c, W, lane, in, in + 12, kp_pos + (size_t)e * K * 3, kp_vel + (size_t)e * K * 3, coll, md, near);
-    if (lane == 0 && is_safe) is_safe[e] = (coll != 7u) ? 1 : 0;
-    if (lane < 3 && min_dist) min_dist[(size_t)e * 3 + lane] = md[lane];
-    if (robot)
-      for (int i = lane; i < J * 7; i += 32) robot[(size_t)e * J * 7 + i] = W.rob[i];
-    if (human)
-      for (int i = lane; i < H * 7; i += 32) human[(size_t)e * H * 7 + i] = W.hum[i];
-    __syncwarp();
+  ri_at(S, 3 * J, e) = s_diff[e];
+  ri_at(S, 3 * J + 1, e) = t_reach[e];
+  for (int k = 0; k < K3; ++k) {
+    S.kp_pos[(size_t)k * N + e] = kp_pos[(size_t)e * K3 + k];
+    S.kp_vel[(size_t)k * N + e] = kp_vel[(size_t)e * K3 + k];
   }
+  S.flags[e] = F_VERIFY;
+}
+
+__global__ void k_stage_unpack(DevState S, double* __restrict__ min_dist, uint8_t* __restrict__ is_safe) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= S.N) return;
+  if (min_dist)
+    for (int m = 0; m < 3; ++m) min_dist[(size_t)e * 3 + m] = S.min_dist[(size_t)m * S.N + e];
+  if (is_safe) is_safe[e] = (S.flags[e] & F_IS_SAFE) ? 1 : 0;
+}
+
+// [3][N] -> caller's [N][3]
+__global__ void k_min_dist_out(DevState S, double* __restrict__ out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= S.N) return;
+  for (int m = 0; m < 3; ++m) out[(size_t)e * 3 + m] = S.min_dist[(size_t)m * S.N + e];
 }
 
 }  // namespace hrg

@@ -1,5 +1,5 @@
 // Thread-per-env kernels of one shield tick (scalar path logic; coalesced field-major state) and the replan kernel
-// (one lane per (env, joint), 8-lane groups).
+// (one warp per replanning env).
 #pragma once
 #include "ltp_math.cuh"
 #include "step_logic.cuh"
@@ -21,54 +21,74 @@ __global__ void __launch_bounds__(kTickBlock) k_pre_plan(DevState S, const doubl
   if (e >= S.N) return;
   const HrgConfig& c = *S.cfg;
   uint32_t f = S.flags[e];
-  if (pre_env(S, c, e, f)) {
+  const bool replan = pre_env(S, c, e, f);
+  if (replan) {
     const int slot = atomicAdd(S.replan_count, 1);
     S.replan_list[slot] = e;
   } else {
     plan_env(S, c, e, t[e], f);
   }
+  S.replan_mark[e] = replan ? 1 : 0;
   S.flags[e] = f;
 }
 
+constexpr int kReplanBlock = 64;  // two warps = two envs per block
+
 // calculateLongTermTrajectory (SS/src/safety_shield.cc:732-760) -> LongTermPlanner::planTrajectory
-// (LTP/src/long_term_planner.cc:7-63) for the envs on the replan list: lane j of an 8-lane group plans joint j
-// (lanes >= J shadow joint J-1 and never write); group-wide decisions go through width-8 shuffles / ballots.
-// Lane 0 then finishes the env's step up to the reach/verify hand-over.
-__global__ void __launch_bounds__(128) k_replan(DevState S, const double* __restrict__ t) {
+// (LTP/src/long_term_planner.cc:7-63) for the envs on the replan list. ONE WARP PER ENV, work fetched from a device
+// counter (plans differ a lot in cost): lane = joint + 8 * sub. The (branchy, FP64) switch-time planning runs on the
+// sub == 0 lanes; while sampling, each sub-lane evaluates the jerk of one of four consecutive samples and stores one of
+// the four components, the integration itself stays the reference's sequential recurrence (bit-identical sums).
+// Lanes with joint >= J shadow joint J-1 and never write. Lane 0 then finishes the env's step up to the reach/verify
+// hand-over. The first version packed four envs into a warp and was latency bound (profiles/r01_ncu_summary.md).
+__global__ void __launch_bounds__(kReplanBlock, 8) k_replan(DevState S, const double* __restrict__ t) {
   const HrgConfig& c = *S.cfg;
+  const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  const int gl = lane & 7;                       // lane in group
-  const unsigned gmask = 0xFFu << (lane & 24);   // the 8 lanes of this group
-  const int group = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-  const int ngroups = (gridDim.x * blockDim.x) >> 3;
+  const int gl = lane & 7, sub = lane >> 3;
   const int count = *S.replan_count;
   const int J = S.J, N = S.N;
   const int j = gl < J ? gl : J - 1;
-  const bool writer = gl < J;
+  const bool joint_lane = gl < J;
+  // dynamically indexed scratch goes to shared memory, not to local memory: with 16 resident warps per SM the per-thread
+  // stack of the first version (companion matrix + jerk sampler, 624 B x 32 lanes x 16 warps) overflowed the L1
+  __shared__ double mat_s[kReplanBlock / 32][36][8];
+  __shared__ JerkSampler samp_s[kReplanBlock / 32][8];
+  const int wib = threadIdx.x >> 5;
   LtpLimits L;
   L.v_max = c.v_max[j]; L.a_max = c.a_max_ltt[j]; L.j_max = c.j_max_ltt[j]; L.t_sample = c.sample_time;
-  for (int idx = group; idx < count; idx += ngroups) {
+  L.mat = &mat_s[wib][0][gl];
+  L.mat_stride = 8;
+  for (;;) {
+    int idx = 0;
+    if (lane == 0) idx = atomicAdd(S.replan_next, 1);
+    idx = __shfl_sync(full, idx, 0);
+    if (idx >= count) break;
     const int e = S.replan_list[idx];
     uint32_t f = S.flags[e];
     const int pend = (f & F_LIVE_SLOT) ? 0 : 1;
-    const double* cur = S.cur + (size_t)e * cur_stride(J);
-    const double q_0 = cur[j], v_0 = cur[J + j], a_0 = cur[2 * J + j];
+    const double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
     const double q_goal = S.goal_q[(size_t)j * N + e];
     uint32_t status = HRG_ST_REPLANNED;
     int len = 0;
-    bool ok = ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0);
-    ok = (__ballot_sync(gmask, ok) & gmask) == gmask;
+    // switch-time planning on the sub == 0 lanes only (it keeps a 6x6 companion matrix in local memory: replicating it
+    // over the sub-lanes would quadruple the L1 footprint); the other lanes vote "ok" and receive the plan afterwards.
+    const bool planner = sub == 0;
+    bool ok = planner ? ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0) : true;
+    ok = __all_sync(full, ok);
     JointPlan opt, sc;
+    ltp_zero7(opt.T);
+    opt.dir = 0.0; opt.v_drive = L.v_max; opt.mod = 0;
+    sc = opt;
     if (ok) {
-      ltp_zero7(opt.T);
-      ok = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, opt.T, opt.dir, opt.mod);
-      ok = (__ballot_sync(gmask, ok) & gmask) == gmask;
+      if (planner) ok = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, opt.T, opt.dir, opt.mod);
+      ok = __all_sync(full, ok);
     }
     if (ok) {
       double t_required = -1;
       int slowest = -1;
       for (int k = 0; k < J; ++k) {
-        double tk = __shfl_sync(gmask, opt.T[6], k, 8);
+        double tk = __shfl_sync(full, opt.T[6], k);
         if (tk > t_required) {
           t_required = tk;
           slowest = k;
@@ -76,18 +96,25 @@ __global__ void __launch_bounds__(128) k_replan(DevState S, const double* __rest
       }
       ok = slowest != -1;
       if (ok) {
-        sc = opt;
-        sc.v_drive = L.v_max;
-        ltp_zero7(sc.T);
-        if (j != slowest)
-          ltp_time_scaling(L, q_goal, q_0, v_0, a_0, opt.dir, t_required, sc.T, sc.v_drive, sc.mod);
-        double mx = sc.T[0];
-        for (int k = 1; k < 7; ++k) mx = (mx < sc.T[k]) ? sc.T[k] : mx;
-        if (mx <= 0.0)
-          for (int k = 0; k < 7; ++k) sc.T[k] = opt.T[k];
+        if (planner) {
+          sc = opt;
+          sc.v_drive = L.v_max;
+          ltp_zero7(sc.T);
+          if (j != slowest)
+            ltp_time_scaling(L, q_goal, q_0, v_0, a_0, opt.dir, t_required, sc.T, sc.v_drive, sc.mod);
+          double mx = sc.T[0];
+          for (int k = 1; k < 7; ++k) mx = (mx < sc.T[k]) ? sc.T[k] : mx;
+          if (mx <= 0.0)
+            for (int k = 0; k < 7; ++k) sc.T[k] = opt.T[k];
+        }
+        // hand the joint's plan to its sub-lanes
+        for (int k = 0; k < 7; ++k) sc.T[k] = __shfl_sync(full, sc.T[k], gl);
+        sc.dir = __shfl_sync(full, sc.dir, gl);
+        sc.v_drive = __shfl_sync(full, sc.v_drive, gl);
+        sc.mod = __shfl_sync(full, sc.mod, gl);
         len = ltp_joint_len(L, sc);
         for (int o = 4; o > 0; o >>= 1) {
-          int other = __shfl_xor_sync(gmask, len, o, 8);
+          int other = __shfl_xor_sync(full, len, o);
           len = other > len ? other : len;
         }
         if (len > S.L) {
@@ -99,18 +126,18 @@ __global__ void __launch_bounds__(128) k_replan(DevState S, const double* __rest
       }
     }
     if (ok) {
-      double qf = c.q_min[j];
-      if (writer) qf = ltp_sample_joint(L, sc, q_0, v_0, a_0, len, ltt_sample_w(S, e, pend, 0) + j, J, (size_t)4 * J);
-      bool in = !(qf < c.q_min[j] || qf > c.q_max[j]);
-      ok = (__ballot_sync(gmask, in) & gmask) == gmask;
+      const double qf = ltp_sample_joint_warp(L, sc, q_0, v_0, a_0, len, ltt_sample_w(S, e, pend, 0), J, gl, sub, joint_lane,
+                                              samp_s[wib][gl]);
+      const bool in = !(qf < c.q_min[j] || qf > c.q_max[j]);
+      ok = __all_sync(full, in);
     }
-    if (ok && writer) {
+    if (ok && joint_lane && sub == 0) {
       S.replan_q[(size_t)j * N + e] = q_0;  // last_replan_start_motion_ = current_motion (:593)
       // SSM/OFF: alpha_i_ = alpha_i_max (long_term_traj.h:108-116)
       S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
     }
-    __syncwarp(gmask);
-    if (gl == 0) {
+    __syncwarp(full);
+    if (lane == 0) {
       if (ok) {
         S.ltt_len[(size_t)pend * N + e] = len;
         S.ltt_cur[(size_t)pend * N + e] = 0;
@@ -128,7 +155,7 @@ __global__ void __launch_bounds__(128) k_replan(DevState S, const double* __rest
       plan_env(S, c, e, t[e], f);
       S.flags[e] = f;
     }
-    __syncwarp(gmask);
+    __syncwarp(full);
   }
 }
 
@@ -142,7 +169,10 @@ __global__ void __launch_bounds__(kTickBlock)
   if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0ull;
   if (threadIdx.x == 0) s_min = INFINITY;
   __syncthreads();
-  if (e == 0) *S.replan_count = 0;
+  if (e == 0) {
+    *S.replan_count = 0;
+    *S.replan_next = 0;
+  }
   unsigned long long my[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum
   double my_min = INFINITY;
   if (e < S.N) {
@@ -165,8 +195,7 @@ __global__ void __launch_bounds__(kTickBlock)
       if ((st & HRG_ST_REPLANNED) && !(st & HRG_ST_REPLAN_FAILED))
         my[7] = (unsigned long long)S.ltt_len[(size_t)((f & F_LIVE_SLOT) ? 0 : 1) * S.N + e];
       if (f & F_VERIFY) {
-        const double* md = S.min_dist + (size_t)e * 3;
-        my_min = fmin(md[0], fmin(md[1], md[2]));
+        my_min = fmin(S.min_dist[e], fmin(S.min_dist[(size_t)S.N + e], S.min_dist[(size_t)2 * S.N + e]));
       }
     }
   }
@@ -224,7 +253,9 @@ __global__ void k_reset(DevState S, const uint8_t* __restrict__ mask, const doub
   f |= (type << F_TYPE_SHIFT) & F_TYPE_MASK;
   if (type == HRG_SHIELD_OFF) f |= F_IS_SAFE;
   const double* p = base_pose + (size_t)e * 6;
-  base_pose_matrix(p[0], p[1], p[2], p[3], p[4], p[5], S.base_T + (size_t)e * 12);
+  double B[12];
+  base_pose_matrix(p[0], p[1], p[2], p[3], p[4], p[5], B);
+  for (int k = 0; k < 12; ++k) S.base_T[(size_t)k * N + e] = B[k];
   S.last_meas[e] = -1;
   PathS z;
   path_clear(z);
@@ -252,7 +283,7 @@ __global__ void k_reset(DevState S, const uint8_t* __restrict__ mask, const doub
   potential_env(S, c, e, f, gq, s_d, t_brake, gslot);
   select_env(S, c, e, f, nullptr, nullptr, nullptr, nullptr);
   S.flags[e] = f;
-  for (int k = 0; k < 3; ++k) S.min_dist[(size_t)e * 3 + k] = INFINITY;
+  for (int k = 0; k < 3; ++k) S.min_dist[(size_t)k * N + e] = INFINITY;
 }
 
 // ---- stage entry points ----------------------------------------------------------------------------------------

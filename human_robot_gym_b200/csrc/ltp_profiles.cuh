@@ -48,7 +48,7 @@ HRG_HD void ltp_cumsum7(const double* t, double* T) {
 }
 
 // optSwitchTimes (LTP/src/long_term_planner.cc:82-353). Returns the reference's bool; T = cumulative switch times.
-HRG_HD bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double v_drive,
+HRG_HD_CALL bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double v_drive,
                                  double* T, double& dir, int& mod_jerk_profile) {
   const double jm = L.j_max, am = L.a_max;
   double t[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
@@ -147,7 +147,7 @@ HRG_HD bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double q_0, 
         A[2] = -24 * sq(a_0) + 48 * jm * v_0;
         A[3] = 48 * dir * sq(jm) * q_0 - 48 * dir * sq(jm) * q_goal + 16 * cube(a_0) - 48 * a_0 * jm * v_0;
         A[4] = -3 * pow4(a_0) + 12.0 * sq(a_0) * jm * v_0 - 12.0 * sq(jm) * sq(v_0);
-        root = smallest_positive_real_root(A, 5);
+        root = smallest_positive_real_root(L, A, 5);
       }
       t[0] = (2.0 * sq(root) - 4 * a_0 * root + sq(a_0) - 2.0 * v_0 * jm) / (4 * jm * root);
       t[6] = sqrt(4 * sq(jm) * sq(t[0]) + 8 * a_0 * jm * t[0] + 2.0 * sq(a_0) + 4 * jm * v_0) / (2.0 * jm);
@@ -182,7 +182,7 @@ HRG_HD bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double q_0, 
         A[4] = 24 * dir * sq(jm) * q_0 * am - 24 * dir * sq(jm) * q_goal * am + 3 * pow4(a_0) + 8 * cube(a_0) * am +
                6 * sq(a_0) * sq(am) - 12.0 * sq(a_0) * jm * v_0 - 24 * a_0 * jm * v_0 * am - 12.0 * sq(am) * jm * v_0 +
                12.0 * sq(jm) * sq(v_0);
-        root = smallest_positive_real_root(A, 5);
+        root = smallest_positive_real_root(L, A, 5);
         t[0] = (root - a_0 - am) / jm;
         t[4] = (a_0 + am) / jm + t[0];
         t[5] = (sq(jm) * sq(t[0]) + 2.0 * sq(jm) * t[0] * t[4] - sq(jm) * sq(t[4]) + 2.0 * a_0 * jm * t[0] +

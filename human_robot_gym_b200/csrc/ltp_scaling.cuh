@@ -5,7 +5,7 @@
 namespace hrg {
 
 // One candidate: accept if optSwitchTimes succeeds and -0.01 < t_required - T[6] < 0.1 (:398-405 and repeats).
-HRG_HD bool ltp_try_vdrive(const LtpLimits& L, double q_goal, double q_0, double v_orig, double a_orig, double v_drive,
+HRG_HD_CALL bool ltp_try_vdrive(const LtpLimits& L, double q_goal, double q_0, double v_orig, double a_orig, double v_drive,
                            double t_required, double* T, int& mod_jerk_profile) {
   const double tol = 0.1;
   if (!isnan(v_drive) && v_drive > 0) {
@@ -16,7 +16,7 @@ HRG_HD bool ltp_try_vdrive(const LtpLimits& L, double q_goal, double q_0, double
   return false;
 }
 
-HRG_HD bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double dir,
+HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double dir,
                              double tr /*t_required*/, double* T /*scaled_t*/, double& v_drive, int& mod_jerk_profile) {
   const double jm = L.j_max, am = L.a_max;
   if (dir < 0) {
@@ -66,7 +66,7 @@ HRG_HD bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, doub
   A[4] = 48 * sq(a_0) * am * jm * tr - 96 * dir * sq(jm) * am * q_0 + 96 * dir * sq(jm) * am * q_goal -
          96 * am * sq(jm) * v_0 * tr + 12.0 * pow4(a_0) + 16 * cube(a_0) * am - 24 * sq(a_0) * sq(am) -
          48 * sq(a_0) * jm * v_0 + 48 * sq(am) * jm * v_0 + 48 * sq(jm) * sq(v_0);
-  root = smallest_positive_real_root(A, 5);
+  root = smallest_positive_real_root(L, A, 5);
   v_drive = (-2.0 * sq(a_0) + 4 * jm * v_0 + sq(root)) / (4 * jm);
   if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
 
@@ -79,7 +79,7 @@ HRG_HD bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, doub
          24 * sq(a_0) * jm * v_0 + 48 * a_0 * am * jm * v_0 + 4 * pow4(am) - 24 * sq(am) * jm * v_0 +
          12.0 * sq(jm) * sq(v_0) + 6 * cube(a_0) + 6 * sq(a_0) * am - 12.0 * a_0 * sq(am) - 12.0 * a_0 * jm * v_0 +
          12.0 * am * jm * v_0 + 4 * a_0 * am - 4 * sq(am);
-  root = smallest_positive_real_root(A, 5);
+  root = smallest_positive_real_root(L, A, 5);
   v_drive = sq(root) / jm;
   if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
 
@@ -96,7 +96,7 @@ HRG_HD bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, doub
          48 * cube(a_0) * dir * sq(jm) * q_goal + 144 * a_0 * dir * cube(jm) * q_0 * v_0 -
          144 * a_0 * dir * cube(jm) * q_goal * v_0 + pow6(a_0) - 6 * pow4(a_0) * jm * v_0 +
          36 * sq(a_0) * sq(jm) * sq(v_0) - 72.0 * cube(jm) * cube(v_0);
-  root = smallest_positive_real_root(A, 6);
+  root = smallest_positive_real_root(L, A, 6);
   v_drive = sq(root) / jm;
   if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
 
@@ -108,7 +108,7 @@ HRG_HD bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, doub
   A[4] = -12.0 * sq(a_0) * am * jm * tr - 24 * dir * sq(jm) * am * q_0 + 24 * dir * sq(jm) * am * q_goal -
          24 * am * sq(jm) * v_0 * tr + 3 * pow4(a_0) + 4 * cube(a_0) * am + 6 * sq(a_0) * sq(am) +
          12.0 * sq(a_0) * jm * v_0 + 12.0 * sq(am) * jm * v_0 + 12.0 * sq(jm) * sq(v_0);
-  root = smallest_positive_real_root(A, 5);
+  root = smallest_positive_real_root(L, A, 5);
   v_drive = -(sq(root) - sq(a_0) - 2.0 * jm * v_0) / (2.0 * jm);
   if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
 
@@ -120,7 +120,7 @@ HRG_HD bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, doub
   A[4] = 24 * dir * sq(jm) * am * q_0 - 24 * dir * sq(jm) * am * q_goal + 3 * pow4(a_0) + 8 * cube(a_0) * am +
          6 * sq(a_0) * sq(am) + 12.0 * sq(a_0) * jm * v_0 + 24 * a_0 * am * jm * v_0 + 12.0 * sq(am) * jm * v_0 +
          12.0 * sq(jm) * sq(v_0);
-  root = smallest_positive_real_root(A, 5);
+  root = smallest_positive_real_root(L, A, 5);
   v_drive = sq(root) / jm;
   if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
 
@@ -138,7 +138,7 @@ HRG_HD bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, doub
          48 * cube(a_0) * dir * sq(jm) * q_goal + 144 * a_0 * dir * cube(jm) * q_0 * v_0 -
          144 * a_0 * dir * cube(jm) * q_goal * v_0 - pow6(a_0) - 6 * pow4(a_0) * jm * v_0 -
          36 * sq(a_0) * sq(jm) * sq(v_0) - 72.0 * cube(jm) * cube(v_0);
-  root = smallest_positive_real_root(A, 7);
+  root = smallest_positive_real_root(L, A, 7);
   v_drive = sq(root) / jm;
   if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
 

@@ -116,6 +116,51 @@ HRG_HD double ltp_sample_joint(const LtpLimits& L, const JointPlan& P, double q_
   return q;
 }
 
+#if defined(__CUDACC__)
+// Warp-cooperative form of ltp_sample_joint for the replan kernel: lane = joint gl + 8 * sub, every lane holds the plan of
+// its joint. Per group of four samples each sub-lane evaluates the jerk of sample 4c + sub (the expensive part: a
+// 7-way range test plus up to 10 corrections), the four values are exchanged by shuffle, and all sub-lanes run the
+// reference's sequential recurrence a += ts*j, v += ts*a, q += ts*v redundantly (identical roundings); sub-lane s then
+// stores component s of {q, v, a, j}, so one store instruction writes the whole [4][J] sample contiguously. The jerk
+// sampler of a joint (34 words, dynamically indexed) sits in shared memory, one copy per joint.
+// `len` must be warp-uniform. Returns the final position (joint-limit test of :59-61).
+__device__ __forceinline__ double ltp_sample_joint_warp(const LtpLimits& L, const JointPlan& P, double q_0, double v_0,
+                                                        double a_0, int len, double* traj /*[len][4][J]*/, int J, int gl,
+                                                        int sub, bool joint_lane, JerkSampler& S /*shared, per joint*/) {
+  if (sub == 0) ltp_sampler_init(L, P, S);
+  __syncwarp();
+  const double ts = L.t_sample;
+  const double v_cruise = P.v_drive * P.dir;
+  // loop invariants in registers (S is shared memory and the sample stores could alias it for the compiler)
+  const int s6 = S.s[6];
+  const int cr_lo = S.phase4 ? S.s[2] + 1 : 0x7fffffff, cr_hi = S.s[3] - 1;
+  double* out = traj + sub * J + gl;
+  const size_t stride = (size_t)4 * J;
+  double a = a_0, v = v_0, q = q_0;
+  for (int c0 = 0; c0 < len; c0 += 4) {
+    const double mine = ltp_jerk_at(S, c0 + sub);
+    double jq[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) jq[u] = __shfl_sync(0xffffffffu, mine, gl + 8 * u);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = c0 + u;
+      if (i < len) {
+        const double jj = jq[u];
+        const bool first = i == 0, live = first || i <= s6;
+        const double an = a + ts * jj;
+        a = live ? an : 0.0;
+        const double vn = v + ts * a;
+        v = (!first && i >= cr_lo && i < cr_hi) ? v_cruise : (live ? vn : 0.0);
+        q = q + ts * v;
+        if (joint_lane) out[(size_t)i * stride] = sub == 0 ? q : (sub == 1 ? v : (sub == 2 ? a : jj));
+      }
+    }
+  }
+  return q;
+}
+#endif
+
 // Sequential planTrajectory for one env (:7-63) — used where one thread owns a whole env (host tests, stage entry);
 // the replan kernel runs the same per-joint calls with one lane per joint. traj layout [len][4][J].
 // Returns the trajectory length, 0 on failure, -len if len > cap (nothing is written then).

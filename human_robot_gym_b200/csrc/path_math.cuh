@@ -9,8 +9,13 @@
 
 #if defined(__CUDACC__)
 #define HRG_HD __host__ __device__ __forceinline__
+// Large, branchy routines that are called from several places are real calls on the device: force-inlining them blew
+// k_replan up to 82k SASS instructions (1.3 MB) and 36 % of its stall samples were instruction-cache misses
+// (profiles/r01_ncu_summary.md).
+#define HRG_HD_CALL __host__ __device__ __noinline__
 #else
 #define HRG_HD inline
+#define HRG_HD_CALL inline
 #endif
 
 namespace hrg {
@@ -86,7 +91,7 @@ HRG_HD double round_to_timestep(double t, double ts) { return ceil(t / ts) * ts;
 // SafetyShield::planSafetyShield (SS/src/safety_shield.cc:203-341). Mirrors the partial side effects: once past the
 // first guard, pos/vel/acc of `path` are overwritten (and is_current cleared, by the caller via the return of
 // `touched`) even if planning later fails; the phases only change on success.
-HRG_HD bool plan_safety_shield(double pos, double vel, double acc, double ve, double a_max, double j_max, double ts,
+HRG_HD_CALL bool plan_safety_shield(double pos, double vel, double acc, double ve, double a_max, double j_max, double ts,
                                PathS& path, bool& touched) {
   touched = false;
   if (a_max < 0 || fabs(acc) > a_max) return false;

@@ -1,10 +1,9 @@
 // Device-resident state of a batch of N shields: structure-of-arrays FP64 in HBM.
 //
-// Two access patterns shape the layout:
-//   * thread-per-env kernels (path planning in s, selection) touch the scalar state: stored field-major [field][N] so
-//     that consecutive threads read consecutive doubles (fully coalesced 8 B x 32 = 256 B per request);
-//   * warp-per-env kernels (measurement, reach + verify) and the per-env gathers (one LTT sample) touch small contiguous
-//     records: stored env-major [N][record] so a warp reads one 128 B-aligned record with consecutive lanes.
+// Every kernel of the tick maps consecutive LANES to consecutive ENVS (thread-per-env path logic; lane-per-env tiles of
+// 32 envs in reach + verify), so all per-env state is stored field-major [field][N]: a warp reads or writes 32
+// consecutive doubles = one fully used 256 B request per field. The only env-major records are the long-term
+// trajectories (one sample = 4J contiguous doubles gathered per env per interpolation).
 // The reference holds the same data as one heap-allocated SafetyShield object per env
 // (SS/include/safety_shield/safety_shield.h:70-293).
 #pragma once
@@ -51,27 +50,31 @@ struct DevState {
   double* ltt_t0;     // [2][N]  time of sample 0 (= path_s_ at planning; PFL scan)
   double* ltt_ts;     // [2][N]  sample_time_ of the LTT (differs from the shield's only for user-supplied LTTs)
   double* ltt_alpha;  // [2][J][N] alpha_i_ of the LTT
-  // ---- env-major [N][..]
-  double* base_T;     // [N][12] rows 0..2 of the base pose matrix
-  double* kp_pos;     // [N][K*3]
-  double* kp_vel;     // [N][K*3]
+  double* base_T;     // [12][N] rows 0..2 of the base pose matrix
+  double* kp_pos;     // [K*3][N]
+  double* kp_vel;     // [K*3][N]
   double* last_meas;  // [N]
+  // ---- env-major [N][..]
   double* ltt;        // [N][2][L][4][J]  q, dq, ddq, dddq per sample
   double* ltt_cart;   // [N][2][L] max Cartesian velocity per sample (PFL; NULL otherwise)
-  // ---- per-step hand-over between the kernels of one tick, env-major
-  double* cur;        // [N][4J+1]: q, dq, ddq, dddq of getCurrentMotion(), then its s
-  double* reach_in;   // [N][3J+2]: q_start[J], q_goal[J], alpha_i[J], s_diff, t_reach
-  double* min_dist;   // [N][3]
+  // ---- per-step hand-over between the kernels of one tick, field-major
+  double* cur;        // [4J+1][N]: q, dq, ddq, dddq of getCurrentMotion(), then its s
+  double* reach_in;   // [3J+2][N]: q_start[J], q_goal[J], alpha_i[J], s_diff, t_reach
+  double* min_dist;   // [3][N]
   int32_t* replan_list;   // [N]
   int32_t* replan_count;  // [1]
+  int32_t* replan_next;   // [1] work counter of k_replan (one env per fetch)
+  uint8_t* replan_mark;   // [N] 1 = this tick's reach + verify of the env runs after k_replan (second pass)
   // optional per-step capsule dump (drop-in getters); NULL = not stored
   double* robot_caps;  // [N][J][7]
   double* human_caps;  // [N][H][7]
   HrgStats* stats;
 };
 
-HRG_HD int cur_stride(int J) { return 4 * J + 1; }
-HRG_HD int reach_stride(int J) { return 3 * J + 2; }
+HRG_HD int cur_fields(int J) { return 4 * J + 1; }
+HRG_HD int reach_fields(int J) { return 3 * J + 2; }
+HRG_HD double& cur_at(const DevState& S, int field, int e) { return S.cur[(size_t)field * S.N + e]; }
+HRG_HD double& ri_at(const DevState& S, int field, int e) { return S.reach_in[(size_t)field * S.N + e]; }
 
 HRG_HD void path_load(const DevState& S, int which, int e, PathS& p) {
   const double* b = S.paths + (size_t)which * PATH_FIELDS * S.N + e;

@@ -135,15 +135,13 @@ HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uin
       f |= (uint32_t)HRG_ST_JOINT_LIMIT << F_STATUS_SHIFT;
     } else {
       f |= F_VERIFY;
-      const double* cur = S.cur + (size_t)e * cur_stride(J);
-      double* ri = S.reach_in + (size_t)e * reach_stride(J);
       for (int j = 0; j < J; ++j) {
-        ri[j] = cur[j];
-        ri[J + j] = gq[j];
-        ri[2 * J + j] = S.ltt_alpha[((size_t)gslot * J + j) * N + e];  // getAlphaI() (:606-610)
+        ri_at(S, j, e) = cur_at(S, j, e);
+        ri_at(S, J + j, e) = gq[j];
+        ri_at(S, 2 * J + j, e) = S.ltt_alpha[((size_t)gslot * J + j) * N + e];  // getAlphaI() (:606-610)
       }
-      ri[3 * J] = s_d - cur[4 * J];                      // goal_motion.getS() - current_motion.getS()
-      ri[3 * J + 1] = t - S.last_meas[e] + t_brake;      // human_reach.cc:79
+      ri_at(S, 3 * J, e) = s_d - cur_at(S, 4 * J, e);          // goal_motion.getS() - current_motion.getS()
+      ri_at(S, 3 * J + 1, e) = t - S.last_meas[e] + t_brake;   // human_reach.cc:79
     }
   } else {
     f |= F_IS_SAFE;
@@ -159,9 +157,10 @@ HRG_HD bool pre_env(const DevState& S, const HrgConfig& c, int e, uint32_t& f) {
   // getCurrentMotion (:649-661): always on the OLD long-term trajectory
   PathS p;
   path_load(S, (f & F_REC_CURRENT) ? P_REC : P_FS, e, p);
-  double* cur = S.cur + (size_t)e * cur_stride(J);
+  double cur[4 * HRG_MAX_JOINTS];
   ltt_interpolate(S, c, e, live, p.pos, p.vel, p.acc, p.jerk, cur, cur + J, cur + 2 * J, cur + 3 * J);
-  cur[4 * J] = p.pos;
+  for (int k = 0; k < 4 * J; ++k) cur_at(S, k, e) = cur[k];
+  cur_at(S, 4 * J, e) = p.pos;
   // :562-568 commit the pending LTT
   if ((f & F_NEW_LTT) && (f & F_NEW_LTT_PROCESSED)) {
     bool stopped = true;  // Motion::isStopped (SS/include/safety_shield/motion.h:142-149)

@@ -41,6 +41,9 @@ def lib():
         L.ref_plan_safety_shield.argtypes = [C.c_void_p, C.c_int, _dp, _u8p, _dp, _dp]
         L.ref_ltp_plan.restype = C.c_int
         L.ref_ltp_plan.argtypes = [C.c_int, C.c_double] + [_dp] * 10 + [C.c_int]
+        L.ref_ltp_opt_braking.argtypes = [C.c_double, _dp, C.c_double, C.c_double, _dp, _dp, _dp]
+        L.ref_ltp_opt_switch_times.argtypes = [C.c_double, _dp] + [C.c_double] * 5 + [_dp, _dp, C.POINTER(C.c_int)]
+        L.ref_ltp_time_scaling.argtypes = [C.c_double, _dp] + [C.c_double] * 6 + [_dp, _dp, C.POINTER(C.c_int)]
         L.ref_poly_roots.restype = C.c_double
         L.ref_poly_roots.argtypes = [C.c_int, _dp, _dp, _dp]
         _lib = L
@@ -153,3 +156,25 @@ def poly_roots(coef):
     re, im = np.zeros(n - 1), np.zeros(n - 1)
     s = lib().ref_poly_roots(n, _d(coef), _d(re), _d(im))
     return s, re, im
+
+
+def ltp_opt_braking(ts, lim, v0, a0):
+    """LongTermPlanner::optBraking for one joint; lim = (q_min, q_max, v_max, a_max, j_max) -> ok, q, t_rel[7], dir."""
+    lim, t = _f64(lim), np.zeros(7)
+    q, d = np.zeros(1), np.zeros(1)
+    ok = lib().ref_ltp_opt_braking(float(ts), _d(lim), float(v0), float(a0), _d(q), _d(t), _d(d))
+    return bool(ok), q[0], t, d[0]
+
+
+def ltp_opt_switch_times(ts, lim, q_goal, q0, v0, a0, v_drive):
+    lim, t, d, m = _f64(lim), np.zeros(7), np.zeros(1), C.c_int(0)
+    ok = lib().ref_ltp_opt_switch_times(float(ts), _d(lim), float(q_goal), float(q0), float(v0), float(a0), float(v_drive),
+                                        _d(t), _d(d), C.byref(m))
+    return bool(ok), t, d[0], m.value
+
+
+def ltp_time_scaling(ts, lim, q_goal, q0, v0, a0, direction, t_required):
+    lim, t, vd, m = _f64(lim), np.zeros(7), np.zeros(1), C.c_int(0)
+    ok = lib().ref_ltp_time_scaling(float(ts), _d(lim), float(q_goal), float(q0), float(v0), float(a0), float(direction),
+                                    float(t_required), _d(t), _d(vd), C.byref(m))
+    return bool(ok), t, vd[0], m.value

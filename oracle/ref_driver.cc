@@ -5,6 +5,7 @@
 // objects and drives them with the loop shape of SS/src/debug.cc:38-55
 // (humanMeasurement -> [newLongTermTrajectory] -> step), dumping everything the parity tests compare.
 // Built with -fno-access-control so private members of the reference classes can be read without touching its sources.
+#include <array>
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -224,6 +225,39 @@ int ref_ltp_plan(int J, double ts, const double* q_min, const double* q_max, con
       o[3 * J + j] = tr.j[j][i];
     }
   return tr.length;
+}
+
+// Single-joint pieces of the planner, as exposed by the reference's own test fixture
+// (LTP/tests/include/long_term_planner_fixture.h:24-29). lim = {q_min, q_max, v_max, a_max, j_max}.
+static long_term_planner::LongTermPlanner make_ltp1(double ts, const double* lim) {
+  return long_term_planner::LongTermPlanner(1, ts, {lim[0]}, {lim[1]}, {lim[2]}, {lim[3]}, {lim[4]});
+}
+int ref_ltp_opt_braking(double ts, const double* lim, double v0, double a0, double* q, double* t_rel /*[7]*/, double* dir) {
+  auto ltp = make_ltp1(ts, lim);
+  std::array<double, 7> t{};
+  bool ok = ltp.optBraking(0, v0, a0, *q, t, *dir);
+  for (int i = 0; i < 7; ++i) t_rel[i] = t[i];
+  return ok ? 1 : 0;
+}
+int ref_ltp_opt_switch_times(double ts, const double* lim, double q_goal, double q0, double v0, double a0, double v_drive,
+                             double* t_out /*[7]*/, double* dir, int* mod) {
+  auto ltp = make_ltp1(ts, lim);
+  std::array<double, 7> t{};
+  char m = 0;
+  bool ok = ltp.optSwitchTimes(0, q_goal, q0, v0, a0, v_drive, t, *dir, m);
+  for (int i = 0; i < 7; ++i) t_out[i] = t[i];
+  *mod = m;
+  return ok ? 1 : 0;
+}
+int ref_ltp_time_scaling(double ts, const double* lim, double q_goal, double q0, double v0, double a0, double dir,
+                         double t_required, double* t_out /*[7]*/, double* v_drive, int* mod) {
+  auto ltp = make_ltp1(ts, lim);
+  std::array<double, 7> t{};
+  char m = 0;
+  bool ok = ltp.timeScaling(0, q_goal, q0, v0, a0, dir, t_required, t, *v_drive, m);
+  for (int i = 0; i < 7; ++i) t_out[i] = t[i];
+  *mod = m;
+  return ok ? 1 : 0;
 }
 
 // roots() + getSmallestPositiveNonComplexRoot (LTP/include/long_term_planner/roots.h:22-50)

@@ -35,7 +35,9 @@ static void emul_reset_env(Emul* E, int e, const double* pose, const double* q0,
   uint32_t f = S.flags[e] & F_UNDER_V_LIMIT;
   f |= ((uint32_t)type << F_TYPE_SHIFT) & F_TYPE_MASK;
   if (type == HRG_SHIELD_OFF) f |= F_IS_SAFE;
-  base_pose_matrix(pose[0], pose[1], pose[2], pose[3], pose[4], pose[5], S.base_T + (size_t)e * 12);
+  double B[12];
+  base_pose_matrix(pose[0], pose[1], pose[2], pose[3], pose[4], pose[5], B);
+  for (int k = 0; k < 12; ++k) S.base_T[(size_t)k * N + e] = B[k];
   S.last_meas[e] = -1;
   PathS z;
   path_clear(z);
@@ -68,8 +70,9 @@ static void emul_reach_verify(Emul* E, int e, uint32_t& f) {
   DevState& S = E->S;
   const HrgConfig& c = E->cfg;
   const int J = S.J, H = S.H;
-  const double* ri = S.reach_in + (size_t)e * reach_stride(J);
-  const double* base = S.base_T + (size_t)e * 12;
+  double ri[3 * HRG_MAX_JOINTS + 2], base[12];
+  for (int k = 0; k < reach_fields(J); ++k) ri[k] = ri_at(S, k, e);
+  for (int k = 0; k < 12; ++k) base[k] = S.base_T[(size_t)k * S.N + e];
   double T[2][16];
   for (int ch = 0; ch < 2; ++ch) {
     for (int i = 0; i < 12; ++i) T[ch][i] = base[i];
@@ -114,9 +117,8 @@ static void emul_reach_verify(Emul* E, int e, uint32_t& f) {
     }
     o[6] = fmax(r_1, r_2) + c.secure_radius;
   }
-  const double* kp = S.kp_pos + (size_t)e * S.K * 3;
-  const double* kv = S.kp_vel + (size_t)e * S.K * 3;
-  for (int h = 0; h < H; ++h) cap_store(human_capsule(c, h, kp, kv, t_reach), hum + h * 7);
+  for (int h = 0; h < H; ++h)
+    cap_store(human_capsule(c, h, S.kp_pos + e, S.kp_vel + e, (size_t)S.N, t_reach), hum + h * 7);
   unsigned coll = 0;
   double md[3] = {INFINITY, INFINITY, INFINITY};
   bool near = false;
@@ -128,7 +130,7 @@ static void emul_reach_verify(Emul* E, int e, uint32_t& f) {
       if (fabs(d) < 1e-6) near = true;
       md[m] = fmin(md[m], d);
     }
-  for (int m = 0; m < 3; ++m) S.min_dist[(size_t)e * 3 + m] = md[m];
+  for (int m = 0; m < 3; ++m) S.min_dist[(size_t)m * S.N + e] = md[m];
   f = (coll != 7u) ? (f | F_IS_SAFE) : (f & ~F_IS_SAFE);
   if (near) f |= (uint32_t)HRG_ST_NEAR_THRESHOLD << F_STATUS_SHIFT;
 }
@@ -151,7 +153,7 @@ void* emul_create(const HrgConfig* cfg, int n, const double* pose, const double*
   E->al(&S.ltt_t0, 2 * N); E->al(&S.ltt_ts, 2 * N); E->al(&S.ltt_alpha, 2 * J * N);
   E->al(&S.base_T, 12 * N); E->al(&S.kp_pos, K * 3 * N); E->al(&S.kp_vel, K * 3 * N); E->al(&S.last_meas, N);
   E->al(&S.ltt, N * 2 * L * 4 * J); E->al(&S.ltt_cart, N * 2 * L);
-  E->al(&S.cur, N * cur_stride(J)); E->al(&S.reach_in, N * reach_stride(J)); E->al(&S.min_dist, 3 * N);
+  E->al(&S.cur, N * cur_fields(J)); E->al(&S.reach_in, N * reach_fields(J)); E->al(&S.min_dist, 3 * N);
   E->robot.assign(N * J * 7, 0.0);
   E->human.assign(N * H * 7, 0.0);
   for (int e = 0; e < n; ++e) emul_reset_env(E, e, pose + 6 * (size_t)e, q0 + (size_t)J * e, type ? type[e] : HRG_SHIELD_SSM);
@@ -185,8 +187,9 @@ void emul_human_measurement(void* h, const uint8_t* mask, const double* kp, cons
     }
     for (int i = 0; i < K3; ++i) {
       double p = kp[(size_t)e * K3 + i];
-      if (diff) S.kp_vel[(size_t)e * K3 + i] = (p - S.kp_pos[(size_t)e * K3 + i]) * inv;
-      S.kp_pos[(size_t)e * K3 + i] = p;
+      const size_t o = (size_t)i * S.N + e;
+      if (diff) S.kp_vel[o] = (p - S.kp_pos[o]) * inv;
+      S.kp_pos[o] = p;
     }
     S.last_meas[e] = now;
   }
@@ -207,7 +210,8 @@ void emul_step(void* h, const double* t, double* q, double* dq, double* ddq, dou
     if (pre_env(S, c, e, f)) {
       // k_replan, sequential
       const int pend = (f & F_LIVE_SLOT) ? 0 : 1;
-      const double* cur = S.cur + (size_t)e * cur_stride(J);
+      double cur[3 * HRG_MAX_JOINTS];
+      for (int k = 0; k < 3 * J; ++k) cur[k] = cur_at(S, k, e);
       double goal[HRG_MAX_JOINTS];
       for (int j = 0; j < J; ++j) goal[j] = S.goal_q[(size_t)j * N + e];
       uint32_t st = HRG_ST_REPLANNED;
@@ -246,7 +250,9 @@ void emul_get_capsules(void* h, double* robot, double* human, double* min_dist) 
   Emul* E = static_cast<Emul*>(h);
   if (robot) memcpy(robot, E->robot.data(), E->robot.size() * 8);
   if (human) memcpy(human, E->human.data(), E->human.size() * 8);
-  if (min_dist) memcpy(min_dist, E->S.min_dist, (size_t)E->S.N * 3 * 8);
+  if (min_dist)
+    for (int e = 0; e < E->S.N; ++e)
+      for (int m = 0; m < 3; ++m) min_dist[(size_t)e * 3 + m] = E->S.min_dist[(size_t)m * E->S.N + e];
 }
 void emul_get_state(void* h, int e, double* out /*[52]*/) {
   Emul* E = static_cast<Emul*>(h);
@@ -282,5 +288,5 @@ int emul_ltp_plan(const HrgConfig* cfg, const double* goal, const double* q0, co
                   double* traj, int cap) {
   return ltp_plan_env_seq(*cfg, goal, q0, v0, a0, traj, cap);
 }
-double emul_poly_root(const double* coef, int ncoef) { return smallest_positive_real_root(coef, ncoef); }
+double emul_poly_root(const double* coef, int ncoef) { LtpLimits L{}; return smallest_positive_real_root(L, coef, ncoef); }
 }

@@ -1,0 +1,90 @@
+"""CPU: the C-ABI library loads, exports every symbol include/hrg_shield.h declares, its structs match the ctypes
+mirrors, and the product path fails loudly (no CPU fallback) when there is no CUDA device."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from human_robot_gym_b200 import cabi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "hrg_shield.h")
+
+
+def declared_functions():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(hrg_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_declares_the_expected_surface():
+    names = declared_functions()
+    # one entry point per method of the reference's pybind class (SS/bindings/safety_shield_bindings.cpp:82-115)
+    for must in ("hrg_shield_create", "hrg_shield_reset", "hrg_shield_step", "hrg_shield_new_goal", "hrg_shield_set_ltt",
+                 "hrg_shield_human_measurement", "hrg_shield_get_capsules", "hrg_shield_destroy"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    lib = cabi.load_library()
+    names = declared_functions()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/hrg_shield.h but not exported by libhrg_shield.so"
+        assert n in cabi.SYMBOLS, f"{n} has no ctypes prototype in cabi.SYMBOLS"
+    assert sorted(cabi.SYMBOLS) == names
+
+
+def test_struct_layout_matches_the_header(tmp_path):
+    prog = tmp_path / "sz.c"
+    prog.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "hrg_shield.h"\n'
+                    'int main(void){printf("%zu %zu %zu %zu %zu\\n", sizeof(HrgConfig), sizeof(HrgStats), '
+                    'offsetof(HrgConfig, link_T), offsetof(HrgConfig, ext_vmax), offsetof(HrgStats, min_dist));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(prog)])
+    out = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert out[0] == C.sizeof(cabi.HrgConfig)
+    assert out[1] == C.sizeof(cabi.HrgStats)
+    assert out[2] == cabi.HrgConfig.link_T.offset
+    assert out[3] == cabi.HrgConfig.ext_vmax.offset
+    assert out[4] == cabi.HrgStats.min_dist.offset
+
+
+def _has_cuda():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.mark.skipif(_has_cuda(), reason="checks the no-device error path")
+def test_no_cpu_fallback(config_dir):
+    """Without a CUDA device creation fails with HRG_ENODEVICE and the host class raises; nothing computes on the CPU."""
+    from human_robot_gym_b200.config import ShieldConfig
+    lib = cabi.load_library()
+    d = config_dir
+    sc = ShieldConfig.from_files(0.004, f"{d}/trajectory_parameters_schunk.yaml", f"{d}/robot_parameters_schunk.yaml",
+                                 f"{d}/mujoco_mocap.yaml")
+    cfg = cabi.make_cfg(sc, 64)
+    pose, q0 = np.zeros((4, 6)), np.zeros((4, 6))
+    h = C.c_void_p()
+    rc = lib.hrg_shield_create(C.byref(cfg), 4, 0, pose.ctypes.data, q0.ctypes.data, None, C.byref(h))
+    assert rc == cabi.ENODEVICE
+    assert not h.value
+    assert b"no CUDA device" in lib.hrg_last_error()
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    with pytest.raises(cabi.ShieldLibraryError):
+        BatchedSafetyShield(4, 0.004, f"{d}/trajectory_parameters_schunk.yaml", f"{d}/robot_parameters_schunk.yaml",
+                            f"{d}/mujoco_mocap.yaml")
+
+
+def test_argument_validation_without_device():
+    lib = cabi.load_library()
+    assert lib.hrg_shield_create(None, 1, 0, None, None, None, C.byref(C.c_void_p())) == cabi.EINVAL
+    assert lib.hrg_shield_step(None, None, None, None, None, None, None, None, None, None) == cabi.EINVAL
+    assert lib.hrg_shield_num_envs(None) == 0
+    assert lib.hrg_stage_capsule_dist(-1, None, None, None, None) == cabi.EINVAL
