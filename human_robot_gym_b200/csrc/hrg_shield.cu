@@ -167,8 +167,13 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   AL(S.min_dist, 3 * N);
   AL(S.replan_list, N);
   AL(S.replan_count, 1);
-  AL(S.replan_next, 1);
+  AL(S.replan_ctr, 8);
+  AL(S.deep_list, (size_t)N * J);
+  AL(S.deep_res, (size_t)N * J * 6);
   AL(S.replan_mark, N);
+  AL(S.plan_opt, (size_t)N * HRG_MAX_JOINTS);
+  AL(S.plan_sc, (size_t)N * HRG_MAX_JOINTS);
+  AL(S.plan_head, N);
   AL(S.stats, 1);
   S.ltt_cart = nullptr;
   S.robot_caps = nullptr;
@@ -288,21 +293,28 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   }
   k_pre_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
   if (prof) cudaEventRecord(ev[1], st);
-  // one warp per replanning env, work fetched from a device counter; the grid only bounds the resident warps
-  const int warps_per_block = kReplanBlock / 32;
-  int rgrid = grid_for(N, warps_per_block);
-  if (rgrid > s->sm_count * 10) rgrid = s->sm_count * 10;
   const bool fork = s->overlap && !prof;
+  cudaStream_t rs = fork ? s->side : st;
   if (fork) {
     // replan || reach + verify of the envs that do not replan, then the replanned envs
     CK(cudaEventRecord(s->ev_fork, st));
     CK(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
-    k_replan<<<rgrid, kReplanBlock, 0, s->side>>>(s->S, t);
+  }
+  {
+    // the replan list length is only known on the device: grids cover the worst case (every env replans) and surplus
+    // groups / warps leave at once; k_replan_scale fetches (env, joint) tasks from a counter, its grid only bounds residency
+    int sgrid = grid_for(N * s->S.J, kReplanBlock / 32);
+    if (sgrid > s->sm_count * HRG_REPLAN_MINBLOCKS) sgrid = s->sm_count * HRG_REPLAN_MINBLOCKS;
+    k_replan_opt<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_scale<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_deep<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_sample<<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
+  }
+  if (fork) {
     CK(cudaEventRecord(s->ev_join, s->side));
     k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 0);
     CK(cudaStreamWaitEvent(st, s->ev_join, 0));
   } else {
-    k_replan<<<rgrid, kReplanBlock, 0, st>>>(s->S, t);
     if (prof) cudaEventRecord(ev[2], st);
     k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 0);
   }
@@ -310,7 +322,7 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   if (prof) cudaEventRecord(ev[3], st);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
   if (prof) cudaEventRecord(ev[4], st);
-  s->launches += 5;
+  s->launches += 8;
   CK(cudaGetLastError());
   return HRG_OK;
 }

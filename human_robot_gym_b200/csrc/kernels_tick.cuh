@@ -32,130 +32,276 @@ __global__ void __launch_bounds__(kTickBlock) k_pre_plan(DevState S, const doubl
   S.flags[e] = f;
 }
 
-constexpr int kReplanBlock = 64;  // two warps = two envs per block
+constexpr int kReplanBlock = 64;
+#ifndef HRG_REPLAN_MINBLOCKS
+#define HRG_REPLAN_MINBLOCKS 12  // resident 64-thread blocks per SM the single-lane replan kernels are compiled for
+#endif
 
-// calculateLongTermTrajectory (SS/src/safety_shield.cc:732-760) -> LongTermPlanner::planTrajectory
-// (LTP/src/long_term_planner.cc:7-63) for the envs on the replan list. ONE WARP PER ENV, work fetched from a device
-// counter (plans differ a lot in cost): lane = joint + 8 * sub. The (branchy, FP64) switch-time planning runs on the
-// sub == 0 lanes; while sampling, each sub-lane evaluates the jerk of one of four consecutive samples and stores one of
-// the four components, the integration itself stays the reference's sequential recurrence (bit-identical sums).
-// Lanes with joint >= J shadow joint J-1 and never write. Lane 0 then finishes the env's step up to the reach/verify
-// hand-over. The first version packed four envs into a warp and was latency bound (profiles/r01_ncu_summary.md).
-__global__ void __launch_bounds__(kReplanBlock, 8) k_replan(DevState S, const double* __restrict__ t) {
+// ---- calculateLongTermTrajectory (SS/src/safety_shield.cc:732-760) -> LongTermPlanner::planTrajectory
+// (LTP/src/long_term_planner.cc:7-63) for the envs on the replan list, as four kernels. The planner is branchy FP64
+// code whose cost differs by two orders of magnitude between joints (up to eight profile shapes, six of them behind a
+// companion-matrix eigenvalue solve, each followed by an optSwitchTimes trial that may solve two more quartics). The
+// whole batch only holds a few thousand such problems per tick, so the kernel time is the LONGEST dependent chain, not
+// the instruction total: lanes that diverge serialise, and a warp that walks the whole ladder is the tail everybody
+// waits for. Hence the unit of scheduling is as small as the reference's data flow allows:
+//   k_replan_opt     1 warp per (env, joint)             checkInputs + optSwitchTimes                      (:20-37)
+//   k_replan_scale   1 warp per (env, joint)             slowest joint -> t_required; the two closed-form
+//                                                        timeScaling candidates (:378-436); joints that need the
+//                                                        polynomial candidates go on the `deep` list
+//   k_replan_deep    1 warp per (deep joint, candidate)  the six polynomial candidates (:449-629), all evaluated; the
+//                                                        first accepted one in the reference's order is taken later,
+//                                                        which is what its sequential ladder returns
+//   k_replan_sample  1 warp per env                      getTrajectory (:706-841), joint-limit test (:59-61), LTT
+//                                                        install, and the rest of the env's step up to reach / verify.
+// Work is fetched from device counters (S.replan_ctr); grids only bound residency. Only lane 0 of a warp computes in
+// the first three kernels: more lanes would only serialise. profiles/r01_ncu_summary.md has the measurements.
+enum { CTR_OPT = 0, CTR_SCALE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, N_CTR = 4 };
+
+__device__ __forceinline__ int fetch_task(int32_t* ctr, int lane) {
+  int task = 0;
+  if (lane == 0) task = atomicAdd(ctr, 1);
+  return __shfl_sync(0xffffffffu, task, 0);
+}
+__device__ __forceinline__ LtpLimits joint_limits(const HrgConfig& c, int j, double* mat) {
+  LtpLimits L;
+  L.v_max = c.v_max[j]; L.a_max = c.a_max_ltt[j]; L.j_max = c.j_max_ltt[j]; L.t_sample = c.sample_time;
+  L.mat = mat;
+  return L;
+}
+
+__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_opt(DevState S) {
+  __shared__ double mat_s[kReplanBlock / 32][36];
+  const HrgConfig& c = *S.cfg;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int J = S.J, N = S.N;
+  const int ntask = *S.replan_count * J;
+  for (;;) {
+    const int task = fetch_task(S.replan_ctr + CTR_OPT, lane);
+    if (task >= ntask) break;
+    if (lane != 0) continue;
+    const int idx = task / J, j = task - idx * J;
+    const int e = S.replan_list[idx];
+    const LtpLimits L = joint_limits(c, j, mat_s[wib]);
+    const double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
+    const double q_goal = S.goal_q[(size_t)j * N + e];
+    PlanRec rec;
+    ltp_zero7(rec.T);
+    rec.dir = 0.0; rec.v_drive = L.v_max; rec.mod = 0;
+    bool ok = ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0);
+    // (the reference stops at the first joint that fails; the outputs of the others are never used then)
+    if (ok) ok = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, rec.T, rec.dir, rec.mod);
+    rec.len = ok ? 1 : 0;
+    S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j] = rec;
+  }
+}
+
+// The `mx <= 0` fallback of planTrajectory (:47-50) and the joint's sample count.
+__device__ __forceinline__ void finish_scaled(const LtpLimits& L, const PlanRec& opt, const double* T, double v_drive,
+                                              int mod, PlanRec& sc) {
+  sc = opt;
+  double mx = T[0];
+  for (int k = 1; k < 7; ++k) mx = (mx < T[k]) ? T[k] : mx;
+  if (!(mx <= 0.0))
+    for (int k = 0; k < 7; ++k) sc.T[k] = T[k];
+  sc.v_drive = v_drive;
+  sc.mod = mod;
+  JointPlan P;
+  for (int k = 0; k < 7; ++k) P.T[k] = sc.T[k];
+  sc.len = ltp_joint_len(L, P);
+}
+
+__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_scale(DevState S) {
+  const HrgConfig& c = *S.cfg;
+  const int lane = threadIdx.x & 31;
+  const int J = S.J, N = S.N;
+  const int ntask = *S.replan_count * J;
+  for (;;) {
+    const int task = fetch_task(S.replan_ctr + CTR_SCALE, lane);
+    if (task >= ntask) break;
+    if (lane != 0) continue;
+    const int idx = task / J, j = task - idx * J;
+    const PlanRec* opts = S.plan_opt + (size_t)idx * HRG_MAX_JOINTS;
+    // slowest joint (:39-45)
+    PlanHead h;
+    h.t_required = -1;
+    h.slowest = -1;
+    h.ok = 1;
+    for (int k = 0; k < J; ++k) {
+      if (!opts[k].len) h.ok = 0;
+      const double tk = opts[k].T[6];
+      if (tk > h.t_required) {
+        h.t_required = tk;
+        h.slowest = k;
+      }
+    }
+    if (h.slowest == -1) h.ok = 0;
+    if (j == 0) S.plan_head[idx] = h;
+    const PlanRec opt = opts[j];
+    PlanRec sc = opt;
+    const LtpLimits L = joint_limits(c, j, nullptr);  // the closed-form candidates never reach the root finder ...
+    if (h.ok) {
+      double T[7];
+      ltp_zero7(T);
+      double v_drive = L.v_max;
+      int mod = opt.mod;
+      bool deep = false;
+      if (j != h.slowest) {
+        const int e = S.replan_list[idx];
+        double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
+        const double q_goal = S.goal_q[(size_t)j * N + e];
+        if (opt.dir < 0) {
+          v_0 = -v_0;
+          a_0 = -a_0;
+        }
+        const double v_orig = opt.dir * v_0, a_orig = opt.dir * a_0;
+        bool acc = false;
+        for (int cand = 0; cand < 2 && !acc; ++cand) {
+          double A[7];
+          int ncoef;
+          v_drive = ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, opt.dir, h.t_required, A, ncoef);
+          // ... but the optSwitchTimes trial can (two quartics, :246-261,301-321): it gets a local matrix then
+          acc = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, h.t_required, T, mod);
+        }
+        deep = !acc;
+      }
+      if (deep) {
+        const int slot = atomicAdd(S.replan_ctr + CTR_DEEP_COUNT, 1);
+        S.deep_list[slot] = task;
+        sc.len = -(slot + 1);
+      } else {
+        finish_scaled(L, opt, T, v_drive, mod, sc);
+      }
+    }
+    S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j] = sc;
+  }
+}
+
+__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_deep(DevState S) {
+  __shared__ double mat_s[kReplanBlock / 32][36];
+  const HrgConfig& c = *S.cfg;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int J = S.J, N = S.N;
+  const int ntask = S.replan_ctr[CTR_DEEP_COUNT] * 6;
+  for (;;) {
+    const int dt = fetch_task(S.replan_ctr + CTR_DEEP, lane);
+    if (dt >= ntask) break;
+    if (lane != 0) continue;
+    const int slot = dt / 6, cand = 2 + (dt - slot * 6);
+    const int task = S.deep_list[slot];
+    const int idx = task / J, j = task - idx * J;
+    const int e = S.replan_list[idx];
+    const PlanHead h = S.plan_head[idx];
+    const PlanRec opt = S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j];
+    const LtpLimits L = joint_limits(c, j, mat_s[wib]);
+    double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
+    const double q_goal = S.goal_q[(size_t)j * N + e];
+    if (opt.dir < 0) {
+      v_0 = -v_0;
+      a_0 = -a_0;
+    }
+    const double v_orig = opt.dir * v_0, a_orig = opt.dir * a_0;
+    PlanRec r;
+    ltp_zero7(r.T);
+    r.dir = opt.dir;
+    r.mod = opt.mod;
+    double A[7];
+    int ncoef;
+    ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, opt.dir, h.t_required, A, ncoef);
+    r.v_drive = ltp_scaling_vdrive(L, cand, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
+    r.len = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, r.v_drive, h.t_required, r.T, r.mod) ? 1 : 0;
+    S.deep_res[(size_t)slot * 6 + (cand - 2)] = r;
+  }
+}
+
+// One warp per env: lane = joint gl + 8 * sub. Each sub-lane evaluates the jerk of one of four consecutive samples and
+// stores one of the four components; the integration itself stays the reference's sequential recurrence (bit-identical
+// sums). Lane 0 then finishes the env's step up to the reach / verify hand-over.
+__global__ void __launch_bounds__(128) k_replan_sample(DevState S, const double* __restrict__ t) {
+  __shared__ JerkSampler samp_s[4][8];
+  __shared__ double jbuf_s[4][8 * 32];
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int gl = lane & 7, sub = lane >> 3;
-  const int count = *S.replan_count;
+  const int idx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (idx >= *S.replan_count) return;  // whole warps leave together
   const int J = S.J, N = S.N;
   const int j = gl < J ? gl : J - 1;
   const bool joint_lane = gl < J;
-  // dynamically indexed scratch goes to shared memory, not to local memory: with 16 resident warps per SM the per-thread
-  // stack of the first version (companion matrix + jerk sampler, 624 B x 32 lanes x 16 warps) overflowed the L1
-  __shared__ double mat_s[kReplanBlock / 32][36][8];
-  __shared__ JerkSampler samp_s[kReplanBlock / 32][8];
-  const int wib = threadIdx.x >> 5;
+  const int e = S.replan_list[idx];
+  uint32_t f = S.flags[e];
+  const int pend = (f & F_LIVE_SLOT) ? 0 : 1;
+  const PlanHead h = S.plan_head[idx];
+  uint32_t status = HRG_ST_REPLANNED;
+  bool ok = h.ok != 0;
+  int len = 0;
   LtpLimits L;
   L.v_max = c.v_max[j]; L.a_max = c.a_max_ltt[j]; L.j_max = c.j_max_ltt[j]; L.t_sample = c.sample_time;
-  L.mat = &mat_s[wib][0][gl];
-  L.mat_stride = 8;
-  for (;;) {
-    int idx = 0;
-    if (lane == 0) idx = atomicAdd(S.replan_next, 1);
-    idx = __shfl_sync(full, idx, 0);
-    if (idx >= count) break;
-    const int e = S.replan_list[idx];
-    uint32_t f = S.flags[e];
-    const int pend = (f & F_LIVE_SLOT) ? 0 : 1;
-    const double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
-    const double q_goal = S.goal_q[(size_t)j * N + e];
-    uint32_t status = HRG_ST_REPLANNED;
-    int len = 0;
-    // switch-time planning on the sub == 0 lanes only (it keeps a 6x6 companion matrix in local memory: replicating it
-    // over the sub-lanes would quadruple the L1 footprint); the other lanes vote "ok" and receive the plan afterwards.
-    const bool planner = sub == 0;
-    bool ok = planner ? ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0) : true;
-    ok = __all_sync(full, ok);
-    JointPlan opt, sc;
-    ltp_zero7(opt.T);
-    opt.dir = 0.0; opt.v_drive = L.v_max; opt.mod = 0;
-    sc = opt;
-    if (ok) {
-      if (planner) ok = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, opt.T, opt.dir, opt.mod);
-      ok = __all_sync(full, ok);
+  const double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
+  if (ok) {
+    PlanRec rec = S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j];
+    if (rec.len < 0) {
+      // a joint from the deep list: first accepted polynomial candidate in the reference's order, else "no valid
+      // solution" (:640-644: zero times, v_drive = v_max, standard profile)
+      const PlanRec* res = S.deep_res + (size_t)(-rec.len - 1) * 6;
+      const PlanRec opt = S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j];
+      double T[7];
+      ltp_zero7(T);
+      double v_drive = L.v_max;
+      int mod = 0;
+      for (int k = 0; k < 6; ++k)
+        if (res[k].len) {
+          for (int i = 0; i < 7; ++i) T[i] = res[k].T[i];
+          v_drive = res[k].v_drive;
+          mod = res[k].mod;
+          break;
+        }
+      finish_scaled(L, opt, T, v_drive, mod, rec);
+    }
+    JointPlan sc;
+    for (int k = 0; k < 7; ++k) sc.T[k] = rec.T[k];
+    sc.dir = rec.dir; sc.v_drive = rec.v_drive; sc.mod = rec.mod;
+    len = rec.len;
+    for (int o = 4; o > 0; o >>= 1) {
+      const int other = __shfl_xor_sync(full, len, o);
+      len = other > len ? other : len;
+    }
+    if (len > S.L) {
+      status |= HRG_ST_LTT_TRUNCATED;
+      ok = false;
+    } else if (len < 1) {
+      ok = false;
     }
     if (ok) {
-      double t_required = -1;
-      int slowest = -1;
-      for (int k = 0; k < J; ++k) {
-        double tk = __shfl_sync(full, opt.T[6], k);
-        if (tk > t_required) {
-          t_required = tk;
-          slowest = k;
-        }
-      }
-      ok = slowest != -1;
-      if (ok) {
-        if (planner) {
-          sc = opt;
-          sc.v_drive = L.v_max;
-          ltp_zero7(sc.T);
-          if (j != slowest)
-            ltp_time_scaling(L, q_goal, q_0, v_0, a_0, opt.dir, t_required, sc.T, sc.v_drive, sc.mod);
-          double mx = sc.T[0];
-          for (int k = 1; k < 7; ++k) mx = (mx < sc.T[k]) ? sc.T[k] : mx;
-          if (mx <= 0.0)
-            for (int k = 0; k < 7; ++k) sc.T[k] = opt.T[k];
-        }
-        // hand the joint's plan to its sub-lanes
-        for (int k = 0; k < 7; ++k) sc.T[k] = __shfl_sync(full, sc.T[k], gl);
-        sc.dir = __shfl_sync(full, sc.dir, gl);
-        sc.v_drive = __shfl_sync(full, sc.v_drive, gl);
-        sc.mod = __shfl_sync(full, sc.mod, gl);
-        len = ltp_joint_len(L, sc);
-        for (int o = 4; o > 0; o >>= 1) {
-          int other = __shfl_xor_sync(full, len, o);
-          len = other > len ? other : len;
-        }
-        if (len > S.L) {
-          status |= HRG_ST_LTT_TRUNCATED;
-          ok = false;
-        } else if (len < 1) {
-          ok = false;
-        }
-      }
-    }
-    if (ok) {
-      const double qf = ltp_sample_joint_warp(L, sc, q_0, v_0, a_0, len, ltt_sample_w(S, e, pend, 0), J, gl, sub, joint_lane,
-                                              samp_s[wib][gl]);
+      const double qf = ltp_sample_joint_warp(L, sc, q_0, v_0, a_0, len, ltt_sample_w(S, e, pend, 0), J, gl, j, sub,
+                                              joint_lane, samp_s[wib], jbuf_s[wib]);
       const bool in = !(qf < c.q_min[j] || qf > c.q_max[j]);
       ok = __all_sync(full, in);
     }
-    if (ok && joint_lane && sub == 0) {
-      S.replan_q[(size_t)j * N + e] = q_0;  // last_replan_start_motion_ = current_motion (:593)
-      // SSM/OFF: alpha_i_ = alpha_i_max (long_term_traj.h:108-116)
-      S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
+  }
+  if (ok && joint_lane && sub == 0) {
+    S.replan_q[(size_t)j * N + e] = q_0;  // last_replan_start_motion_ = current_motion (:593)
+    // SSM/OFF: alpha_i_ = alpha_i_max (long_term_traj.h:108-116)
+    S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
+  }
+  __syncwarp(full);
+  if (lane == 0) {
+    if (ok) {
+      S.ltt_len[(size_t)pend * N + e] = len;
+      S.ltt_cur[(size_t)pend * N + e] = 0;
+      S.ltt_start[(size_t)pend * N + e] = S.path_sd[e];
+      S.ltt_t0[(size_t)pend * N + e] = S.path_s[e];
+      S.ltt_ts[(size_t)pend * N + e] = c.sample_time;
+      f |= F_NEW_LTT;
+      f &= ~F_NEW_LTT_PROCESSED;
+    } else {
+      f &= ~F_NEW_LTT;
+      status |= HRG_ST_REPLAN_FAILED;
     }
-    __syncwarp(full);
-    if (lane == 0) {
-      if (ok) {
-        S.ltt_len[(size_t)pend * N + e] = len;
-        S.ltt_cur[(size_t)pend * N + e] = 0;
-        S.ltt_start[(size_t)pend * N + e] = S.path_sd[e];
-        S.ltt_t0[(size_t)pend * N + e] = S.path_s[e];
-        S.ltt_ts[(size_t)pend * N + e] = c.sample_time;
-        f |= F_NEW_LTT;
-        f &= ~F_NEW_LTT_PROCESSED;
-      } else {
-        f &= ~F_NEW_LTT;
-        status |= HRG_ST_REPLAN_FAILED;
-      }
-      f &= ~F_PENDING_REPLAN;
-      f |= status << F_STATUS_SHIFT;
-      plan_env(S, c, e, t[e], f);
-      S.flags[e] = f;
-    }
-    __syncwarp(full);
+    f &= ~F_PENDING_REPLAN;
+    f |= status << F_STATUS_SHIFT;
+    plan_env(S, c, e, t[e], f);
+    S.flags[e] = f;
   }
 }
 
@@ -171,7 +317,7 @@ __global__ void __launch_bounds__(kTickBlock)
   __syncthreads();
   if (e == 0) {
     *S.replan_count = 0;
-    *S.replan_next = 0;
+    for (int k = 0; k < N_CTR; ++k) S.replan_ctr[k] = 0;
   }
   unsigned long long my[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum
   double my_min = INFINITY;

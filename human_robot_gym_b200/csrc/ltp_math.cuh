@@ -8,10 +8,9 @@ namespace hrg {
 
 struct LtpLimits {  // limits of ONE joint (LongTermPlanner members, long_term_planner.h)
   double v_max, a_max, j_max, t_sample;
-  // scratch for the <= 6x6 companion matrix of the root finder: element k lives at mat[k * mat_stride]. NULL = a local
-  // array (host tests, stage kernel); the replan kernel points it at a lane-interleaved slice of shared memory.
+  // 36 doubles of scratch for the <= 6x6 companion matrix of the root finder. NULL = a local array (host tests, stage
+  // kernel); the replan kernels point it at shared memory (dynamically indexed local arrays would live in L1/L2).
   double* mat = nullptr;
-  int mat_stride = 1;
 };
 
 HRG_HD int isign(double v) { return (0.0 < v) - (v < 0.0); }  // long_term_planner.h sign()
@@ -24,12 +23,10 @@ HRG_HD double pow6(double x) { return sq(cube(x)); }
 // Same algorithm family as Eigen::EigenSolver (real Schur form by Francis double-shift QR on the — already upper
 // Hessenberg — companion matrix); real eigenvalues are those whose 1x1 block was deflated or whose 2x2 block has a
 // non-negative discriminant, which is exactly when Eigen reports imag() == 0 (roots.h:46).
-struct SmallMat {
+struct SmallMat {  // column-major with a fixed leading dimension of 6
   double* a;
-  int st;
   int n;
-  HRG_HD double& operator()(int i, int j) { return a[(j * n + i) * st]; }
-  HRG_HD double& at(int k) { return a[k * st]; }
+  HRG_HD double& operator()(int i, int j) { return a[j * 6 + i]; }
 };
 
 HRG_HD void mk_householder(const double* x, int m, double* ess, double& tau, double& beta) {
@@ -221,21 +218,23 @@ HRG_HD_CALL double smallest_positive_real_root(const LtpLimits& L, const double*
   double local_mat[36];
   SmallMat C;
   C.a = L.mat ? L.mat : local_mat;
-  C.st = L.mat ? L.mat_stride : 1;
   const int n = ncoef - 1;
   C.n = n;
-  for (int i = 0; i < n * n; ++i) C.at(i) = 0.0;
+  for (int i = 0; i < 36; ++i) C.a[i] = 0.0;
   for (int i = 0; i + 1 < n; ++i) C(i + 1, i) = 1.0;
   // poly = -1 * poly / poly[0]; last column = reversed poly, first n entries (constant term on top)
   for (int i = 0; i < n; ++i) C(i, n - 1) = (-1 * coef[ncoef - 1 - i]) / coef[0];
   // EigenSolver: scale by the largest |coefficient|, (Hessenberg reduction is the identity here), Schur, scale back
   double scale = 0.0;
-  for (int i = 0; i < n * n; ++i) scale = fabs(C.at(i)) > scale ? fabs(C.at(i)) : scale;
+  for (int j = 0; j < n; ++j)
+    for (int i = 0; i < n; ++i) scale = fabs(C(i, j)) > scale ? fabs(C(i, j)) : scale;
   double best = INFINITY;
   if (scale < 2.2250738585072014e-308) return best;  // all eigenvalues 0
-  for (int i = 0; i < n * n; ++i) C.at(i) /= scale;
+  for (int j = 0; j < n; ++j)
+    for (int i = 0; i < n; ++i) C(i, j) /= scale;
   real_schur_hessenberg(C);
-  for (int i = 0; i < n * n; ++i) C.at(i) *= scale;
+  for (int j = 0; j < n; ++j)
+    for (int i = 0; i < n; ++i) C(i, j) *= scale;
   int i = 0;
   while (i < n) {
     if (i == n - 1 || C(i + 1, i) == 0.0) {

@@ -16,16 +16,16 @@ HRG_HD_CALL bool ltp_try_vdrive(const LtpLimits& L, double q_goal, double q_0, d
   return false;
 }
 
-HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double dir,
-                             double tr /*t_required*/, double* T /*scaled_t*/, double& v_drive, int& mod_jerk_profile) {
+// Candidate c (0..7 = the reference's profile shapes in its order, :378-629): either the closed-form v_drive (c = 0, 1;
+// ncoef = 0) or the coefficients A[0..ncoef) of the polynomial whose smallest positive real root gives v_drive.
+// v_0 / a_0 are already mirrored for dir < 0.
+HRG_HD_CALL double ltp_scaling_setup(const LtpLimits& L, int cand, double q_goal, double q_0, double v_0, double a_0,
+                                     double dir, double tr /*t_required*/, double* A /*[7]*/, int& ncoef) {
   const double jm = L.j_max, am = L.a_max;
-  if (dir < 0) {
-    v_0 = -v_0;
-    a_0 = -a_0;
-  }
-  const double v_orig = dir * v_0, a_orig = dir * a_0;  // what the reference passes on to optSwitchTimes
-
-  // (1) standard profile, phases 2 and 6 exist (:378-396)
+  double v_drive = 0.0;
+  ncoef = 0;
+  switch (cand) {
+    case 0: {  // (1) standard profile, phases 2 and 6 exist (:378-396)
   v_drive = (am * jm * tr / 2 - sq(a_0) / 4 + a_0 * am / 2 - sq(am) / 2 + v_0 * jm / 2 -
              sqrt(36 * sq(am) * sq(jm) * sq(tr) - 36 * sq(a_0) * am * jm * tr + 72.0 * a_0 * sq(am) * jm * tr -
                   72.0 * cube(am) * jm * tr + 144 * am * dir * sq(jm) * q_0 - 144 * am * dir * sq(jm) * q_goal +
@@ -34,12 +34,10 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
                   36 * sq(jm) * sq(v_0)) /
                  12) /
             jm;
-  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
-
-  // (2) modified profile, phases 2 and 6 exist (:408-436). Common sub-terms of the reference expression:
-  //   w  = (v_0 + a_0 (a_0 - am) / (2 jm)) / am
-  //   h  = am / (2 jm),  g = (a_0 - am) / (2 jm),  s = a_0 + am
-  {
+      break;
+    }
+    case 1: {  // (2) modified profile, phases 2 and 6 exist (:408-436). Common sub-terms of the reference expression:
+      //   w  = (v_0 + a_0 (a_0 - am) / (2 jm)) / am,  h  = am / (2 jm),  g = (a_0 - am) / (2 jm),  s = a_0 + am
     const double w = (v_0 + (a_0 * (a_0 - am)) / (2.0 * jm)) / am;
     const double h = am / (2.0 * jm);
     const double g = (a_0 - am) / (2.0 * jm);
@@ -54,11 +52,9 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
                        (sq(a_0) + 2.0 * a_0 * am + 4 * sq(am) - 2.0 * jm * tr * am + 2.0 * jm * v_0) / (2.0 * am * jm) +
                        sq(s) / (2.0 * am * jm) - (a_0 * s) / (am * jm);
     v_drive = -num / den;
-  }
-  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
-
-  double A[7], root;
-  // (3) standard profile, phase 2 does not exist (:449-473)
+      break;
+    }
+    case 2:  // (3) standard profile, phase 2 does not exist (:449-473)
   A[0] = 3;
   A[1] = 12.0 * am;
   A[2] = -24 * am * jm * tr - 12.0 * sq(a_0) - 24 * a_0 * am + 12.0 * sq(am) + 24 * jm * v_0;
@@ -66,11 +62,9 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
   A[4] = 48 * sq(a_0) * am * jm * tr - 96 * dir * sq(jm) * am * q_0 + 96 * dir * sq(jm) * am * q_goal -
          96 * am * sq(jm) * v_0 * tr + 12.0 * pow4(a_0) + 16 * cube(a_0) * am - 24 * sq(a_0) * sq(am) -
          48 * sq(a_0) * jm * v_0 + 48 * sq(am) * jm * v_0 + 48 * sq(jm) * sq(v_0);
-  root = smallest_positive_real_root(L, A, 5);
-  v_drive = (-2.0 * sq(a_0) + 4 * jm * v_0 + sq(root)) / (4 * jm);
-  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
-
-  // (4) standard profile, phase 6 does not exist (:485-514)
+      ncoef = 5;
+      break;
+    case 3:  // (4) standard profile, phase 6 does not exist (:485-514)
   A[0] = 12;
   A[1] = 24 * am;
   A[2] = -24 * am * jm * tr + 24 * sq(a_0) - 48 * a_0 * am + 24 * sq(am) - 24 * jm * v_0 + 12.0 * a_0 - 12.0 * am;
@@ -79,11 +73,9 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
          24 * sq(a_0) * jm * v_0 + 48 * a_0 * am * jm * v_0 + 4 * pow4(am) - 24 * sq(am) * jm * v_0 +
          12.0 * sq(jm) * sq(v_0) + 6 * cube(a_0) + 6 * sq(a_0) * am - 12.0 * a_0 * sq(am) - 12.0 * a_0 * jm * v_0 +
          12.0 * am * jm * v_0 + 4 * a_0 * am - 4 * sq(am);
-  root = smallest_positive_real_root(L, A, 5);
-  v_drive = sq(root) / jm;
-  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
-
-  // (5) standard profile, phases 2 and 6 do not exist (:526-541), degree 5
+      ncoef = 5;
+      break;
+    case 4:  // (5) standard profile, phases 2 and 6 do not exist (:526-541), degree 5
   A[0] = (144 * jm * tr + 144 * a_0);
   A[1] = (-72.0 * sq(jm) * sq(tr) - 144 * a_0 * jm * tr + 36 * sq(a_0) - 216 * jm * v_0);
   A[2] = (144 * dir * sq(jm) * q_0 - 144 * dir * sq(jm) * q_goal + 48 * cube(a_0) - 144 * a_0 * jm * v_0);
@@ -96,11 +88,9 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
          48 * cube(a_0) * dir * sq(jm) * q_goal + 144 * a_0 * dir * cube(jm) * q_0 * v_0 -
          144 * a_0 * dir * cube(jm) * q_goal * v_0 + pow6(a_0) - 6 * pow4(a_0) * jm * v_0 +
          36 * sq(a_0) * sq(jm) * sq(v_0) - 72.0 * cube(jm) * cube(v_0);
-  root = smallest_positive_real_root(L, A, 6);
-  v_drive = sq(root) / jm;
-  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
-
-  // (6) modified profile, phase 2 does not exist (:553-567)
+      ncoef = 6;
+      break;
+    case 5:  // (6) modified profile, phase 2 does not exist (:553-567)
   A[0] = 3;
   A[1] = -6 * sqrt(2.0) * am;
   A[2] = (12.0 * am * jm * tr - 6 * sq(a_0) - 12.0 * a_0 * am - 6 * sq(am) - 12.0 * jm * v_0);
@@ -108,11 +98,9 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
   A[4] = -12.0 * sq(a_0) * am * jm * tr - 24 * dir * sq(jm) * am * q_0 + 24 * dir * sq(jm) * am * q_goal -
          24 * am * sq(jm) * v_0 * tr + 3 * pow4(a_0) + 4 * cube(a_0) * am + 6 * sq(a_0) * sq(am) +
          12.0 * sq(a_0) * jm * v_0 + 12.0 * sq(am) * jm * v_0 + 12.0 * sq(jm) * sq(v_0);
-  root = smallest_positive_real_root(L, A, 5);
-  v_drive = -(sq(root) - sq(a_0) - 2.0 * jm * v_0) / (2.0 * jm);
-  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
-
-  // (7) modified profile, phase 6 does not exist (:579-593)
+      ncoef = 5;
+      break;
+    case 6:  // (7) modified profile, phase 6 does not exist (:579-593)
   A[0] = 12;
   A[1] = -24 * am;
   A[2] = (24 * am * jm * tr - 12.0 * sq(a_0) - 24 * a_0 * am - 12.0 * sq(am) - 24 * jm * v_0);
@@ -120,11 +108,9 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
   A[4] = 24 * dir * sq(jm) * am * q_0 - 24 * dir * sq(jm) * am * q_goal + 3 * pow4(a_0) + 8 * cube(a_0) * am +
          6 * sq(a_0) * sq(am) + 12.0 * sq(a_0) * jm * v_0 + 24 * a_0 * am * jm * v_0 + 12.0 * sq(am) * jm * v_0 +
          12.0 * sq(jm) * sq(v_0);
-  root = smallest_positive_real_root(L, A, 5);
-  v_drive = sq(root) / jm;
-  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
-
-  // (8) modified profile, phases 2 and 6 do not exist (:606-629), degree 6
+      ncoef = 5;
+      break;
+    default:  // (8) modified profile, phases 2 and 6 do not exist (:606-629), degree 6
   A[0] = 144;
   A[1] = (-144 * jm * tr + 144 * a_0);
   A[2] = (72.0 * sq(jm) * sq(tr) - 144 * a_0 * jm * tr - 36 * sq(a_0) - 216 * jm * v_0);
@@ -138,16 +124,83 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
          48 * cube(a_0) * dir * sq(jm) * q_goal + 144 * a_0 * dir * cube(jm) * q_0 * v_0 -
          144 * a_0 * dir * cube(jm) * q_goal * v_0 - pow6(a_0) - 6 * pow4(a_0) * jm * v_0 -
          36 * sq(a_0) * sq(jm) * sq(v_0) - 72.0 * cube(jm) * cube(v_0);
-  root = smallest_positive_real_root(L, A, 7);
-  v_drive = sq(root) / jm;
-  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
+      ncoef = 7;
+      break;
+  }
+  return v_drive;
+}
 
+// v_drive of candidate c >= 2 from its polynomial root (the line after each roots() call of the reference).
+HRG_HD double ltp_scaling_vdrive(const LtpLimits& L, int cand, double root, double v_0, double a_0) {
+  const double jm = L.j_max;
+  if (cand == 2) return (-2.0 * sq(a_0) + 4 * jm * v_0 + sq(root)) / (4 * jm);
+  if (cand == 5) return -(sq(root) - sq(a_0) - 2.0 * jm * v_0) / (2.0 * jm);
+  return sq(root) / jm;
+}
+
+// Sequential form: the candidates one after the other, first accepted wins (host tests, stage kernel).
+HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double dir,
+                                  double tr /*t_required*/, double* T /*scaled_t*/, double& v_drive,
+                                  int& mod_jerk_profile) {
+  if (dir < 0) {
+    v_0 = -v_0;
+    a_0 = -a_0;
+  }
+  const double v_orig = dir * v_0, a_orig = dir * a_0;  // what the reference passes on to optSwitchTimes
+  for (int cand = 0; cand < 8; ++cand) {
+    double A[7];
+    int ncoef;
+    v_drive = ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, dir, tr, A, ncoef);
+    if (ncoef) v_drive = ltp_scaling_vdrive(L, cand, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
+    if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
+  }
   // no valid solution (:640-644)
   mod_jerk_profile = 0;
   ltp_zero7(T);
   v_drive = L.v_max;
   return false;
 }
+
+#if defined(__CUDACC__)
+// Warp form for k_replan_scale: lane c < 8 evaluates candidate c. The candidates share all the expensive code (the
+// eigenvalue solve and the optSwitchTimes trial), so the eight lanes run it together and the time of a task is that of
+// its slowest candidate instead of the sum over the ladder; the first accepted candidate in the reference's order wins,
+// which is exactly what the sequential form returns. L.mat must point at this lane's own matrix scratch.
+// All 32 lanes must call; lanes >= 8 idle. Outputs are valid on every lane.
+__device__ __forceinline__ bool ltp_time_scaling_warp(const LtpLimits& L, int lane, double q_goal, double q_0, double v_0,
+                                                      double a_0, double dir, double tr, double* T, double& v_drive,
+                                                      int& mod_jerk_profile) {
+  if (dir < 0) {
+    v_0 = -v_0;
+    a_0 = -a_0;
+  }
+  const double v_orig = dir * v_0, a_orig = dir * a_0;
+  bool acc = false;
+  double Tc[7];
+  ltp_zero7(Tc);
+  double vd = L.v_max;
+  int mod = 0;
+  if (lane < 8) {
+    double A[7];
+    int ncoef;
+    vd = ltp_scaling_setup(L, lane, q_goal, q_0, v_0, a_0, dir, tr, A, ncoef);
+    if (ncoef) vd = ltp_scaling_vdrive(L, lane, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
+    acc = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, vd, tr, Tc, mod);
+  }
+  const unsigned won = __ballot_sync(0xffffffffu, acc);
+  if (won == 0u) {
+    mod_jerk_profile = 0;
+    ltp_zero7(T);
+    v_drive = L.v_max;
+    return false;
+  }
+  const int src = __ffs(won) - 1;
+  for (int k = 0; k < 7; ++k) T[k] = __shfl_sync(0xffffffffu, Tc[k], src);
+  v_drive = __shfl_sync(0xffffffffu, vd, src);
+  mod_jerk_profile = __shfl_sync(0xffffffffu, mod, src);
+  return true;
+}
+#endif
 
 }  // namespace hrg
 #include "ltp_traj.cuh"

@@ -117,45 +117,66 @@ HRG_HD double ltp_sample_joint(const LtpLimits& L, const JointPlan& P, double q_
 }
 
 #if defined(__CUDACC__)
-// Warp-cooperative form of ltp_sample_joint for the replan kernel: lane = joint gl + 8 * sub, every lane holds the plan of
-// its joint. Per group of four samples each sub-lane evaluates the jerk of sample 4c + sub (the expensive part: a
-// 7-way range test plus up to 10 corrections), the four values are exchanged by shuffle, and all sub-lanes run the
-// reference's sequential recurrence a += ts*j, v += ts*a, q += ts*v redundantly (identical roundings); sub-lane s then
-// stores component s of {q, v, a, j}, so one store instruction writes the whole [4][J] sample contiguously. The jerk
-// sampler of a joint (34 words, dynamically indexed) sits in shared memory, one copy per joint.
+// Warp-cooperative form of ltp_sample_joint for k_replan_sample: lane = joint gl + 8 * sub, every lane holds the plan
+// of joint `row` (= gl, or J-1 for the shadow lanes gl >= J). The trajectory is produced in chunks of 32 samples:
+//   1. all 32 lanes evaluate the piecewise-constant jerk fill (:759-766) of sample c0 + lane, joint after joint, into a
+//      [8][32] shared buffer (the 7-way range test is the expensive part of ltp_jerk_at and has no serial dependence);
+//   2. one lane per joint adds the sub-sample corrections (:767-807) that fall into the chunk, in program order;
+//   3. every lane runs the reference's sequential recurrence a += ts*j, v += ts*a, q += ts*v over the chunk (identical
+//      roundings); sub-lane s stores component s of {q, v, a, j}, so one store instruction writes a whole [4][J] sample.
 // `len` must be warp-uniform. Returns the final position (joint-limit test of :59-61).
 __device__ __forceinline__ double ltp_sample_joint_warp(const LtpLimits& L, const JointPlan& P, double q_0, double v_0,
                                                         double a_0, int len, double* traj /*[len][4][J]*/, int J, int gl,
-                                                        int sub, bool joint_lane, JerkSampler& S /*shared, per joint*/) {
-  if (sub == 0) ltp_sampler_init(L, P, S);
+                                                        int row, int sub, bool joint_lane,
+                                                        JerkSampler* samp /*[8] shared*/, double* jbuf /*[8][32] shared*/) {
+  const int lane = gl + 8 * sub;
+  if (sub == 0) ltp_sampler_init(L, P, samp[gl]);
   __syncwarp();
+  const JerkSampler& S = samp[row];
   const double ts = L.t_sample;
   const double v_cruise = P.v_drive * P.dir;
-  // loop invariants in registers (S is shared memory and the sample stores could alias it for the compiler)
   const int s6 = S.s[6];
   const int cr_lo = S.phase4 ? S.s[2] + 1 : 0x7fffffff, cr_hi = S.s[3] - 1;
-  double* out = traj + sub * J + gl;
-  const size_t stride = (size_t)4 * J;
+  const bool p1 = sub == 1, p2 = sub == 2, p3 = sub == 3;
+  double* o = traj + sub * J + gl;
+  const int stride = 4 * J;
   double a = a_0, v = v_0, q = q_0;
-  for (int c0 = 0; c0 < len; c0 += 4) {
-    const double mine = ltp_jerk_at(S, c0 + sub);
-    double jq[4];
+  for (int c0 = 0; c0 < len; c0 += 32) {
+    const int i_mine = c0 + lane;
+    for (int jj = 0; jj < J; ++jj) {
+      const JerkSampler& Q = samp[jj];
+      double j = 0.0;
+      if (i_mine < Q.s[0]) j = Q.jp[0];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) jq[u] = __shfl_sync(0xffffffffu, mine, gl + 8 * u);
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int i = c0 + u;
-      if (i < len) {
-        const double jj = jq[u];
-        const bool first = i == 0, live = first || i <= s6;
-        const double an = a + ts * jj;
-        a = live ? an : 0.0;
-        const double vn = v + ts * a;
-        v = (!first && i >= cr_lo && i < cr_hi) ? v_cruise : (live ? vn : 0.0);
-        q = q + ts * v;
-        if (joint_lane) out[(size_t)i * stride] = sub == 0 ? q : (sub == 1 ? v : (sub == 2 ? a : jj));
-      }
+      for (int k = 1; k < 7; ++k)
+        if (i_mine >= Q.s[k - 1] && i_mine < Q.s[k]) j = Q.jp[k];
+      jbuf[jj * 32 + lane] = j;
     }
+    __syncwarp();
+    if (sub == 0 && joint_lane)
+      for (int k = 0; k < S.nc; ++k) {
+        const int d = S.cidx[k] - c0;
+        if (d >= 0 && d < 32) jbuf[gl * 32 + d] = jbuf[gl * 32 + d] + S.cval[k];
+      }
+    __syncwarp();
+    const int n = (len - c0) < 32 ? (len - c0) : 32;
+    for (int u = 0; u < n; ++u) {
+      const int i = c0 + u;
+      const double jj = jbuf[row * 32 + u];
+      const bool first = i == 0, live = first || i <= s6;
+      const double an = a + ts * jj;
+      a = live ? an : 0.0;
+      const double vn = v + ts * a;
+      v = (!first && i >= cr_lo && i < cr_hi) ? v_cruise : (live ? vn : 0.0);
+      q = q + ts * v;
+      double val = q;
+      val = p1 ? v : val;
+      val = p2 ? a : val;
+      val = p3 ? jj : val;
+      if (joint_lane) *o = val;
+      o += stride;
+    }
+    __syncwarp();
   }
   return q;
 }

@@ -33,6 +33,17 @@ enum : uint32_t {
 
 enum { P_REC = 0, P_FS = 1, P_FS2 = 2, P_SAFE = 3, N_PATHS = 4, PATH_FIELDS = 10 };
 
+// Hand-over records between the three replan kernels, indexed by position on the replan list.
+struct PlanRec {   // one joint: cumulative jerk switch times, direction, cruise velocity, profile flag, samples needed
+  double T[7];
+  double dir, v_drive;
+  int32_t mod, len;
+};
+struct PlanHead {  // one env: time of the slowest joint, its index, and whether every joint passed checkInputs/optSwitchTimes
+  double t_required;
+  int32_t slowest, ok;
+};
+
 struct DevState {
   int N, J, K, H, L;  // envs, joints, keypoints, human capsules, LTT capacity (samples per slot)
   const HrgConfig* cfg;
@@ -63,7 +74,12 @@ struct DevState {
   double* min_dist;   // [3][N]
   int32_t* replan_list;   // [N]
   int32_t* replan_count;  // [1]
-  int32_t* replan_next;   // [1] work counter of k_replan (one env per fetch)
+  int32_t* replan_ctr;    // [4] work counters of the replan kernels + length of the deep list (kernels_tick.cuh CTR_*)
+  PlanRec* plan_opt;      // [N][HRG_MAX_JOINTS] time-optimal plan per joint (k_replan_opt); len = optSwitchTimes ok
+  PlanRec* plan_sc;       // [N][HRG_MAX_JOINTS] plan scaled to the slowest joint; len < 0 = -(deep slot + 1)
+  PlanHead* plan_head;    // [N]
+  int32_t* deep_list;     // [N * J] (env, joint) tasks whose closed-form timeScaling candidates were rejected
+  PlanRec* deep_res;      // [N * J][6] result of each polynomial candidate; len = accepted
   uint8_t* replan_mark;   // [N] 1 = this tick's reach + verify of the env runs after k_replan (second pass)
   // optional per-step capsule dump (drop-in getters); NULL = not stored
   double* robot_caps;  // [N][J][7]
