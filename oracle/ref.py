@@ -44,6 +44,9 @@ def lib():
         L.ref_ltp_opt_braking.argtypes = [C.c_double, _dp, C.c_double, C.c_double, _dp, _dp, _dp]
         L.ref_ltp_opt_switch_times.argtypes = [C.c_double, _dp] + [C.c_double] * 5 + [_dp, _dp, C.POINTER(C.c_int)]
         L.ref_ltp_time_scaling.argtypes = [C.c_double, _dp] + [C.c_double] * 6 + [_dp, _dp, C.POINTER(C.c_int)]
+        L.ref_ltt_interpolate.argtypes = [C.c_int, C.c_int, _dp, C.c_double, C.c_int, C.c_int, _dp, _dp, _dp, _dp, _dp]
+        L.ref_human_reach.restype = C.c_int
+        L.ref_human_reach.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, _dp, C.c_int]
         L.ref_poly_roots.restype = C.c_double
         L.ref_poly_roots.argtypes = [C.c_int, _dp, _dp, _dp]
         _lib = L
@@ -127,6 +130,12 @@ class RefBatch:
         lib().ref_get_state(self.h, int(i), _d(out))
         return out
 
+    def human_reach(self, i, t_command, t_brake, max_caps=128):
+        """HumanReach::humanReachabilityAnalysis of env i -> capsules [H,7] ordered Pos, Vel, Accel."""
+        out = np.zeros((max_caps, 7))
+        n = lib().ref_human_reach(self.h, int(i), float(t_command), float(t_brake), _d(out), max_caps)
+        return out[:n]
+
     def plan_safety_shield(self, cases):
         cases = _f64(cases).reshape(-1, 6)
         n = cases.shape[0]
@@ -178,3 +187,14 @@ def ltp_time_scaling(ts, lim, q_goal, q0, v0, a0, direction, t_required):
     ok = lib().ref_ltp_time_scaling(float(ts), _d(lim), float(q_goal), float(q0), float(v0), float(a0), float(direction),
                                     float(t_required), _d(t), _d(vd), C.byref(m))
     return bool(ok), t, vd[0], m.value
+
+
+def ltt_interpolate(traj, sample_time, sdd, v_max, a_max, j_max, starting_index=0):
+    """LongTermTraj::interpolate on traj [L,4,J] at the rows of sdd [n,4] = (s, ds, dds, ddds) -> [n,4,J]."""
+    traj = _f64(traj)
+    L, _, J = traj.shape
+    sdd = _f64(sdd).reshape(-1, 4)
+    out = np.zeros((sdd.shape[0], 4, J))
+    lib().ref_ltt_interpolate(J, L, _d(traj), float(sample_time), int(starting_index), sdd.shape[0], _d(sdd),
+                              _d(_f64(v_max)), _d(_f64(a_max)), _d(_f64(j_max)), _d(out))
+    return out

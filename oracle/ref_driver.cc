@@ -260,6 +260,39 @@ int ref_ltp_time_scaling(double ts, const double* lim, double q_goal, double q0,
   return ok ? 1 : 0;
 }
 
+// LongTermTraj::interpolate (SS/src/long_term_traj.cc:41-77) on a caller-supplied trajectory [L][4][J].
+void ref_ltt_interpolate(int J, int L, const double* traj, double sample_time, int starting_index, int n,
+                         const double* sdd /*[n,4]: s ds dds ddds*/, const double* v_max, const double* a_max,
+                         const double* j_max, double* out /*[n,4,J]*/) {
+  std::vector<Motion> ms;
+  for (int i = 0; i < L; ++i) {
+    const double* p = traj + static_cast<size_t>(i) * 4 * J;
+    ms.emplace_back(i * sample_time, std::vector<double>(p, p + J), std::vector<double>(p + J, p + 2 * J),
+                    std::vector<double>(p + 2 * J, p + 3 * J), std::vector<double>(p + 3 * J, p + 4 * J));
+  }
+  safety_shield::LongTermTraj ltt(ms, sample_time, starting_index);
+  std::vector<double> vm(v_max, v_max + J), am(a_max, a_max + J), jm(j_max, j_max + J);
+  for (int k = 0; k < n; ++k) {
+    Motion m = ltt.interpolate(sdd[4 * k], sdd[4 * k + 1], sdd[4 * k + 2], sdd[4 * k + 3], vm, am, jm);
+    double* o = out + static_cast<size_t>(k) * 4 * J;
+    for (int j = 0; j < J; ++j) {
+      o[j] = m.q_[j]; o[J + j] = m.dq_[j]; o[2 * J + j] = m.ddq_[j]; o[3 * J + j] = m.dddq_[j];
+    }
+  }
+}
+
+// HumanReach::humanReachabilityAnalysis (SS/src/human_reach.cc:76-87) of env i on its stored measurement; returns the
+// number of capsules written as Pos, Vel, Accel (7 doubles each).
+int ref_human_reach(void* h, int i, double t_command, double t_brake, double* out, int max_caps) {
+  SafetyShield& s = *static_cast<RefBatch*>(h)->env[i];
+  s.human_reach_->humanReachabilityAnalysis(t_command, t_brake);
+  int k = 0;
+  for (auto& set : s.human_reach_->getAllCapsules())
+    for (auto& c : set)
+      if (k < max_caps) put_capsule(c, out + 7 * k++);
+  return k;
+}
+
 // roots() + getSmallestPositiveNonComplexRoot (LTP/include/long_term_planner/roots.h:22-50)
 double ref_poly_roots(int ncoef, const double* coef, double* re, double* im) {
   Eigen::VectorXd pv(ncoef);

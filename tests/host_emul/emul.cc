@@ -289,4 +289,48 @@ int emul_ltp_plan(const HrgConfig* cfg, const double* goal, const double* q0, co
   return ltp_plan_env_seq(*cfg, goal, q0, v0, a0, traj, cap);
 }
 double emul_poly_root(const double* coef, int ncoef) { LtpLimits L{}; return smallest_positive_real_root(L, coef, ncoef); }
+
+// ---- single-function entry points for the golden-vector tests -------------------------------------------------------
+static LtpLimits lim1(double ts, const double* lim) {
+  LtpLimits L{};
+  L.v_max = lim[2]; L.a_max = lim[3]; L.j_max = lim[4]; L.t_sample = ts;
+  return L;
+}
+void emul_ltp_opt_braking(double ts, const double* lim, double v0, double a0, double* q, double* t_rel, double* dir) {
+  LtpLimits L = lim1(ts, lim);
+  for (int i = 0; i < 7; ++i) t_rel[i] = 0.0;
+  ltp_opt_braking(L, v0, a0, *q, t_rel, *dir);
+}
+int emul_ltp_opt_switch_times(double ts, const double* lim, double q_goal, double q0, double v0, double a0, double v_drive,
+                              double* T, double* dir, int* mod) {
+  LtpLimits L = lim1(ts, lim);
+  for (int i = 0; i < 7; ++i) T[i] = 0.0;
+  return ltp_opt_switch_times(L, q_goal, q0, v0, a0, v_drive, T, *dir, *mod) ? 1 : 0;
+}
+int emul_ltp_time_scaling(double ts, const double* lim, double q_goal, double q0, double v0, double a0, double dir,
+                          double t_required, double* T, double* v_drive, int* mod) {
+  LtpLimits L = lim1(ts, lim);
+  for (int i = 0; i < 7; ++i) T[i] = 0.0;
+  return ltp_time_scaling(L, q_goal, q0, v0, a0, dir, t_required, T, *v_drive, *mod) ? 1 : 0;
+}
+// LongTermTraj::interpolate on traj [L][4][J] (current_pos = 0)
+void emul_ltt_interpolate(int J, int L, const double* traj, double sample_time, int starting_index, int n,
+                          const double* sdd, const double* v_max, const double* a_max, double* out) {
+  for (int k = 0; k < n; ++k) {
+    int sample;
+    double dt;
+    ltt_locate(sdd[4 * k], sample_time, starting_index, L, 0, sample, dt);
+    const double* m = traj + (size_t)sample * 4 * J;
+    double* o = out + (size_t)k * 4 * J;
+    for (int j = 0; j < J; ++j)
+      ltt_interp_joint(m[j], m[J + j], m[2 * J + j], m[3 * J + j], dt, sdd[4 * k + 1], sdd[4 * k + 2], sdd[4 * k + 3],
+                       v_max[j], a_max[j], o[j], o[J + j], o[2 * J + j], o[3 * J + j]);
+  }
+}
+// all human capsules (Pos, Vel, Accel) of one env from contiguous keypoints / velocities [K*3]
+int emul_human_capsules(const HrgConfig* cfg, const double* kp, const double* kv, double t_reach, double* out) {
+  const int H = cfg->n_ext + 2 * cfg->n_bodies;
+  for (int h = 0; h < H; ++h) cap_store(human_capsule(*cfg, h, kp, kv, 1, t_reach), out + 7 * h);
+  return H;
+}
 }

@@ -33,6 +33,12 @@ def lib():
         L.emul_plan_safety_shield.argtypes = [C.c_double, C.c_int, _p, _p, _p, _p]
         L.emul_ltp_plan.restype = C.c_int
         L.emul_ltp_plan.argtypes = [C.POINTER(HrgConfig), _p, _p, _p, _p, _p, C.c_int]
+        D = C.c_double
+        L.emul_ltp_opt_braking.argtypes = [D, _p, D, D, _p, _p, _p]
+        L.emul_ltp_opt_switch_times.argtypes = [D, _p, D, D, D, D, D, _p, _p, _p]
+        L.emul_ltp_time_scaling.argtypes = [D, _p, D, D, D, D, D, D, _p, _p, _p]
+        L.emul_ltt_interpolate.argtypes = [C.c_int, C.c_int, _p, D, C.c_int, C.c_int, _p, _p, _p, _p]
+        L.emul_human_capsules.argtypes = [C.POINTER(HrgConfig), _p, _p, D, _p]
         L.emul_poly_root.restype = C.c_double
         L.emul_poly_root.argtypes = [_p, C.c_int]
         _lib = L
@@ -125,3 +131,38 @@ def ltp_plan(cfg, goal, q0, v0, a0, cap=4096):
 def poly_root(coef):
     c = _a(coef)
     return lib().emul_poly_root(_ptr(c), c.shape[0])
+
+
+def ltp_opt_braking(ts, lim, v0, a0):
+    lim, t, q, d = _a(lim), np.zeros(7), np.zeros(1), np.zeros(1)
+    lib().emul_ltp_opt_braking(ts, _ptr(lim), v0, a0, _ptr(q), _ptr(t), _ptr(d))
+    return True, q[0], t, d[0]
+
+
+def ltp_opt_switch_times(ts, lim, q_goal, q0, v0, a0, v_drive):
+    lim, t, d, m = _a(lim), np.zeros(7), np.zeros(1), np.zeros(1, np.int32)
+    ok = lib().emul_ltp_opt_switch_times(ts, _ptr(lim), q_goal, q0, v0, a0, v_drive, _ptr(t), _ptr(d), _ptr(m))
+    return bool(ok), t, d[0], int(m[0])
+
+
+def ltp_time_scaling(ts, lim, q_goal, q0, v0, a0, direction, t_required):
+    lim, t, vd, m = _a(lim), np.zeros(7), np.zeros(1), np.zeros(1, np.int32)
+    ok = lib().emul_ltp_time_scaling(ts, _ptr(lim), q_goal, q0, v0, a0, direction, t_required, _ptr(t), _ptr(vd), _ptr(m))
+    return bool(ok), t, vd[0], int(m[0])
+
+
+def ltt_interpolate(traj, sample_time, sdd, v_max, a_max, j_max=None, starting_index=0):
+    traj = _a(traj)
+    L, _, J = traj.shape
+    sdd = _a(sdd).reshape(-1, 4)
+    out = np.zeros((sdd.shape[0], 4, J))
+    lib().emul_ltt_interpolate(J, L, _ptr(traj), sample_time, starting_index, sdd.shape[0], _ptr(sdd), _ptr(_a(v_max)),
+                               _ptr(_a(a_max)), _ptr(out))
+    return out
+
+
+def human_capsules(cfg, kp, kv, t_reach):
+    H = cfg.n_ext + 2 * cfg.n_bodies
+    out = np.zeros((H, 7))
+    lib().emul_human_capsules(C.byref(cfg), _ptr(_a(kp)), _ptr(_a(kv)), t_reach, _ptr(out))
+    return out
