@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--seed", type=int, default=1003)
+    ap.add_argument("--chunks", type=int, default=1, help="env blocks of the pipelined host-buffer tick (e2e leg)")
     return ap.parse_args()
 
 
@@ -246,12 +247,10 @@ def main():
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
     # verify statistics of the timed region: the one collective of the path (SUM of counts, MIN of min_dist)
-    st = shield.stats_tensor().clone()
-    counts, mind = st[:9].clone(), st[9:10].view(torch.float64).clone()
-    if world > 1:
-        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
-        dist.all_reduce(mind, op=dist.ReduceOp.MIN)
-    counts = counts.cpu().tolist()
+    from human_robot_gym_b200.sharded import reduce_stats
+    gs = reduce_stats(shield.stats_tensor().clone())
+    counts = [gs["n_steps"], gs["n_unsafe"]] + gs["n_branch"] + [gs["n_replan"], gs["n_replan_failed"],
+                                                                  gs["n_near_threshold"], gs["ltt_len_sum"]]
 
     # ---- per-kernel device time (separate pass so the events do not perturb `value`) ---------------------------
     shield.profile(S)
@@ -262,9 +261,17 @@ def main():
     shield.profile(0)
 
     # ---- end to end through the C ABI with HOST buffers -----------------------------------------------------------
+    # The call a vectorised env makes: pinned host keypoints/goals in, pinned host setpoints out, every tick. The batch
+    # is cut into env blocks on separate streams so the copies of one block overlap the kernels of another.
     e2e = None
     if not args.no_e2e:
+        from human_robot_gym_b200.batched import PipelinedHostShield
+        shield.close()
+        del shield
+        torch.cuda.empty_cache()
         pin = dict(pin_memory=True)
+        hs = PipelinedHostShield(N, SAMPLE_TIME, *files, init_qpos=scen.init_q, device=dev, chunks=args.chunks,
+                                 ltt_capacity=args.ltt_capacity, config=sc)
         kp_p = torch.from_numpy(kp_h).pin_memory()
         goals_p = torch.from_numpy(goals_h).pin_memory()
         masks_p = torch.from_numpy(masks_h).pin_memory()
@@ -274,40 +281,59 @@ def main():
 
         def tick_host(kk):
             t_p.fill_(kk * SAMPLE_TIME)
-            shield.tick_host(kp_p[ring_index(kk, args.ring)], t_p, masks_p[kk % GOAL_PERIOD],
-                             goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], q_p, dq_p, ddq_p, fl_p)
-            torch.cuda.current_stream(dev).synchronize()  # the caller consumes the setpoints before the next tick
+            hs.tick_host(kp_p[ring_index(kk, args.ring)], t_p, masks_p[kk % GOAL_PERIOD],
+                         goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], q_p, dq_p, ddq_p, fl_p)
+            hs.synchronize()  # the caller consumes the setpoints before the next tick
 
-        for _ in range(max(3, min(W, 10))):
-            tick_host(k)
-            k += 1
+        ke = 0
+        for _ in range(max(W, 2 * GOAL_PERIOD)):  # fresh shields: run past the first policy periods before timing
+            tick_host(ke)
+            ke += 1
         sync_all()
+        l0 = hs.launch_count()
         t0 = time.perf_counter()
-        e0.record()
         for _ in range(S):
-            tick_host(k)
-            k += 1
-        e1.record()
+            tick_host(ke)
+            ke += 1
         sync_all()
-        ms_e = torch.tensor([max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)], dtype=torch.float64, device=dev)
+        ms_e = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(ms_e, op=dist.ReduceOp.MAX)
+        checksum = float(q_p.sum().item()) + float(fl_p.sum().item())  # the result was really read back
         e2e = {"value": N * world * S / (float(ms_e.item()) / 1e3), "unit": METRIC,
                "h2d_bytes_per_step": N * (K * 3 * 8 + 8 + 1 + J * 8), "d2h_bytes_per_step": N * (3 * J * 8 + 1),
-               "ms_per_step": float(ms_e.item()) / S}
+               "ms_per_step": float(ms_e.item()) / S, "env_blocks": len(hs.parts), "gpu_launches": hs.launch_count() - l0,
+               "timer": "host wall clock around the synchronous calls (every tick ends in a stream sync)",
+               "checksum": checksum}
+        hs.close()
+        shield = None
 
     if rank == 0:
         peak, peak_src = peaks()
         H = sc.human.n_capsules
-        # algorithmic bytes per env of the dominant kernel (fused K1+K2+K3): reads keypoint positions
-        # and velocities 48K, start/goal angles + alpha 24J, s_diff + t_reach 16; writes is_safe 1 + min_dist 24
-        b_reach = 48 * K + 24 * J + 41
-        dom = max(kms, key=kms.get)
-        dom_ms = kms[dom] / max(ksteps, 1)
-        alg = {"k_reach_verify": b_reach}.get(dom, b_reach)
-        achieved = alg * N / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
         n_ok = max(1, counts[5] - counts[6])
         L_mean = counts[8] / n_ok
+        replans_per_step = counts[5] / max(1, S) / world
+        # ALGORITHMIC bytes per launch group (FP64 state, nothing recomputable counted):
+        #   k_pre_plan      3 paths in/out 480, scalars/flags 40, prev dq 8J, 2 LTT samples 64J; writes the current motion
+        #                   32J+8 and the reach inputs 24J+16
+        #   k_replan_*      per REPLANNING env: the new LTT 32*J*L plus goal/current state 40J
+        #   k_reach_verify  keypoint positions + velocities 48K, reach inputs 24J+16, base pose 96, flags 8; writes 24+4
+        #   k_select        3 paths in 240, one out 80, one LTT sample 32J, outputs 32J, prev dq 8J, flags 16
+        alg_bytes = {
+            "k_pre_plan": N * (544 + 128 * J),
+            "k_replan": replans_per_step * (32 * J * L_mean + 40 * J),
+            "k_reach_verify": N * (48 * K + 24 * J + 148),
+            "k_select": N * (336 + 72 * J),
+        }
+        dom = max(kms, key=kms.get)
+        dom_ms = kms[dom] / max(ksteps, 1)
+        alg = alg_bytes[dom]
+        achieved = alg / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
+        per_kernel = {kk: {"ms": kms[kk] / max(ksteps, 1), "algorithmic_bytes": alg_bytes[kk],
+                           "GBps": alg_bytes[kk] / (kms[kk] / max(ksteps, 1) / 1e3) / 1e9 if kms[kk] > 0 else 0.0,
+                           "frac_of_hbm_peak": alg_bytes[kk] / (kms[kk] / max(ksteps, 1) / 1e3) / 1e9 / peak
+                           if kms[kk] > 0 else 0.0} for kk in kms}
         b_tick = 48 * K + 770 + 136 * J
         b_step = b_tick + (32 * J * L_mean + 16 * J) / GOAL_PERIOD
         value = N * world * S / (ms_total / 1e3)
@@ -321,13 +347,17 @@ def main():
                        "ltt_capacity": args.ltt_capacity, "mean_ltt_len": L_mean},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic_per_launch(dom), "peak_source": peak_src,
-                         "algorithmic_bytes_per_env": alg, "kernel_ms": dom_ms},
+                         "algorithmic_bytes_per_launch": alg, "kernel_ms": dom_ms,
+                         "note": "k_replan = the four k_replan_* launches of one tick, timed serially (in the timed "
+                                 "region they overlap k_reach_verify pass 0 on a second stream); latency bound, see "
+                                 "profiles/"},
             "kernel_ms_per_step": {kk: v / max(ksteps, 1) for kk, v in kms.items()},
+            "roofline_per_kernel": per_kernel,
             "roofline_tick": {"algorithmic_bytes_per_step": b_step, "achieved": b_step * N / (ms_total / S / 1e3) / 1e9,
                               "unit": "GB/s", "frac": b_step * N / (ms_total / S / 1e3) / 1e9 / peak},
             "verify_stats": {"n_steps": counts[0], "unsafe_frac": counts[1] / max(1, counts[0]),
                              "branch_hist": counts[2:5], "n_replan": counts[5], "n_replan_failed": counts[6],
-                             "n_near_threshold": counts[7], "min_dist": float(mind.item())},
+                             "n_near_threshold": counts[7], "min_dist": gs["min_dist"]},
             "clocks": clk, "gpu_launches": int(launches),
         }
         if e2e:
@@ -337,7 +367,8 @@ def main():
             cb, _, _ = cpu_loop(args, files, sc, names, min(args.cpu_envs, N), 25, 100, threads)
             line["cpu_baseline"] = cb
         print(json.dumps(line), flush=True)
-    shield.close()
+    if shield is not None:
+        shield.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

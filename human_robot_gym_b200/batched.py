@@ -187,3 +187,74 @@ class BatchedSafetyShield:
         cabi.check(self.lib.hrg_shield_tick_host(self._h, kp_host.data_ptr(), t_host.data_ptr(), _ptr(goal_mask_host),
                                                  _ptr(goal_q_host), _ptr(q_host), _ptr(dq_host), _ptr(ddq_host),
                                                  _ptr(flags_host), self._stream()), "hrg_shield_tick_host")
+
+
+class PipelinedHostShield:
+    """Host-buffer front end: the batch is cut into `chunks` independent env blocks, each a BatchedSafetyShield with its
+    own CUDA stream, so that inside ONE tick the host->device copy of block i+1, the kernels of block i and the
+    device->host copy of block i-1 overlap (separate copy engines + SMs). Envs are independent, so the result is
+    identical to one big batch. This is what a vectorised env with host-resident (MuJoCo) state calls once per tick:
+
+        shield.tick_host(kp, t, goal_mask, goal_q, q_out, dq_out, ddq_out, flags_out); shield.synchronize()
+
+    All arguments are pinned host tensors over the WHOLE batch ([N, K, 3], [N], [N] u8, [N, J], 3 x [N, J], [N] u8).
+    """
+
+    def __init__(self, n_envs: int, sample_time: float, trajectory_config_file: str, robot_config_file: str,
+                 mocap_config_file: str, base_pose=None, init_qpos=None, shield_type=cabi.SHIELD_SSM, device=None,
+                 chunks: int = 4, **kw):
+        from .sharded import shard_range
+        self.n_envs = int(n_envs)
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.bounds = [shard_range(self.n_envs, c, chunks) for c in range(chunks) if shard_range(self.n_envs, c, chunks)[1] >
+                       shard_range(self.n_envs, c, chunks)[0]]
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in self.bounds]
+
+        def rows(x, lo, hi):
+            if x is None:
+                return None
+            x = np.asarray(x)
+            return x[lo:hi] if x.ndim == 2 else x
+        ty = np.broadcast_to(np.asarray(shield_type, np.int32), (self.n_envs,))
+        self.parts = [BatchedSafetyShield(hi - lo, sample_time, trajectory_config_file, robot_config_file,
+                                          mocap_config_file, base_pose=rows(base_pose, lo, hi),
+                                          init_qpos=rows(init_qpos, lo, hi), shield_type=ty[lo:hi], device=self.device, **kw)
+                      for lo, hi in self.bounds]
+        self.J, self.K = self.parts[0].J, self.parts[0].K
+
+    def tick_host(self, kp_host, t_host, goal_mask_host, goal_q_host, q_host, dq_host, ddq_host, flags_host):
+        for (lo, hi), st, p in zip(self.bounds, self.streams, self.parts):
+            cabi.check(p.lib.hrg_shield_tick_host(
+                p._h, kp_host[lo:hi].data_ptr(), t_host[lo:hi].data_ptr(),
+                None if goal_mask_host is None else goal_mask_host[lo:hi].data_ptr(),
+                None if goal_q_host is None else goal_q_host[lo:hi].data_ptr(),
+                _ptr(None if q_host is None else q_host[lo:hi]), _ptr(None if dq_host is None else dq_host[lo:hi]),
+                _ptr(None if ddq_host is None else ddq_host[lo:hi]),
+                _ptr(None if flags_host is None else flags_host[lo:hi]), st.cuda_stream), "hrg_shield_tick_host")
+
+    def synchronize(self):
+        for st in self.streams:
+            st.synchronize()
+
+    def launch_count(self) -> int:
+        return sum(p.launch_count() for p in self.parts)
+
+    def stats(self, clear=False) -> dict:
+        out = None
+        for p in self.parts:
+            s = p.stats(clear=clear)
+            if out is None:
+                out = s
+            else:
+                for k, v in s.items():
+                    if k == "min_dist":
+                        out[k] = min(out[k], v)
+                    elif k == "n_branch":
+                        out[k] = [a + b for a, b in zip(out[k], v)]
+                    else:
+                        out[k] += v
+        return out
+
+    def close(self):
+        for p in self.parts:
+            p.close()

@@ -133,6 +133,12 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   h->pfl = false;
   if (shield_type_host)
     for (size_t i = 0; i < N; ++i) h->pfl |= (shield_type_host[i] == HRG_SHIELD_PFL);
+  if (h->pfl) {
+    // PFL needs the per-sample Cartesian capsule velocities of every planned LTT (long_term_traj.cc:5-39,
+    // robot_reach.cc:110-199); that constructor is not built yet, and a silently wrong v_limit is worse than a refusal
+    delete h;
+    return fail(HRG_EINVAL, "ShieldType PFL is not supported yet (SSM and OFF are)");
+  }
   HrgConfig* dcfg = nullptr;
 #define AL(ptr, count)                         \
   do {                                         \
