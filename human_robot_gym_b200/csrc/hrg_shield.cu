@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -72,6 +73,7 @@ struct HrgShield {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool overlap = true;
+  int replan_blocks_per_sm = 12;  // resident 64-thread replan blocks per SM while overlapped with k_reach_verify pass 0 (measured best)
   // optional per-kernel timing of hrg_shield_step (bench.py's roofline leg): 5 boundary events per step
   bool prof = false;
   std::vector<cudaEvent_t> ev;
@@ -203,7 +205,13 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   h->measure_smem = (size_t)kTileEnvs * ((K * 3) | 1) * sizeof(double);
   cudaFuncSetAttribute(k_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
   cudaFuncSetAttribute(k_measure, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->measure_smem);
-  ce = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
+  {
+    int lo = 0, hi = 0;  // the replan chain is the critical path of the tick: highest priority for its blocks
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    ce = cudaStreamCreateWithPriority(&h->side, cudaStreamNonBlocking, hi);
+    if (const char* v = getenv("HRG_REPLAN_BLOCKS_PER_SM")) h->replan_blocks_per_sm = atoi(v) > 0 ? atoi(v) : 12;
+    if (const char* v = getenv("HRG_NO_OVERLAP")) h->overlap = !(atoi(v) > 0);
+  }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaMemcpy(dcfg, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice);
@@ -310,7 +318,8 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
     // the replan list length is only known on the device: grids cover the worst case (every env replans) and surplus
     // groups / warps leave at once; k_replan_scale fetches (env, joint) tasks from a counter, its grid only bounds residency
     int sgrid = grid_for(N * s->S.J, kReplanBlock / 32);
-    if (sgrid > s->sm_count * HRG_REPLAN_MINBLOCKS) sgrid = s->sm_count * HRG_REPLAN_MINBLOCKS;
+    const int per_sm = fork ? s->replan_blocks_per_sm : HRG_REPLAN_MINBLOCKS;
+    if (sgrid > s->sm_count * per_sm) sgrid = s->sm_count * per_sm;
     k_replan_opt<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     k_replan_scale<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     k_replan_deep<<<sgrid, kReplanBlock, 0, rs>>>(s->S);

@@ -57,10 +57,27 @@ constexpr int kReplanBlock = 64;
 // the first three kernels: more lanes would only serialise. profiles/r01_ncu_summary.md has the measurements.
 enum { CTR_OPT = 0, CTR_SCALE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, N_CTR = 4 };
 
-__device__ __forceinline__ int fetch_task(int32_t* ctr, int lane) {
-  int task = 0;
-  if (lane == 0) task = atomicAdd(ctr, 1);
-  return __shfl_sync(0xffffffffu, task, 0);
+// Lanes per warp that carry a task in the three planning kernels. 1 = one problem per warp (shortest chains, but every
+// warp instruction is fetched for a single lane and the kernels become instruction-fetch bound); larger = several
+// independent problems share a warp and the instructions they have in common, at the price of serialising where they
+// diverge. Measured on B200 (profiles/r01_replan_packing.md).
+#ifndef HRG_G_OPT
+#define HRG_G_OPT 16
+#endif
+#ifndef HRG_G_SCALE
+#define HRG_G_SCALE 8
+#endif
+#ifndef HRG_G_DEEP
+#define HRG_G_DEEP 3
+#endif
+
+// Fetches G consecutive tasks for the warp; lane l < G gets task base + l (or >= ntask when the list is exhausted).
+template <int G>
+__device__ __forceinline__ int fetch_tasks(int32_t* ctr, int lane) {
+  int base = 0;
+  if (lane == 0) base = atomicAdd(ctr, G);
+  base = __shfl_sync(0xffffffffu, base, 0);
+  return base + (lane < G ? lane : 0);
 }
 __device__ __forceinline__ LtpLimits joint_limits(const HrgConfig& c, int j, double* mat) {
   LtpLimits L;
@@ -70,18 +87,18 @@ __device__ __forceinline__ LtpLimits joint_limits(const HrgConfig& c, int j, dou
 }
 
 __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_opt(DevState S) {
-  __shared__ double mat_s[kReplanBlock / 32][36];
+  __shared__ double mat_s[kReplanBlock / 32][HRG_G_OPT][37];
   const HrgConfig& c = *S.cfg;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int J = S.J, N = S.N;
   const int ntask = *S.replan_count * J;
   for (;;) {
-    const int task = fetch_task(S.replan_ctr + CTR_OPT, lane);
-    if (task >= ntask) break;
-    if (lane != 0) continue;
+    const int task = fetch_tasks<HRG_G_OPT>(S.replan_ctr + CTR_OPT, lane);
+    if (__shfl_sync(0xffffffffu, task, 0) >= ntask) break;
+    if (lane >= HRG_G_OPT || task >= ntask) continue;
     const int idx = task / J, j = task - idx * J;
     const int e = S.replan_list[idx];
-    const LtpLimits L = joint_limits(c, j, mat_s[wib]);
+    const LtpLimits L = joint_limits(c, j, mat_s[wib][lane]);
     const double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
     const double q_goal = S.goal_q[(size_t)j * N + e];
     PlanRec rec;
@@ -116,9 +133,9 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_s
   const int J = S.J, N = S.N;
   const int ntask = *S.replan_count * J;
   for (;;) {
-    const int task = fetch_task(S.replan_ctr + CTR_SCALE, lane);
-    if (task >= ntask) break;
-    if (lane != 0) continue;
+    const int task = fetch_tasks<HRG_G_SCALE>(S.replan_ctr + CTR_SCALE, lane);
+    if (__shfl_sync(0xffffffffu, task, 0) >= ntask) break;
+    if (lane >= HRG_G_SCALE || task >= ntask) continue;
     const int idx = task / J, j = task - idx * J;
     const PlanRec* opts = S.plan_opt + (size_t)idx * HRG_MAX_JOINTS;
     // slowest joint (:39-45)
@@ -177,22 +194,22 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_s
 }
 
 __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_deep(DevState S) {
-  __shared__ double mat_s[kReplanBlock / 32][36];
+  __shared__ double mat_s[kReplanBlock / 32][HRG_G_DEEP][37];
   const HrgConfig& c = *S.cfg;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int J = S.J, N = S.N;
   const int ntask = S.replan_ctr[CTR_DEEP_COUNT] * 6;
   for (;;) {
-    const int dt = fetch_task(S.replan_ctr + CTR_DEEP, lane);
-    if (dt >= ntask) break;
-    if (lane != 0) continue;
+    const int dt = fetch_tasks<HRG_G_DEEP>(S.replan_ctr + CTR_DEEP, lane);
+    if (__shfl_sync(0xffffffffu, dt, 0) >= ntask) break;
+    if (lane >= HRG_G_DEEP || dt >= ntask) continue;
     const int slot = dt / 6, cand = 2 + (dt - slot * 6);
     const int task = S.deep_list[slot];
     const int idx = task / J, j = task - idx * J;
     const int e = S.replan_list[idx];
     const PlanHead h = S.plan_head[idx];
     const PlanRec opt = S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j];
-    const LtpLimits L = joint_limits(c, j, mat_s[wib]);
+    const LtpLimits L = joint_limits(c, j, mat_s[wib][lane]);
     double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
     const double q_goal = S.goal_q[(size_t)j * N + e];
     if (opt.dir < 0) {

@@ -136,10 +136,14 @@ __device__ __forceinline__ double ltp_sample_joint_warp(const LtpLimits& L, cons
   const double ts = L.t_sample;
   const double v_cruise = P.v_drive * P.dir;
   const int s6 = S.s[6];
-  const int cr_lo = S.phase4 ? S.s[2] + 1 : 0x7fffffff, cr_hi = S.s[3] - 1;
+  // cruise window [cr_lo, cr_hi) as one unsigned compare; empty when phase 4 is short (:818)
+  const int cr_lo = S.s[2] + 1;
+  const unsigned cr_span = (S.phase4 && S.s[3] - 1 > cr_lo) ? (unsigned)(S.s[3] - 1 - cr_lo) : 0u;
   const bool p1 = sub == 1, p2 = sub == 2, p3 = sub == 3;
-  double* o = traj + sub * J + gl;
-  const int stride = 4 * J;
+  // shadow lanes (gl >= J) carry joint J-1 and store the same values to the same address as its real lane
+  unsigned off = (unsigned)(sub * J + row);
+  const unsigned stride = 4u * J;
+  const double* jb = jbuf + row * 32;
   double a = a_0, v = v_0, q = q_0;
   for (int c0 = 0; c0 < len; c0 += 32) {
     const int i_mine = c0 + lane;
@@ -160,21 +164,38 @@ __device__ __forceinline__ double ltp_sample_joint_warp(const LtpLimits& L, cons
       }
     __syncwarp();
     const int n = (len - c0) < 32 ? (len - c0) : 32;
-    for (int u = 0; u < n; ++u) {
+    int u = 0;
+    if (c0 == 0) {  // the first sample integrates unconditionally (:810-813)
+      const double jj = jb[0];
+      a = a_0 + ts * jj;
+      v = v_0 + ts * a;
+      q = q_0 + ts * v;
+      double val = q;
+      val = p1 ? v : val;
+      val = p2 ? a : val;
+      val = p3 ? jj : val;
+      traj[off] = val;
+      off += stride;
+      u = 1;
+    }
+#pragma unroll 4
+    for (; u < n; ++u) {
       const int i = c0 + u;
-      const double jj = jbuf[row * 32 + u];
-      const bool first = i == 0, live = first || i <= s6;
+      const double jj = jb[u];
+      const bool live = i <= s6;
+      const bool cruise = (unsigned)(i - cr_lo) < cr_span;
       const double an = a + ts * jj;
       a = live ? an : 0.0;
-      const double vn = v + ts * a;
-      v = (!first && i >= cr_lo && i < cr_hi) ? v_cruise : (live ? vn : 0.0);
+      double vn = v + ts * a;
+      vn = live ? vn : 0.0;
+      v = cruise ? v_cruise : vn;
       q = q + ts * v;
       double val = q;
       val = p1 ? v : val;
       val = p2 ? a : val;
       val = p3 ? jj : val;
-      if (joint_lane) *o = val;
-      o += stride;
+      traj[off] = val;
+      off += stride;
     }
     __syncwarp();
   }
