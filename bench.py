@@ -46,7 +46,6 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--seed", type=int, default=1003)
-    ap.add_argument("--chunks", type=int, default=1, help="env blocks of the pipelined host-buffer tick (e2e leg)")
     return ap.parse_args()
 
 
@@ -261,52 +260,67 @@ def main():
     shield.profile(0)
 
     # ---- end to end through the C ABI with HOST buffers -----------------------------------------------------------
-    # The call a vectorised env makes: pinned host keypoints/goals in, pinned host setpoints out, every tick. The batch
-    # is cut into env blocks on separate streams so the copies of one block overlap the kernels of another.
+    # The call a vectorised env makes every tick: pinned host keypoints/goals in, pinned host setpoints out, and a stream
+    # sync before the setpoints are consumed. Headline form: double-buffered (hrg_shield_upload_inputs of tick k+1 on a
+    # copy stream while hrg_shield_tick_staged of tick k computes) - the human is an animation replay in the reference, so
+    # the next keypoints exist early. `unpipelined` is the plain hrg_shield_tick_host (copy -> kernels -> copy).
     e2e = None
     if not args.no_e2e:
-        from human_robot_gym_b200.batched import PipelinedHostShield
-        shield.close()
-        del shield
-        torch.cuda.empty_cache()
         pin = dict(pin_memory=True)
-        hs = PipelinedHostShield(N, SAMPLE_TIME, *files, init_qpos=scen.init_q, device=dev, chunks=args.chunks,
-                                 ltt_capacity=args.ltt_capacity, config=sc)
         kp_p = torch.from_numpy(kp_h).pin_memory()
         goals_p = torch.from_numpy(goals_h).pin_memory()
         masks_p = torch.from_numpy(masks_h).pin_memory()
-        t_p = torch.zeros(N, dtype=torch.float64, **pin)
+        t_p = [torch.zeros(N, dtype=torch.float64, **pin) for _ in range(2)]
         q_p, dq_p, ddq_p = (torch.zeros(N, J, dtype=torch.float64, **pin) for _ in range(3))
         fl_p = torch.zeros(N, dtype=torch.uint8, **pin)
+        copy_stream = torch.cuda.Stream(device=dev)
+        main = torch.cuda.current_stream(dev)
 
-        def tick_host(kk):
-            t_p.fill_(kk * SAMPLE_TIME)
-            hs.tick_host(kp_p[ring_index(kk, args.ring)], t_p, masks_p[kk % GOAL_PERIOD],
-                         goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], q_p, dq_p, ddq_p, fl_p)
-            hs.synchronize()  # the caller consumes the setpoints before the next tick
+        def upload(kk):
+            slot = kk & 1
+            t_p[slot].fill_(kk * SAMPLE_TIME)
+            shield.upload_inputs(slot, kp_p[ring_index(kk, args.ring)], t_p[slot], masks_p[kk % GOAL_PERIOD],
+                                 goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], copy_stream)
 
-        ke = 0
-        for _ in range(max(W, 2 * GOAL_PERIOD)):  # fresh shields: run past the first policy periods before timing
-            tick_host(ke)
-            ke += 1
-        sync_all()
-        l0 = hs.launch_count()
-        t0 = time.perf_counter()
-        for _ in range(S):
-            tick_host(ke)
-            ke += 1
-        sync_all()
-        ms_e = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(ms_e, op=dist.ReduceOp.MAX)
+        def tick_piped(kk):
+            upload(kk + 1)                       # next tick's inputs travel while this tick computes
+            shield.tick_staged(kk & 1, q_p, dq_p, ddq_p, fl_p)
+            main.synchronize()                   # the caller consumes the setpoints before the next tick
+
+        def tick_plain(kk):
+            t_p[0].fill_(kk * SAMPLE_TIME)
+            shield.tick_host(kp_p[ring_index(kk, args.ring)], t_p[0], masks_p[kk % GOAL_PERIOD],
+                             goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], q_p, dq_p, ddq_p, fl_p)
+            main.synchronize()
+
+        def timed(fn, kk):
+            for _ in range(max(3, min(W, 10))):
+                fn(kk)
+                kk += 1
+            sync_all()
+            copy_stream.synchronize()
+            l0 = shield.launch_count()
+            t0 = time.perf_counter()
+            for _ in range(S):
+                fn(kk)
+                kk += 1
+            sync_all()
+            ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            return float(ms.item()), kk, shield.launch_count() - l0
+
+        ms_plain, k, _ = timed(tick_plain, k)
+        upload(k)
+        ms_piped, k, l_e = timed(tick_piped, k)
+        copy_stream.synchronize()
         checksum = float(q_p.sum().item()) + float(fl_p.sum().item())  # the result was really read back
-        e2e = {"value": N * world * S / (float(ms_e.item()) / 1e3), "unit": METRIC,
+        e2e = {"value": N * world * S / (ms_piped / 1e3), "unit": METRIC,
                "h2d_bytes_per_step": N * (K * 3 * 8 + 8 + 1 + J * 8), "d2h_bytes_per_step": N * (3 * J * 8 + 1),
-               "ms_per_step": float(ms_e.item()) / S, "env_blocks": len(hs.parts), "gpu_launches": hs.launch_count() - l0,
-               "timer": "host wall clock around the synchronous calls (every tick ends in a stream sync)",
+               "ms_per_step": ms_piped / S, "gpu_launches": l_e,
+               "mode": "double-buffered upload of tick k+1 during tick k; stream sync per tick; host wall clock",
+               "unpipelined": {"value": N * world * S / (ms_plain / 1e3), "ms_per_step": ms_plain / S},
                "checksum": checksum}
-        hs.close()
-        shield = None
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -367,8 +381,7 @@ def main():
             cb, _, _ = cpu_loop(args, files, sc, names, min(args.cpu_envs, N), 25, 100, threads)
             line["cpu_baseline"] = cb
         print(json.dumps(line), flush=True)
-    if shield is not None:
-        shield.close()
+    shield.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -188,6 +188,18 @@ class BatchedSafetyShield:
                                                  _ptr(goal_q_host), _ptr(q_host), _ptr(dq_host), _ptr(ddq_host),
                                                  _ptr(flags_host), self._stream()), "hrg_shield_tick_host")
 
+    def upload_inputs(self, slot: int, kp_host, t_host, goal_mask_host=None, goal_q_host=None, copy_stream=None):
+        """Copy one tick's pinned HOST inputs into staging slot 0/1 on `copy_stream` (a torch.cuda.Stream)."""
+        cs = (copy_stream or torch.cuda.current_stream(self.device)).cuda_stream
+        cabi.check(self.lib.hrg_shield_upload_inputs(self._h, int(slot), kp_host.data_ptr(), t_host.data_ptr(),
+                                                     _ptr(goal_mask_host), _ptr(goal_q_host), cs),
+                   "hrg_shield_upload_inputs")
+
+    def tick_staged(self, slot: int, q_host, dq_host, ddq_host, flags_host):
+        """humanMeasurement + [newLongTermTrajectory] + step on a previously uploaded slot; setpoints to pinned HOST."""
+        cabi.check(self.lib.hrg_shield_tick_staged(self._h, int(slot), _ptr(q_host), _ptr(dq_host), _ptr(ddq_host),
+                                                   _ptr(flags_host), self._stream()), "hrg_shield_tick_staged")
+
 
 class PipelinedHostShield:
     """Host-buffer front end: the batch is cut into `chunks` independent env blocks, each a BatchedSafetyShield with its

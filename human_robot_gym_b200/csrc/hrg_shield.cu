@@ -61,6 +61,14 @@ struct HrgShield {
   double* d_t = nullptr;
   double* d_goal = nullptr;
   uint8_t* d_goal_mask = nullptr;
+  // second staging slot + events of the double-buffered host tick (hrg_shield_upload_inputs / hrg_shield_tick_staged)
+  double* d_kp2[2] = {nullptr, nullptr};
+  double* d_t2[2] = {nullptr, nullptr};
+  double* d_goal2[2] = {nullptr, nullptr};
+  uint8_t* d_goal_mask2[2] = {nullptr, nullptr};
+  bool slot_has_goal[2] = {false, false};
+  bool slot_used[2] = {false, false};
+  cudaEvent_t ev_up[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   double* d_q = nullptr;
   double* d_dq = nullptr;
   double* d_ddq = nullptr;
@@ -194,6 +202,11 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   AL(h->d_t, N);
   AL(h->d_goal, (size_t)J * N);
   AL(h->d_goal_mask, N);
+  h->d_kp2[0] = h->d_kp; h->d_t2[0] = h->d_t; h->d_goal2[0] = h->d_goal; h->d_goal_mask2[0] = h->d_goal_mask;
+  AL(h->d_kp2[1], (size_t)K * 3 * N);
+  AL(h->d_t2[1], N);
+  AL(h->d_goal2[1], (size_t)J * N);
+  AL(h->d_goal_mask2[1], N);
   AL(h->d_q, (size_t)J * N);
   AL(h->d_dq, (size_t)J * N);
   AL(h->d_ddq, (size_t)J * N);
@@ -214,6 +227,10 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
+  for (int k = 0; k < 2 && ce == cudaSuccess; ++k) {
+    ce = cudaEventCreateWithFlags(&h->ev_up[k], cudaEventDisableTiming);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_done[k], cudaEventDisableTiming);
+  }
   if (ce == cudaSuccess) ce = cudaMemcpy(dcfg, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice);
   HrgStats st0;
   memset(&st0, 0, sizeof(st0));
@@ -253,6 +270,10 @@ int hrg_shield_destroy(HrgShield* s) {
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
   if (s->ev_fork) cudaEventDestroy(s->ev_fork);
   if (s->ev_join) cudaEventDestroy(s->ev_join);
+  for (int k = 0; k < 2; ++k) {
+    if (s->ev_up[k]) cudaEventDestroy(s->ev_up[k]);
+    if (s->ev_done[k]) cudaEventDestroy(s->ev_done[k]);
+  }
   if (s->side) cudaStreamDestroy(s->side);
   delete s;
   return HRG_OK;
@@ -360,6 +381,52 @@ int hrg_shield_tick_host(HrgShield* s, const double* keypoints_host, const doubl
   }
   rc = hrg_shield_step(s, s->d_t, s->d_q, s->d_dq, s->d_ddq, nullptr, s->d_safe, s->d_branch, nullptr, stream);
   if (rc) return rc;
+  if (q_host) CK(cudaMemcpyAsync(q_host, s->d_q, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (dq_host) CK(cudaMemcpyAsync(dq_host, s->d_dq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (ddq_host) CK(cudaMemcpyAsync(ddq_host, s->d_ddq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (flags_host) {
+    k_pack_flags<<<grid_for((int)N, 256), 256, 0, st>>>((int)N, s->d_safe, s->d_branch, s->d_flags8);
+    s->launches++;
+    CK(cudaMemcpyAsync(flags_host, s->d_flags8, N, cudaMemcpyDeviceToHost, st));
+  }
+  return HRG_OK;
+}
+
+int hrg_shield_upload_inputs(HrgShield* s, int slot, const double* keypoints_host, const double* t_host,
+                             const uint8_t* goal_mask_host, const double* goal_q_host, void* copy_stream) {
+  if (!s || !keypoints_host || !t_host || slot < 0 || slot > 1)
+    return fail(HRG_EINVAL, "hrg_shield_upload_inputs: bad argument");
+  cudaStream_t cs = static_cast<cudaStream_t>(copy_stream);
+  const size_t N = s->S.N, J = s->S.J, K3 = (size_t)s->S.K * 3;
+  // do not overwrite the slot before the tick that consumed it last has finished with it
+  if (s->slot_used[slot]) CK(cudaStreamWaitEvent(cs, s->ev_done[slot], 0));
+  CK(cudaMemcpyAsync(s->d_kp2[slot], keypoints_host, N * K3 * sizeof(double), cudaMemcpyHostToDevice, cs));
+  CK(cudaMemcpyAsync(s->d_t2[slot], t_host, N * sizeof(double), cudaMemcpyHostToDevice, cs));
+  s->slot_has_goal[slot] = goal_mask_host && goal_q_host;
+  if (s->slot_has_goal[slot]) {
+    CK(cudaMemcpyAsync(s->d_goal_mask2[slot], goal_mask_host, N, cudaMemcpyHostToDevice, cs));
+    CK(cudaMemcpyAsync(s->d_goal2[slot], goal_q_host, N * J * sizeof(double), cudaMemcpyHostToDevice, cs));
+  }
+  CK(cudaEventRecord(s->ev_up[slot], cs));
+  return HRG_OK;
+}
+
+int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_host, double* ddq_host,
+                           uint8_t* flags_host, void* stream) {
+  if (!s || slot < 0 || slot > 1) return fail(HRG_EINVAL, "hrg_shield_tick_staged: bad argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t N = s->S.N, J = s->S.J;
+  CK(cudaStreamWaitEvent(st, s->ev_up[slot], 0));
+  int rc = hrg_shield_human_measurement(s, nullptr, s->d_kp2[slot], s->d_t2[slot], stream);
+  if (rc) return rc;
+  if (s->slot_has_goal[slot]) {
+    rc = hrg_shield_new_goal(s, s->d_goal_mask2[slot], s->d_goal2[slot], nullptr, stream);
+    if (rc) return rc;
+  }
+  rc = hrg_shield_step(s, s->d_t2[slot], s->d_q, s->d_dq, s->d_ddq, nullptr, s->d_safe, s->d_branch, nullptr, stream);
+  if (rc) return rc;
+  CK(cudaEventRecord(s->ev_done[slot], st));
+  s->slot_used[slot] = true;
   if (q_host) CK(cudaMemcpyAsync(q_host, s->d_q, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
   if (dq_host) CK(cudaMemcpyAsync(dq_host, s->d_dq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
   if (ddq_host) CK(cudaMemcpyAsync(ddq_host, s->d_ddq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));

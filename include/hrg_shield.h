@@ -132,6 +132,17 @@ int hrg_shield_tick_host(HrgShield* s, const double* keypoints_host, const doubl
                          const double* goal_q_host, double* q_host, double* dq_host, double* ddq_host,
                          uint8_t* flags_host, void* stream);
 
+/* Double-buffered form of hrg_shield_tick_host for callers whose next inputs exist before the current tick has finished
+ * (the human of human-robot-gym is an animation replay, human_env.py:1710-1767; goals only change every 25th tick):
+ * hrg_shield_upload_inputs copies one tick's HOST inputs into staging slot 0/1 on `copy_stream`;
+ * hrg_shield_tick_staged runs humanMeasurement + [newLongTermTrajectory] + step on that slot on `stream` (it waits for the
+ * upload) and copies the setpoints back. Uploading tick k+1 while tick k computes hides the host->device copy. A slot is
+ * not overwritten before the tick that consumed it has finished (events inside the handle). */
+int hrg_shield_upload_inputs(HrgShield* s, int slot, const double* keypoints_host, const double* t_host,
+                             const uint8_t* goal_mask_host, const double* goal_q_host, void* copy_stream);
+int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_host, double* ddq_host,
+                           uint8_t* flags_host, void* stream);
+
 /* getRobotReachCapsules / getHumanReachCapsules — bindings :111-112 / safety_shield.h:549-574 — of the last step.
  * robot [N,J,7], human [N,H,7] with H = n_ext + 2*n_bodies ordered Pos, Vel, Accel; min_dist [N,3] = per human model
  * the minimum capsule_capsule_dist over robot x human capsules (+inf where the step skipped verification).

@@ -155,3 +155,45 @@ def test_full_body_long_horizon():
     print(res)
     assert res["mismatch_excl_near"] == 0, res
     assert res["max_setpoint_diff"] < 1e-5 and res["max_min_dist_diff"] < 1e-5, res
+
+
+def test_host_buffer_ticks_agree():
+    """hrg_shield_tick_host, the double-buffered upload/tick_staged pair and the device-tensor verbs give bit-identical
+    setpoints and flags (they run the same kernels; only the staging differs)."""
+    from human_robot_gym_b200.batched import BatchedSafetyShield, PipelinedHostShield
+    from human_robot_gym_b200.config import ShieldConfig
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+    files = pu.default_files("schunk")
+    sc = ShieldConfig.from_files(0.004, *files)
+    n, ticks = 300, 80
+    scen = SyntheticScenario(n, pu.mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, 77)
+    mk = lambda: BatchedSafetyShield(n, 0.004, *files, init_qpos=scen.init_q, device="cuda:0", ltt_capacity=1024)
+    a, b, c = mk(), mk(), mk()
+    d = PipelinedHostShield(n, 0.004, *files, init_qpos=scen.init_q, device="cuda:0", chunks=3, ltt_capacity=1024)
+    pin = lambda *shape, dt=torch.float64: torch.zeros(*shape, dtype=dt).pin_memory()
+    outs = {k: (pin(n, 6), pin(n, 6), pin(n, 6), pin(n, dt=torch.uint8)) for k in "bcd"}
+    kp = [torch.from_numpy(scen.keypoints(k * 0.004)).pin_memory() for k in range(ticks + 1)]
+    tt = [torch.full((n,), k * 0.004, dtype=torch.float64).pin_memory() for k in range(ticks + 1)]
+    phase = np.arange(n) % 25
+    masks = [torch.from_numpy((phase == (k % 25)).astype(np.uint8)).pin_memory() for k in range(ticks + 1)]
+    goals = [torch.from_numpy(scen.next_goal()).pin_memory() for _ in range(ticks + 1)]
+    cs = torch.cuda.Stream()
+    c.upload_inputs(0, kp[0], tt[0], masks[0], goals[0], cs)
+    for k in range(ticks):
+        a.humanMeasurement(kp[k], k * 0.004)
+        a.newLongTermTrajectory(goals[k], env_mask=masks[k])
+        a.step(k * 0.004)
+        b.tick_host(kp[k], tt[k], masks[k], goals[k], *outs["b"])
+        c.upload_inputs((k + 1) & 1, kp[k + 1], tt[k + 1], masks[k + 1], goals[k + 1], cs)
+        c.tick_staged(k & 1, *outs["c"])
+        d.tick_host(kp[k], tt[k], masks[k], goals[k], *outs["d"])
+        torch.cuda.synchronize()
+        qa, dqa, ddqa = a.q.cpu(), a.dq.cpu(), a.ddq.cpu()
+        fa = (a.is_safe | (a.branch << 1)).cpu()
+        for key in "bcd":
+            q, dq, ddq, fl = outs[key]
+            assert torch.equal(q, qa) and torch.equal(dq, dqa) and torch.equal(ddq, ddqa), (key, k)
+            assert torch.equal(fl, fa), (key, k)
+    assert a.stats()["n_replan"] > 0 and a.stats() == b.stats() == c.stats()
+    for x in (a, b, c, d):
+        x.close()
