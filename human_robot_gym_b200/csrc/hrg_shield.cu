@@ -337,12 +337,11 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   }
   {
     // the replan list length is only known on the device: grids cover the worst case (every env replans) and surplus
-    // groups / warps leave at once; k_replan_scale fetches (env, joint) tasks from a counter, its grid only bounds residency
+    // groups / warps leave at once; the planning kernels fetch their tasks from counters, their grid only bounds residency
     int sgrid = grid_for(N * s->S.J, kReplanBlock / 32);
     const int per_sm = fork ? s->replan_blocks_per_sm : HRG_REPLAN_MINBLOCKS;
     if (sgrid > s->sm_count * per_sm) sgrid = s->sm_count * per_sm;
-    k_replan_opt<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
-    k_replan_scale<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_plan<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     k_replan_deep<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     k_replan_sample<<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
   }
@@ -358,7 +357,7 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   if (prof) cudaEventRecord(ev[3], st);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
   if (prof) cudaEventRecord(ev[4], st);
-  s->launches += 8;
+  s->launches += 7;
   CK(cudaGetLastError());
   return HRG_OK;
 }

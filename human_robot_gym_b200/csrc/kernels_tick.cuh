@@ -44,28 +44,26 @@ constexpr int kReplanBlock = 64;
 // whole batch only holds a few thousand such problems per tick, so the kernel time is the LONGEST dependent chain, not
 // the instruction total: lanes that diverge serialise, and a warp that walks the whole ladder is the tail everybody
 // waits for. Hence the unit of scheduling is as small as the reference's data flow allows:
-//   k_replan_opt     1 warp per (env, joint)             checkInputs + optSwitchTimes                      (:20-37)
-//   k_replan_scale   1 warp per (env, joint)             slowest joint -> t_required; the two closed-form
-//                                                        timeScaling candidates (:378-436); joints that need the
-//                                                        polynomial candidates go on the `deep` list
+//   k_replan_plan    8 lanes per env, 4 envs per warp    checkInputs + optSwitchTimes (:20-37); slowest joint ->
+//                                                        t_required; the two closed-form timeScaling candidates
+//                                                        (:378-436); joints that need the polynomial candidates go
+//                                                        on the `deep` list
 //   k_replan_deep    1 warp per (deep joint, candidate)  the six polynomial candidates (:449-629), all evaluated; the
 //                                                        first accepted one in the reference's order is taken later,
 //                                                        which is what its sequential ladder returns
 //   k_replan_sample  1 warp per env                      getTrajectory (:706-841), joint-limit test (:59-61), LTT
 //                                                        install, and the rest of the env's step up to reach / verify.
-// Work is fetched from device counters (S.replan_ctr); grids only bound residency. Only lane 0 of a warp computes in
-// the first three kernels: more lanes would only serialise. profiles/r01_ncu_summary.md has the measurements.
+// Work is fetched from device counters (S.replan_ctr); grids only bound residency. How many independent problems share
+// a warp is a measured trade-off (profiles/r01_replan_packing.md): one per warp has the shortest chains but is
+// instruction-fetch bound, many per warp serialise where they diverge.
 enum { CTR_OPT = 0, CTR_SCALE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, N_CTR = 4 };
 
 // Lanes per warp that carry a task in the three planning kernels. 1 = one problem per warp (shortest chains, but every
 // warp instruction is fetched for a single lane and the kernels become instruction-fetch bound); larger = several
 // independent problems share a warp and the instructions they have in common, at the price of serialising where they
 // diverge. Measured on B200 (profiles/r01_replan_packing.md).
-#ifndef HRG_G_OPT
-#define HRG_G_OPT 16
-#endif
-#ifndef HRG_G_SCALE
-#define HRG_G_SCALE 8
+#ifndef HRG_G_ENVS
+#define HRG_G_ENVS 4  // envs (8-lane groups) per warp in k_replan_plan
 #endif
 #ifndef HRG_G_DEEP
 #define HRG_G_DEEP 3
@@ -86,32 +84,6 @@ __device__ __forceinline__ LtpLimits joint_limits(const HrgConfig& c, int j, dou
   return L;
 }
 
-__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_opt(DevState S) {
-  __shared__ double mat_s[kReplanBlock / 32][HRG_G_OPT][37];
-  const HrgConfig& c = *S.cfg;
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int J = S.J, N = S.N;
-  const int ntask = *S.replan_count * J;
-  for (;;) {
-    const int task = fetch_tasks<HRG_G_OPT>(S.replan_ctr + CTR_OPT, lane);
-    if (__shfl_sync(0xffffffffu, task, 0) >= ntask) break;
-    if (lane >= HRG_G_OPT || task >= ntask) continue;
-    const int idx = task / J, j = task - idx * J;
-    const int e = S.replan_list[idx];
-    const LtpLimits L = joint_limits(c, j, mat_s[wib][lane]);
-    const double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
-    const double q_goal = S.goal_q[(size_t)j * N + e];
-    PlanRec rec;
-    ltp_zero7(rec.T);
-    rec.dir = 0.0; rec.v_drive = L.v_max; rec.mod = 0;
-    bool ok = ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0);
-    // (the reference stops at the first joint that fails; the outputs of the others are never used then)
-    if (ok) ok = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, rec.T, rec.dir, rec.mod);
-    rec.len = ok ? 1 : 0;
-    S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j] = rec;
-  }
-}
-
 // The `mx <= 0` fallback of planTrajectory (:47-50) and the joint's sample count.
 __device__ __forceinline__ void finish_scaled(const LtpLimits& L, const PlanRec& opt, const double* T, double v_drive,
                                               int mod, PlanRec& sc) {
@@ -127,69 +99,88 @@ __device__ __forceinline__ void finish_scaled(const LtpLimits& L, const PlanRec&
   sc.len = ltp_joint_len(L, P);
 }
 
-__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_scale(DevState S) {
+// HRG_G_ENVS envs per warp, 8 lanes per env: lane j of a group plans joint j (lanes >= J shadow joint J-1 and never
+// write). Because the joints of an env sit in one group, the slowest joint is a width-8 shuffle away and the two
+// closed-form timeScaling candidates follow at once, without a kernel boundary.
+__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_plan(DevState S) {
+  __shared__ double mat_s[kReplanBlock / 32][HRG_G_ENVS * 8][37];
   const HrgConfig& c = *S.cfg;
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int gl = lane & 7, grp = lane >> 3;
+  const unsigned gmask = 0xFFu << (lane & 24);
   const int J = S.J, N = S.N;
-  const int ntask = *S.replan_count * J;
+  const int count = *S.replan_count;
+  const int j = gl < J ? gl : J - 1;
+  const bool writer = gl < J;
   for (;;) {
-    const int task = fetch_tasks<HRG_G_SCALE>(S.replan_ctr + CTR_SCALE, lane);
-    if (__shfl_sync(0xffffffffu, task, 0) >= ntask) break;
-    if (lane >= HRG_G_SCALE || task >= ntask) continue;
-    const int idx = task / J, j = task - idx * J;
-    const PlanRec* opts = S.plan_opt + (size_t)idx * HRG_MAX_JOINTS;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(S.replan_ctr + CTR_OPT, HRG_G_ENVS);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= count) break;
+    const int idx = base + grp;
+    if (grp >= HRG_G_ENVS || idx >= count) continue;  // whole 8-lane groups leave together
+    const int e = S.replan_list[idx];
+    const LtpLimits L = joint_limits(c, j, mat_s[wib][lane]);
+    double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
+    const double q_goal = S.goal_q[(size_t)j * N + e];
+    PlanRec opt;
+    ltp_zero7(opt.T);
+    opt.dir = 0.0; opt.v_drive = L.v_max; opt.mod = 0; opt.len = 0;
+    // checkInputs + optSwitchTimes (:20-37); the reference stops at the first joint that fails
+    bool ok = ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0);
+    if (ok) ok = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, opt.T, opt.dir, opt.mod);
+    ok = (__ballot_sync(gmask, ok) & gmask) == gmask;
     // slowest joint (:39-45)
     PlanHead h;
     h.t_required = -1;
     h.slowest = -1;
-    h.ok = 1;
     for (int k = 0; k < J; ++k) {
-      if (!opts[k].len) h.ok = 0;
-      const double tk = opts[k].T[6];
+      const double tk = __shfl_sync(gmask, opt.T[6], k, 8);
       if (tk > h.t_required) {
         h.t_required = tk;
         h.slowest = k;
       }
     }
-    if (h.slowest == -1) h.ok = 0;
-    if (j == 0) S.plan_head[idx] = h;
-    const PlanRec opt = opts[j];
+    if (h.slowest == -1) ok = false;
+    h.ok = ok ? 1 : 0;
+    opt.len = h.ok;
     PlanRec sc = opt;
-    const LtpLimits L = joint_limits(c, j, nullptr);  // the closed-form candidates never reach the root finder ...
-    if (h.ok) {
+    if (ok) {
       double T[7];
       ltp_zero7(T);
       double v_drive = L.v_max;
       int mod = opt.mod;
       bool deep = false;
       if (j != h.slowest) {
-        const int e = S.replan_list[idx];
-        double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
-        const double q_goal = S.goal_q[(size_t)j * N + e];
         if (opt.dir < 0) {
           v_0 = -v_0;
           a_0 = -a_0;
         }
         const double v_orig = opt.dir * v_0, a_orig = opt.dir * a_0;
         bool acc = false;
-        for (int cand = 0; cand < 2 && !acc; ++cand) {
+        for (int cand = 0; cand < 2 && !acc; ++cand) {  // the closed-form candidates (:378-436)
           double A[7];
           int ncoef;
           v_drive = ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, opt.dir, h.t_required, A, ncoef);
-          // ... but the optSwitchTimes trial can (two quartics, :246-261,301-321): it gets a local matrix then
           acc = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, h.t_required, T, mod);
         }
         deep = !acc;
       }
       if (deep) {
-        const int slot = atomicAdd(S.replan_ctr + CTR_DEEP_COUNT, 1);
-        S.deep_list[slot] = task;
-        sc.len = -(slot + 1);
+        if (writer) {
+          const int slot = atomicAdd(S.replan_ctr + CTR_DEEP_COUNT, 1);
+          S.deep_list[slot] = idx * J + j;
+          sc.len = -(slot + 1);
+        }
       } else {
         finish_scaled(L, opt, T, v_drive, mod, sc);
       }
     }
-    S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j] = sc;
+    if (writer) {
+      S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j] = opt;
+      S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j] = sc;
+    }
+    if (gl == 0) S.plan_head[idx] = h;
   }
 }
 

@@ -161,46 +161,6 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
   return false;
 }
 
-#if defined(__CUDACC__)
-// Warp form for k_replan_scale: lane c < 8 evaluates candidate c. The candidates share all the expensive code (the
-// eigenvalue solve and the optSwitchTimes trial), so the eight lanes run it together and the time of a task is that of
-// its slowest candidate instead of the sum over the ladder; the first accepted candidate in the reference's order wins,
-// which is exactly what the sequential form returns. L.mat must point at this lane's own matrix scratch.
-// All 32 lanes must call; lanes >= 8 idle. Outputs are valid on every lane.
-__device__ __forceinline__ bool ltp_time_scaling_warp(const LtpLimits& L, int lane, double q_goal, double q_0, double v_0,
-                                                      double a_0, double dir, double tr, double* T, double& v_drive,
-                                                      int& mod_jerk_profile) {
-  if (dir < 0) {
-    v_0 = -v_0;
-    a_0 = -a_0;
-  }
-  const double v_orig = dir * v_0, a_orig = dir * a_0;
-  bool acc = false;
-  double Tc[7];
-  ltp_zero7(Tc);
-  double vd = L.v_max;
-  int mod = 0;
-  if (lane < 8) {
-    double A[7];
-    int ncoef;
-    vd = ltp_scaling_setup(L, lane, q_goal, q_0, v_0, a_0, dir, tr, A, ncoef);
-    if (ncoef) vd = ltp_scaling_vdrive(L, lane, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
-    acc = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, vd, tr, Tc, mod);
-  }
-  const unsigned won = __ballot_sync(0xffffffffu, acc);
-  if (won == 0u) {
-    mod_jerk_profile = 0;
-    ltp_zero7(T);
-    v_drive = L.v_max;
-    return false;
-  }
-  const int src = __ffs(won) - 1;
-  for (int k = 0; k < 7; ++k) T[k] = __shfl_sync(0xffffffffu, Tc[k], src);
-  v_drive = __shfl_sync(0xffffffffu, vd, src);
-  mod_jerk_profile = __shfl_sync(0xffffffffu, mod, src);
-  return true;
-}
-#endif
 
 }  // namespace hrg
 #include "ltp_traj.cuh"
