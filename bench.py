@@ -201,6 +201,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries exactly one JSON line
         dist.init_process_group("nccl", device_id=dev)
     N, J, K = args.envs, sc.robot.nb_joints, sc.human.n_keypoints
     W, S = args.warmup, args.steps
