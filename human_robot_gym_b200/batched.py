@@ -88,7 +88,9 @@ class BatchedSafetyShield:
         N, J = self.n_envs, self.J
         pose, q0 = self._f64(base_pose, (N, 6)), self._f64(init_qpos, (N, J))
         t = self._f64(current_time, (N,))
-        ty = torch.as_tensor(shield_type, dtype=torch.int32, device=self.device).expand(N).contiguous()
+        ty = None  # NULL = all SSM (the library then does not need its PFL buffers)
+        if np.any(np.asarray(shield_type) != cabi.SHIELD_SSM):
+            ty = torch.as_tensor(shield_type, dtype=torch.int32, device=self.device).expand(N).contiguous()
         m = self._mask(env_mask)
         cabi.check(self.lib.hrg_shield_reset(self._h, _ptr(m), _ptr(pose), _ptr(q0), _ptr(t), _ptr(ty), self._stream()),
                    "hrg_shield_reset")

@@ -143,12 +143,6 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   h->pfl = false;
   if (shield_type_host)
     for (size_t i = 0; i < N; ++i) h->pfl |= (shield_type_host[i] == HRG_SHIELD_PFL);
-  if (h->pfl) {
-    // PFL needs the per-sample Cartesian capsule velocities of every planned LTT (long_term_traj.cc:5-39,
-    // robot_reach.cc:110-199); that constructor is not built yet, and a silently wrong v_limit is worse than a refusal
-    delete h;
-    return fail(HRG_EINVAL, "ShieldType PFL is not supported yet (SSM and OFF are)");
-  }
   HrgConfig* dcfg = nullptr;
 #define AL(ptr, count)                         \
   do {                                         \
@@ -194,8 +188,10 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   S.ltt_cart = nullptr;
   S.robot_caps = nullptr;
   S.human_caps = nullptr;
+  S.ltt_time = nullptr;
   if (h->pfl) {
     AL(S.ltt_cart, (size_t)N * 2 * L);
+    AL(S.ltt_time, (size_t)N * 2 * L);
   }
   // staging buffers of hrg_shield_tick_host
   AL(h->d_kp, (size_t)K * 3 * N);
@@ -286,6 +282,15 @@ int64_t hrg_shield_launch_count(const HrgShield* s) { return s ? s->launches : 0
 int hrg_shield_reset(HrgShield* s, const uint8_t* env_mask, const double* base_pose, const double* init_q,
                      const double* t, const int32_t* shield_type, void* stream) {
   if (!s || !base_pose || !init_q) return fail(HRG_EINVAL, "hrg_shield_reset: NULL argument");
+  if (shield_type && !s->S.ltt_cart) {
+    // explicit types may contain PFL: make sure the per-sample Cartesian velocity / time buffers exist
+    CK(cudaSetDevice(s->device));
+    int rc = s->alloc(&s->S.ltt_cart, (size_t)s->S.N * 2 * s->S.L);
+    if (rc) return rc;
+    rc = s->alloc(&s->S.ltt_time, (size_t)s->S.N * 2 * s->S.L);
+    if (rc) return rc;
+    s->pfl = true;
+  }
   (void)t;  // cycle_begin_time_ is only stored by the reference (safety_shield.cc:185)
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   k_reset<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S, env_mask, base_pose, init_q, shield_type);
@@ -343,7 +348,10 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
     if (sgrid > s->sm_count * per_sm) sgrid = s->sm_count * per_sm;
     k_replan_plan<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     k_replan_deep<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
-    k_replan_sample<<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
+    if (s->pfl)
+      k_replan_sample<true><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
+    else
+      k_replan_sample<false><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
   }
   if (fork) {
     CK(cudaEventRecord(s->ev_join, s->side));

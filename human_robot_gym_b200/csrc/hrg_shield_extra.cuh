@@ -60,6 +60,11 @@ __global__ void k_set_ltt(DevState S, int e, const double* __restrict__ traj, in
     const int pend = (S.flags[e] & F_LIVE_SLOT) ? 0 : 1;
     double* dst = ltt_sample_w(S, e, pend, 0);
     for (int i = threadIdx.x; i < length * 4 * J; i += blockDim.x) dst[i] = traj[i];
+    if (S.ltt_cart)  // a user-built LongTermTraj comes from the SSM constructor: no Cartesian velocities (long_term_traj.h:108-116)
+      for (int i = threadIdx.x; i < length; i += blockDim.x) {
+        S.ltt_cart[((size_t)e * 2 + pend) * S.L + i] = 0.0;
+        S.ltt_time[((size_t)e * 2 + pend) * S.L + i] = i * sample_time;
+      }
   }
 }
 }  // namespace

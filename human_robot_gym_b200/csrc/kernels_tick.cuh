@@ -3,6 +3,7 @@
 #pragma once
 #include "ltp_math.cuh"
 #include "step_logic.cuh"
+#include "pfl_math.cuh"
 
 namespace hrg {
 
@@ -224,6 +225,9 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_d
 // One warp per env: lane = joint gl + 8 * sub. Each sub-lane evaluates the jerk of one of four consecutive samples and
 // stores one of the four components; the integration itself stays the reference's sequential recurrence (bit-identical
 // sums). Lane 0 then finishes the env's step up to the reach / verify hand-over.
+// WITH_PFL = false is the build every SSM/OFF-only handle launches: the PFL branch is compiled out of it (its call would
+// otherwise cost the sampler registers even when never taken).
+template <bool WITH_PFL>
 __global__ void __launch_bounds__(128) k_replan_sample(DevState S, const double* __restrict__ t) {
   __shared__ JerkSampler samp_s[4][8];
   __shared__ double jbuf_s[4][8 * 32];
@@ -287,10 +291,15 @@ __global__ void __launch_bounds__(128) k_replan_sample(DevState S, const double*
       ok = __all_sync(full, in);
     }
   }
+  const bool pfl = WITH_PFL && ((f & F_TYPE_MASK) >> F_TYPE_SHIFT) == HRG_SHIELD_PFL;
+  if (WITH_PFL && ok && pfl) {
+    __syncwarp(full);
+    pfl_ltt_warp(S, c, e, pend, len, lane);  // PFL LongTermTraj ctor: Cartesian velocities + alpha_i (long_term_traj.cc:5-39)
+  }
   if (ok && joint_lane && sub == 0) {
     S.replan_q[(size_t)j * N + e] = q_0;  // last_replan_start_motion_ = current_motion (:593)
     // SSM/OFF: alpha_i_ = alpha_i_max (long_term_traj.h:108-116)
-    S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
+    if (!pfl) S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
   }
   __syncwarp(full);
   if (lane == 0) {
@@ -424,7 +433,10 @@ __global__ void k_reset(DevState S, const uint8_t* __restrict__ mask, const doub
     S.prev_dq[(size_t)j * N + e] = 0.0;
     S.ltt_alpha[((size_t)0 * J + j) * N + e] = (type == HRG_SHIELD_PFL) ? 0.0 : c.alpha_i_max;
   }
-  if (S.ltt_cart) S.ltt_cart[((size_t)e * 2 + 0) * S.L] = 0.0;
+  if (S.ltt_cart) {  // PFL ctor on the one-sample LTT: zero joint velocity -> zero Cartesian velocity, alpha_i = 0
+    S.ltt_cart[((size_t)e * 2 + 0) * S.L] = 0.0;
+    S.ltt_time[((size_t)e * 2 + 0) * S.L] = 0.0;
+  }
   for (int s = 0; s < 2; ++s) {
     S.ltt_len[(size_t)s * N + e] = 1;
     S.ltt_cur[(size_t)s * N + e] = 0;

@@ -1,0 +1,152 @@
+// PFL (power-and-force-limiting) shields: per-sample Cartesian capsule velocities of a long-term trajectory.
+// Restates the PFL LongTermTraj constructor (SS/src/long_term_traj.cc:5-39) and the RobotReach velocity helpers it uses
+// (SS/src/robot_reach.cc:110-199: calculateAllTransformationMatricesAndCapsules, getJacobian, getVelocityOfCapsule,
+// approximateVelOfCapsule). exactVelOfCapsule is never reached from this constructor (SURVEY.md §8(a) a18 note).
+#pragma once
+#include "state.cuh"
+
+namespace hrg {
+
+// One LTT sample (q, qd): forward kinematics from the base pose (rows 0..2 at base[k * bs]), world end points of every
+// link capsule, the geometric Jacobian at p1 of link j (columns i <= j: z_{i+1} x (p1_j - p1_i) ; z_{i+1}) applied to
+// qd[0..j], v2 = v1 + w x (p2 - p1). Outputs |v1|, |v2| per link (for alpha_i) and returns the approximate maximum
+// surface speed of the LAST link: long_term_traj.cc:19-35 overwrites motion_vel per link, so the value stored per
+// sample is the last link's, not the maximum over links - mirrored on purpose.
+HRG_HD_CALL double pfl_sample_velocity(const HrgConfig& c, const double* base, size_t bs, const double* q,
+                                       const double* qd, double* n1 /*[J]*/, double* n2 /*[J]*/) {
+  const int J = c.nb_joints;
+  double T[12];
+  for (int k = 0; k < 12; ++k) T[k] = base[(size_t)k * bs];
+  double z[HRG_MAX_JOINTS + 1][3], p1[HRG_MAX_JOINTS][3], p2[HRG_MAX_JOINTS][3];
+  z[0][0] = T[2]; z[0][1] = T[6]; z[0][2] = T[10];
+  for (int i = 0; i < J; ++i) {  // RobotReach::forwardKinematic (robot_reach.h:136-142) + transformCapsule (:54-59)
+    const double* F = c.link_T[i];
+    const double cs = cos(q[i]), sn = sin(q[i]);
+    for (int r = 0; r < 3; ++r) {
+      const double r0 = T[r * 4 + 0], r1 = T[r * 4 + 1], r2 = T[r * 4 + 2], r3 = T[r * 4 + 3];
+      const double t0 = r0 * F[0] + r1 * F[4] + r2 * F[8] + r3 * F[12];
+      const double t1 = r0 * F[1] + r1 * F[5] + r2 * F[9] + r3 * F[13];
+      const double t2 = r0 * F[2] + r1 * F[6] + r2 * F[10] + r3 * F[14];
+      const double t3 = r0 * F[3] + r1 * F[7] + r2 * F[11] + r3 * F[15];
+      T[r * 4 + 0] = t0 * cs + t1 * sn;
+      T[r * 4 + 1] = t1 * cs - t0 * sn;
+      T[r * 4 + 2] = t2;
+      T[r * 4 + 3] = t3;
+      const double* lp = c.link_caps[i];
+      p1[i][r] = T[r * 4 + 0] * lp[0] + T[r * 4 + 1] * lp[1] + T[r * 4 + 2] * lp[2] + T[r * 4 + 3];
+      p2[i][r] = T[r * 4 + 0] * lp[3] + T[r * 4 + 1] * lp[4] + T[r * 4 + 2] * lp[5] + T[r * 4 + 3];
+      z[i + 1][r] = T[r * 4 + 2];
+    }
+  }
+  double motion_vel = 0.0;
+  for (int j = 0; j < J; ++j) {
+    // result1 = jacobian1 * velocity.segment(0, j + 1): s = col_0 * qd_0, then += col_k * qd_k (k ascending)
+    double v1[3], w[3];
+    for (int i = 0; i <= j; ++i) {
+      const V3 zi = v3(z[i + 1][0], z[i + 1][1], z[i + 1][2]);
+      const V3 up = vcross(zi, v3(p1[j][0] - p1[i][0], p1[j][1] - p1[i][1], p1[j][2] - p1[i][2]));
+      if (i == 0) {
+        v1[0] = up.x * qd[0]; v1[1] = up.y * qd[0]; v1[2] = up.z * qd[0];
+        w[0] = zi.x * qd[0]; w[1] = zi.y * qd[0]; w[2] = zi.z * qd[0];
+      } else {
+        v1[0] += up.x * qd[i]; v1[1] += up.y * qd[i]; v1[2] += up.z * qd[i];
+        w[0] += zi.x * qd[i]; w[1] += zi.y * qd[i]; w[2] += zi.z * qd[i];
+      }
+    }
+    const V3 W = v3(w[0], w[1], w[2]);
+    const V3 d21 = v3(p2[j][0] - p1[j][0], p2[j][1] - p1[j][1], p2[j][2] - p1[j][2]);
+    const V3 V1 = v3(v1[0], v1[1], v1[2]);
+    const V3 V2 = vadd(V1, vcross(W, d21));  // v_2 = v_1 + w x (p_2 - p_1)
+    n1[j] = vnorm(V1);
+    n2[j] = vnorm(V2);
+    // approximateVelOfCapsule(j, v2, w) (robot_reach.cc:165-177)
+    const V3 link = v3(p1[j][0] - p2[j][0], p1[j][1] - p2[j][1], p1[j][2] - p2[j][2]);
+    const double r = c.link_caps[j][6];
+    const double wn = vnorm(W);
+    const double s2 = vnorm(V2) + wn * r;
+    const double s1 = vnorm(vadd(V2, vcross(W, link))) + wn * r;
+    motion_vel = fmax(s1, s2);
+  }
+  return motion_vel;
+}
+
+// Sequential form of the whole constructor for one env (host emulation, single-thread use): fills time[i] (the Motion
+// times of calculateLongTermTrajectory, safety_shield.cc:739-752: new_time accumulates), cart[i] and alpha[j].
+HRG_HD void pfl_ltt_env_seq(const HrgConfig& c, const double* base, size_t bs, const double* traj /*[len][4][J]*/,
+                            int len, double t0, double* time, double* cart, double* alpha /*[J]*/) {
+  const int J = c.nb_joints;
+  double prev1[HRG_MAX_JOINTS], prev2[HRG_MAX_JOINTS];
+  for (int j = 0; j < J; ++j) alpha[j] = 0.0;
+  double t = t0;
+  for (int i = 0; i < len; ++i) {
+    time[i] = t;
+    t += c.sample_time;
+    double n1[HRG_MAX_JOINTS], n2[HRG_MAX_JOINTS];
+    const double* m = traj + (size_t)i * 4 * J;
+    cart[i] = pfl_sample_velocity(c, base, bs, m, m + J, n1, n2);
+    for (int j = 0; j < J; ++j) {
+      if (i > 0) {
+        const double dt = time[i] - time[i - 1];
+        const double a1 = fabs(n1[j] - prev1[j]) / dt, a2 = fabs(n2[j] - prev2[j]) / dt;
+        alpha[j] = fmax(alpha[j], fmax(a1, a2));
+      }
+      prev1[j] = n1[j];
+      prev2[j] = n2[j];
+    }
+  }
+}
+
+#if defined(__CUDACC__)
+// Warp form for k_replan_sample: lane = sample within a chunk of 32 (samples are independent except for the
+// neighbour difference of alpha_i, which travels by shuffle). `len` warp-uniform; the trajectory was just written by
+// this warp. Writes ltt_time / ltt_cart of the slot and alpha_i of the env.
+__device__ __noinline__ void pfl_ltt_warp(const DevState& S, const HrgConfig& c, int e, int slot, int len, int lane) {
+  const int J = S.J, N = S.N;
+  double* tm = S.ltt_time + ((size_t)e * 2 + slot) * S.L;
+  double* cv = S.ltt_cart + ((size_t)e * 2 + slot) * S.L;
+  if (lane == 0) {
+    double t = S.path_s[e];
+    for (int i = 0; i < len; ++i) {
+      tm[i] = t;
+      t += c.sample_time;
+    }
+  }
+  __syncwarp();
+  double amax[HRG_MAX_JOINTS], c1[HRG_MAX_JOINTS], c2[HRG_MAX_JOINTS];
+  for (int j = 0; j < HRG_MAX_JOINTS; ++j) amax[j] = c1[j] = c2[j] = 0.0;
+  for (int c0 = 0; c0 < len; c0 += 32) {
+    const int i = c0 + lane;
+    const bool valid = i < len;
+    double n1[HRG_MAX_JOINTS], n2[HRG_MAX_JOINTS];
+    for (int j = 0; j < HRG_MAX_JOINTS; ++j) n1[j] = n2[j] = 0.0;
+    if (valid) {
+      const double* m = ltt_sample(S, e, slot, i);
+      double q[HRG_MAX_JOINTS], qd[HRG_MAX_JOINTS];
+      for (int j = 0; j < J; ++j) {
+        q[j] = m[j];
+        qd[j] = m[J + j];
+      }
+      cv[i] = pfl_sample_velocity(c, S.base_T + e, (size_t)N, q, qd, n1, n2);
+    }
+    const double dt = (valid && i > 0) ? tm[i] - tm[i - 1] : 1.0;
+    for (int j = 0; j < J; ++j) {
+      double p1 = __shfl_up_sync(0xffffffffu, n1[j], 1), p2 = __shfl_up_sync(0xffffffffu, n2[j], 1);
+      if (lane == 0) {
+        p1 = c1[j];
+        p2 = c2[j];
+      }
+      if (valid && i > 0) amax[j] = fmax(amax[j], fmax(fabs(n1[j] - p1) / dt, fabs(n2[j] - p2) / dt));
+      c1[j] = __shfl_sync(0xffffffffu, n1[j], 31);
+      c2[j] = __shfl_sync(0xffffffffu, n2[j], 31);
+    }
+  }
+  for (int j = 0; j < J; ++j) {
+    double a = amax[j];
+    for (int o = 16; o > 0; o >>= 1) a = fmax(a, __shfl_xor_sync(0xffffffffu, a, o));
+    if (lane == j) S.ltt_alpha[((size_t)slot * J + j) * N + e] = a;
+  }
+  __syncwarp();
+}
+#endif
+
+}  // namespace hrg

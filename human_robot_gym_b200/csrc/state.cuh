@@ -68,6 +68,7 @@ struct DevState {
   // ---- env-major [N][..]
   double* ltt;        // [N][2][L][4][J]  q, dq, ddq, dddq per sample
   double* ltt_cart;   // [N][2][L] max Cartesian velocity per sample (PFL; NULL otherwise)
+  double* ltt_time;   // [N][2][L] Motion time of each sample (PFL scan of getMaxofMaximumCartesianVelocityWithS)
   // ---- per-step hand-over between the kernels of one tick, field-major
   double* cur;        // [4J+1][N]: q, dq, ddq, dddq of getCurrentMotion(), then its s
   double* reach_in;   // [3J+2][N]: q_start[J], q_goal[J], alpha_i[J], s_diff, t_reach

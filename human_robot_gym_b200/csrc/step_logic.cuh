@@ -80,12 +80,12 @@ HRG_HD void potential_env(const DevState& S, const HrgConfig& c, int e, uint32_t
         // LongTermTraj::getMaxofMaximumCartesianVelocityWithS (SS/src/long_term_traj.cc:165-176)
         int i = S.ltt_cur[(size_t)slot * N + e];
         const int len = S.ltt_len[(size_t)slot * N + e];
-        const double t0 = S.ltt_t0[(size_t)slot * N + e];
         const double* cv = S.ltt_cart + ((size_t)e * 2 + slot) * S.L;
+        const double* tm = S.ltt_time + ((size_t)e * 2 + slot) * S.L;
         double vmax = cv[i];
         while (i < len) {
           vmax = fmax(vmax, cv[i]);
-          if (t0 + i * ts > s_d) break;
+          if (tm[i] > s_d) break;
           ++i;
         }
         const bool under_iso = vmax <= c.v_safe;

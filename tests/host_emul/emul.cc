@@ -13,6 +13,7 @@
 
 #include "../../human_robot_gym_b200/csrc/ltp_math.cuh"
 #include "../../human_robot_gym_b200/csrc/step_logic.cuh"
+#include "../../human_robot_gym_b200/csrc/pfl_math.cuh"
 
 using namespace hrg;
 
@@ -51,6 +52,8 @@ static void emul_reset_env(Emul* E, int e, const double* pose, const double* q0,
     S.prev_dq[(size_t)j * N + e] = 0.0;
     S.ltt_alpha[((size_t)0 * J + j) * N + e] = (type == HRG_SHIELD_PFL) ? 0.0 : c.alpha_i_max;
   }
+  S.ltt_cart[((size_t)e * 2 + 0) * S.L] = 0.0;
+  S.ltt_time[((size_t)e * 2 + 0) * S.L] = 0.0;
   for (int s = 0; s < 2; ++s) {
     S.ltt_len[(size_t)s * N + e] = 1;
     S.ltt_cur[(size_t)s * N + e] = 0;
@@ -152,7 +155,7 @@ void* emul_create(const HrgConfig* cfg, int n, const double* pose, const double*
   E->al(&S.ltt_len, 2 * N); E->al(&S.ltt_cur, 2 * N); E->al(&S.ltt_start, 2 * N);
   E->al(&S.ltt_t0, 2 * N); E->al(&S.ltt_ts, 2 * N); E->al(&S.ltt_alpha, 2 * J * N);
   E->al(&S.base_T, 12 * N); E->al(&S.kp_pos, K * 3 * N); E->al(&S.kp_vel, K * 3 * N); E->al(&S.last_meas, N);
-  E->al(&S.ltt, N * 2 * L * 4 * J); E->al(&S.ltt_cart, N * 2 * L);
+  E->al(&S.ltt, N * 2 * L * 4 * J); E->al(&S.ltt_cart, N * 2 * L); E->al(&S.ltt_time, N * 2 * L);
   E->al(&S.cur, N * cur_fields(J)); E->al(&S.reach_in, N * reach_fields(J)); E->al(&S.min_dist, 3 * N);
   E->robot.assign(N * J * 7, 0.0);
   E->human.assign(N * H * 7, 0.0);
@@ -217,9 +220,14 @@ void emul_step(void* h, const double* t, double* q, double* dq, double* ddq, dou
       uint32_t st = HRG_ST_REPLANNED;
       int len = ltp_plan_env_seq(c, goal, cur, cur + J, cur + 2 * J, ltt_sample_w(S, e, pend, 0), S.L);
       if (len > 0) {
+        const bool pfl = ((f & F_TYPE_MASK) >> F_TYPE_SHIFT) == HRG_SHIELD_PFL;
+        double alpha[HRG_MAX_JOINTS];
+        if (pfl)
+          pfl_ltt_env_seq(c, S.base_T + e, (size_t)N, ltt_sample(S, e, pend, 0), len, S.path_s[e],
+                          S.ltt_time + ((size_t)e * 2 + pend) * S.L, S.ltt_cart + ((size_t)e * 2 + pend) * S.L, alpha);
         for (int j = 0; j < J; ++j) {
           S.replan_q[(size_t)j * N + e] = cur[j];
-          S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
+          S.ltt_alpha[((size_t)pend * J + j) * N + e] = pfl ? alpha[j] : c.alpha_i_max;
         }
         S.ltt_len[(size_t)pend * N + e] = len;
         S.ltt_cur[(size_t)pend * N + e] = 0;

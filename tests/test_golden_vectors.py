@@ -337,12 +337,13 @@ def _closed_loop(files, n, ticks, seed, shield_type=1):
 
 
 @needs_ref
-@pytest.mark.parametrize("robot,mocap,traj,n,ticks,seed", [
-    ("schunk", "mujoco_mocap", None, 48, 200, 1001),
-    ("panda", "mujoco_mocap", None, 32, 150, 1002),
-    ("schunk", "mujoco_mocap_full_body", "trajectory_parameters_schunk_long", 24, 120, 1004)])
-def test_tick_logic_matches_oracle_closed_loop(robot, mocap, traj, n, ticks, seed):
-    mis, near, worst, hist = _closed_loop(pu.default_files(robot, mocap, traj), n, ticks, seed)
+@pytest.mark.parametrize("robot,mocap,traj,n,ticks,seed,shield_type", [
+    ("schunk", "mujoco_mocap", None, 48, 200, 1001, 1),
+    ("panda", "mujoco_mocap", None, 32, 150, 1002, 1),
+    ("schunk", "mujoco_mocap_full_body", "trajectory_parameters_schunk_long", 24, 120, 1004, 1),
+    ("schunk", "mujoco_mocap", None, 32, 200, 1004, 2)])   # PFL (robot_human_handover_cart.yaml:24)
+def test_tick_logic_matches_oracle_closed_loop(robot, mocap, traj, n, ticks, seed, shield_type):
+    mis, near, worst, hist = _closed_loop(pu.default_files(robot, mocap, traj), n, ticks, seed, shield_type)
     assert mis == 0, (mis, near)
     assert near <= 1
     assert worst < 1e-9            # north_star tolerance is 1e-5; same IEEE operations give ~1e-13

@@ -149,6 +149,16 @@ def test_closed_loop_matches_checker(robot, n_envs, ticks, seed):
     assert res["branch_hist"][0] > 0 and res["branch_hist"][2] > 0
 
 
+def test_pfl_shield_matches_checker():
+    """ShieldType PFL (BASELINE config 4b, robot_human_handover_cart.yaml:24): per-sample Cartesian velocities of every
+    planned LTT, alpha_i from their differences, v_limit failsafe, is_safe || is_under_v_limit."""
+    res = pu.closed_loop_compare(pu.default_files("schunk"), n_envs=384, ticks=150, seed=1004, shield_type=2)
+    print(res)
+    assert res["mismatch_excl_near"] == 0, res
+    assert res["max_setpoint_diff"] < 1e-5 and res["max_min_dist_diff"] < 1e-5 and res["max_capsule_diff"] < 1e-5, res
+    assert res["gpu_stats"]["n_replan"] > 0
+
+
 def test_full_body_long_horizon():
     files = pu.default_files("schunk", "mujoco_mocap_full_body", "trajectory_parameters_schunk_long")
     res = pu.closed_loop_compare(files, n_envs=256, ticks=100, seed=1004)
