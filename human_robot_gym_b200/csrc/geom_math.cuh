@@ -19,6 +19,13 @@ HRG_HD V3 vadd(const V3& a, const V3& b) { return v3(a.x + b.x, a.y + b.y, a.z +
 HRG_HD V3 vscale(const V3& a, double s) { return v3(a.x * s, a.y * s, a.z * s); }
 HRG_HD bool veq(const V3& a, const V3& b) { return a.x == b.x && a.y == b.y && a.z == b.z; }  // RL point.hpp:93-99
 HRG_HD double vnorm(const V3& p) { return sqrt(p.x * p.x + p.y * p.y + p.z * p.z); }          // RL point.cpp:34-36
+// vnorm for operands that are often exactly zero (a resting link, two balls with one centre): the device sqrt sends 0
+// down its slow special-case path, lane by lane; sqrt(1) + a select of the exact result 0 stays on the fast path.
+HRG_HD double vnorm_z(const V3& p) {
+  const double s = p.x * p.x + p.y * p.y + p.z * p.z;
+  const double r = sqrt(s == 0.0 ? 1.0 : s);
+  return s == 0.0 ? 0.0 : r;
+}
 HRG_HD double vdot(const V3& a, const V3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }    // RL point.cpp:42-44
 HRG_HD V3 vcross(const V3& a, const V3& b) {                                                   // RL point.cpp:46-52
   return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
@@ -44,10 +51,29 @@ HRG_HD void cap_store(const Cap& k, double* c) {
   c[6] = k.r;
 }
 
+// Axis of a capsule: d = p2 - p1, its length and the unit vector d / |d| (NaN for a sphere, where it is never used).
+// Every distance routine below needs these of both capsules; k_reach_verify evaluates J x H pairs per env, so it
+// derives them once per link and once per human capsule instead of once per pair - same operations, same bits.
+struct Axis {
+  V3 d;
+  double mag;
+  V3 u;
+};
+HRG_HD Axis axis_of(const Cap& c) {
+  Axis a;
+  a.d = vsub(c.p2, c.p1);
+  a.mag = 0.0;
+  a.u = v3(0, 0, 0);
+  if (veq(c.p1, c.p2)) return a;  // sphere: no routine reads its axis, and 0 / 0 would only visit the slow division path
+  a.mag = vnorm(a.d);
+  a.u = v3(a.d.x / a.mag, a.d.y / a.mag, a.d.z / a.mag);
+  return a;
+}
+
 // point_line_segment_dist (RL/include/intersections.hpp:62-84)
-HRG_HD double point_segment_dist(const V3& p, const Cap& c) {
-  V3 se = vsub(c.p2, c.p1);
-  double dse = vnorm(se);
+HRG_HD double point_segment_dist(const V3& p, const Cap& c, const Axis& ax) {
+  const V3& se = ax.d;
+  double dse = ax.mag;
   double dsp = vnorm(vsub(p, c.p1));
   V3 ep = vsub(p, c.p2);
   double dep = vnorm(ep);
@@ -55,36 +81,47 @@ HRG_HD double point_segment_dist(const V3& p, const Cap& c) {
   if (sqrt(dse * dse + dsp * dsp) <= dep) return dsp;
   return vnorm(vcross(se, ep)) / dse;
 }
+HRG_HD double point_segment_dist(const V3& p, const Cap& c) { return point_segment_dist(p, c, axis_of(c)); }
 
-// min_segment_distance (RL/src/intersections.cpp:65-140), including the chained comparisons of the parallel branch:
-// `d0 <= 0 >= d1` parses as ((d0 <= 0) ? 1.0 : 0.0) >= d1, `d0 >= magA <= d1` as ((d0 >= magA) ? 1.0 : 0.0) <= d1.
-HRG_HD double min_segment_distance(const Cap& c1, const Cap& c2) {
-  V3 A = vsub(c1.p2, c1.p1);
-  V3 B = vsub(c2.p2, c2.p1);
-  double magA = vnorm(A), magB = vnorm(B);
-  V3 _A = v3(A.x / magA, A.y / magA, A.z / magA);
-  V3 _B = v3(B.x / magB, B.y / magB, B.z / magB);
+// The parallel-segments branch of min_segment_distance (RL/src/intersections.cpp:80-104), including its chained
+// comparisons: `d0 <= 0 >= d1` parses as ((d0 <= 0) ? 1.0 : 0.0) >= d1, `d0 >= magA <= d1` as
+// ((d0 >= magA) ? 1.0 : 0.0) <= d1. Rare (exactly parallel axes), so it stays a call.
+HRG_HD_CALL double parallel_segment_distance(const Cap& c1, const Axis& a1, const Cap& c2) {
+  const V3& _A = a1.u;
+  const double magA = a1.mag;
+  double d0 = vdot(_A, vsub(c2.p1, c1.p1));
+  double d1 = vdot(_A, vsub(c2.p2, c1.p1));
+  if (((d0 <= 0) ? 1.0 : 0.0) >= d1) {
+    if (fabs(d0) < fabs(d1)) return vnorm(vsub(c1.p1, c2.p1));
+    return vnorm(vsub(c1.p1, c2.p2));
+  } else if (((d0 >= magA) ? 1.0 : 0.0) <= d1) {
+    if (fabs(d0) < fabs(d1)) return vnorm(vsub(c1.p2, c2.p1));
+    return vnorm(vsub(c1.p2, c2.p2));
+  }
+  return vnorm(vsub(vadd(v3(_A.x * d0, _A.y * d0, _A.z * d0), c1.p1), c2.p1));
+}
+
+HRG_HD V3 vsel(bool k, const V3& a, const V3& b) { return v3(k ? a.x : b.x, k ? a.y : b.y, k ? a.z : b.z); }
+
+// min_segment_distance (RL/src/intersections.cpp:65-140). The clamping cascade of the reference (:112-137) is written
+// with selects: 32 envs share a warp and nearly every warp sees every case, so straight-line code that computes both
+// re-projections and keeps the one the reference would have taken is cheaper than the divergent branches. The values
+// selected are the ones the reference computes, operation for operation.
+HRG_HD double min_segment_distance(const Cap& c1, const Axis& a1, const Cap& c2, const Axis& a2) {
+  const V3& _A = a1.u;
+  const V3& _B = a2.u;
+  const double magA = a1.mag, magB = a2.mag;
   V3 cross = vcross(_A, _B);
   double nc = vnorm(cross);
   double denom = nc * nc;  // std::pow(norm, 2)
-  if (denom == 0) {
-    double d0 = vdot(_A, vsub(c2.p1, c1.p1));
-    double d1 = vdot(_A, vsub(c2.p2, c1.p1));
-    if (((d0 <= 0) ? 1.0 : 0.0) >= d1) {
-      if (fabs(d0) < fabs(d1)) return vnorm(vsub(c1.p1, c2.p1));
-      return vnorm(vsub(c1.p1, c2.p2));
-    } else if (((d0 >= magA) ? 1.0 : 0.0) <= d1) {
-      if (fabs(d0) < fabs(d1)) return vnorm(vsub(c1.p2, c2.p1));
-      return vnorm(vsub(c1.p2, c2.p2));
-    }
-    return vnorm(vsub(vadd(v3(_A.x * d0, _A.y * d0, _A.z * d0), c1.p1), c2.p1));
-  }
+  if (denom == 0) return parallel_segment_distance(c1, a1, c2);
   V3 t = vsub(c2.p1, c1.p1);
   double detA = vdet3(t, _B, cross);
   double detB = vdet3(t, _A, cross);
   double t0 = detA / denom, t1 = detB / denom;
   V3 pA = vadd(c1.p1, v3(_A.x * t0, _A.y * t0, _A.z * t0));
   V3 pB = vadd(c2.p1, v3(_B.x * t1, _B.y * t1, _B.z * t1));
+#ifdef HRG_BRANCHY_CLAMP
   if (t0 < 0)
     pA = c1.p1;
   else if (t0 > magA)
@@ -109,21 +146,44 @@ HRG_HD double min_segment_distance(const Cap& c1, const Cap& c2) {
       dot = magA;
     pA = vadd(c1.p1, v3(_A.x * dot, _A.y * dot, _A.z * dot));
   }
+#else
+  const bool a_lo = t0 < 0, a_hi = t0 > magA, a_out = a_lo || a_hi;
+  const bool b_lo = t1 < 0, b_hi = t1 > magB, b_out = b_lo || b_hi;
+  // if (t0 < 0) pA = p1A; else if (t0 > magA) pA = p2A; else if (t1 < 0) pB = p1B; else if (t1 > magB) pB = p2B;
+  pA = vsel(a_lo, c1.p1, vsel(a_hi, c1.p2, pA));
+  pB = vsel(!a_out && b_lo, c2.p1, vsel(!a_out && b_hi, c2.p2, pB));
+  {  // if (t0 < 0 || t0 > magA): project pA onto segment B
+    double dot = vdot(_B, vsub(pA, c2.p1));
+    dot = dot < 0 ? 0.0 : (dot > magB ? magB : dot);
+    pB = vsel(a_out, vadd(c2.p1, v3(_B.x * dot, _B.y * dot, _B.z * dot)), pB);
+  }
+  {  // if (t1 < 0 || t1 > magB): project pB onto segment A
+    double dot = vdot(_A, vsub(pB, c1.p1));
+    dot = dot < 0 ? 0.0 : (dot > magA ? magA : dot);
+    pA = vsel(b_out, vadd(c1.p1, v3(_A.x * dot, _A.y * dot, _A.z * dot)), pA);
+  }
+#endif
   return vnorm(vsub(pA, pB));
+}
+HRG_HD double min_segment_distance(const Cap& c1, const Cap& c2) {
+  return min_segment_distance(c1, axis_of(c1), c2, axis_of(c2));
 }
 
 // capsule_capsule_dist (RL/include/intersections.hpp:105-124); collision iff the result is < 0.0 (:129-131).
-HRG_HD double capsule_capsule_dist(const Cap& c1, const Cap& c2) {
+HRG_HD double capsule_capsule_dist(const Cap& c1, const Axis& a1, const Cap& c2, const Axis& a2) {
   bool s1 = veq(c1.p1, c1.p2), s2 = veq(c2.p1, c2.p2);
   if (s1 && s2) {
     V3 d = vsub(c1.p1, c2.p1);
     return vnorm(d) - c1.r - c2.r;
   } else if (s1 && !s2) {
-    return point_segment_dist(c1.p1, c2) - c1.r - c2.r;
+    return point_segment_dist(c1.p1, c2, a2) - c1.r - c2.r;
   } else if (!s1 && s2) {
-    return point_segment_dist(c2.p1, c1) - c1.r - c2.r;
+    return point_segment_dist(c2.p1, c1, a1) - c1.r - c2.r;
   }
-  return min_segment_distance(c1, c2) - c1.r - c2.r;
+  return min_segment_distance(c1, a1, c2, a2) - c1.r - c2.r;
+}
+HRG_HD double capsule_capsule_dist(const Cap& c1, const Cap& c2) {
+  return capsule_capsule_dist(c1, axis_of(c1), c2, axis_of(c2));
 }
 
 // ---- human occupancy models --------------------------------------------------------------------------------------
@@ -142,7 +202,7 @@ HRG_HD Ball ball_enclosure(const Ball& c1, const Ball& c2) {
     ri = c2.r; rj = c1.r; pi = c2.p; pj = c1.p;
   }
   V3 x = vsub(pi, pj);
-  double n = vnorm(x);
+  double n = vnorm_z(x);  // the Vel model encloses two balls with the SAME centre
   double alpha = fmax(ri - rj, n), beta = fmin(ri - rj, n);
   V3 pk = pj;
   if (!(n == 0.0)) pk = v3(pj.x + (x.x / n) * beta, pj.y + (x.y / n) * beta, pj.z + (x.z / n) * beta);

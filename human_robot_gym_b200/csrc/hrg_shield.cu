@@ -75,7 +75,7 @@ struct HrgShield {
   uint8_t* d_safe = nullptr;
   uint8_t* d_branch = nullptr;
   uint8_t* d_flags8 = nullptr;
-  size_t reach_smem = 0;
+  size_t reach_smem = 0, reach_smem_p0 = 0;
   size_t measure_smem = 0;
   // k_replan runs on its own stream, concurrently with the first reach + verify pass (envs that do not replan)
   cudaStream_t side = nullptr;
@@ -212,7 +212,10 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
 #undef AL
   h->reach_smem = (size_t)reach_smem_doubles(J, H) * sizeof(double);
   h->measure_smem = (size_t)kTileEnvs * ((K * 3) | 1) * sizeof(double);
-  cudaFuncSetAttribute(k_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
+  h->reach_smem_p0 = h->reach_smem;
+  if (const char* v = getenv("HRG_REACH_P0_SMEM_KB"))  // residency experiment: pad pass 0's shared memory (fewer blocks / SM)
+    if ((size_t)atoi(v) * 1024 > h->reach_smem_p0) h->reach_smem_p0 = (size_t)atoi(v) * 1024;
+  cudaFuncSetAttribute(k_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem_p0);
   cudaFuncSetAttribute(k_measure, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->measure_smem);
   {
     int lo = 0, hi = 0;  // the replan chain is the critical path of the tick: highest priority for its blocks
@@ -355,7 +358,7 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   }
   if (fork) {
     CK(cudaEventRecord(s->ev_join, s->side));
-    k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 0);
+    k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem_p0, st>>>(s->S, 0);
     CK(cudaStreamWaitEvent(st, s->ev_join, 0));
   } else {
     if (prof) cudaEventRecord(ev[2], st);

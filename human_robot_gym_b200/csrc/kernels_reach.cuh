@@ -13,6 +13,13 @@ namespace hrg {
 
 constexpr int kTileEnvs = 32;
 constexpr int kMeasureWarps = 8;
+constexpr int kHumDoubles = 11;
+#ifndef HRG_REACH_MINBLOCKS
+// 2 -> 112 registers, no spills, 3 resident blocks of J = 6 warps. 3 (80 registers, 4 blocks) is 6 % faster for pass 0 alone
+// but spills, and the spills lengthen the latency-bound pass 1 that sits on the tick's critical path (B200: 0.714 vs
+// 0.750 ms / tick).
+#define HRG_REACH_MINBLOCKS 2
+#endif
 
 // HumanReach::measurement (SS/src/human_reach.cc:52-74): vel = (new - old) * (1 / dt) when a previous measurement
 // exists and dt >= 1e-7; pos = new; last_meas = t. kp_in is the caller's [N][K][3] array; one block transposes a tile
@@ -57,13 +64,17 @@ __global__ void __launch_bounds__(kMeasureWarps * 32)
   }
 }
 
-// Shared-memory footprint of one 32-env tile, in doubles: sin/cos [2][J][2], link end points [2][J][2][3], human
-// capsules [H][7], each x 32 lanes. The per-link partial results of the final reduction reuse the sin/cos region.
-__host__ __device__ inline int reach_smem_doubles(int J, int H) { return (4 * J + 12 * J + 7 * H) * kTileEnvs; }
+// Shared-memory footprint of one 32-env tile, in doubles x 32 lanes: the kinematics scratch (sin/cos [2][J][2] + link end
+// points [2][J][2][3]) and the human capsules [H][kHumDoubles] (end points, radius, axis length, unit axis) are live at
+// different times and share one region, as do the per-link partial results of the final reduction.
+__host__ __device__ inline int reach_smem_doubles(int J, int H) {
+  const int kin = 4 * J + 12 * J, hum = kHumDoubles * H;
+  return (kin > hum ? kin : hum) * kTileEnvs;
+}
 
 // pass 0: every env of the batch except those marked for the second pass; pass 1: the envs on this tick's replan list
 // (their goal motion only exists once k_replan has run). Grid = ceil(N / 32) tiles, block = J warps.
-__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32) k_reach_verify(DevState S, int pass) {
+__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_REACH_MINBLOCKS) k_reach_verify(DevState S, int pass) {
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
   __shared__ unsigned bits_s[HRG_MAX_JOINTS][kTileEnvs];
@@ -91,7 +102,7 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32) k_reach_verify(DevState S
   const bool act = in_tile && (f & F_VERIFY);
   double* sc = smem;                          // [(ch * J + j) * 2 + {cos, sin}][32]
   double* P = sc + 4 * J * kTileEnvs;         // [((ch * J + i) * 2 + k) * 3 + r][32]
-  double* hum = P + 12 * J * kTileEnvs;       // [h * 7 + k][32]
+  double* hum = smem;                         // [h * 11 + k][32] (reuses sc / P once the link capsules are in registers)
   // ---- phase 0: sin / cos of joint w for the start and the goal configuration -------------------------------------
   if (w < J) {
     double sn, cs;
@@ -133,21 +144,12 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32) k_reach_verify(DevState S
       P[(((ch * J + i) * 2 + 1) * 3 + r) * kTileEnvs + lane] = r0 * lp[3] + r1 * lp[4] + r2 * lp[5] + r3;
     }
   }
-  // ---- phase 2: human capsules, capsule index h uniform per warp (HumanReach::humanReachabilityAnalysis) ------------
-  for (int h = w; h < H; h += NW) {
-    Cap hc;
-    hc.p1 = v3(0, 0, 0); hc.p2 = v3(0, 0, 1); hc.r = 0;
-    if (act) hc = human_capsule(c, h, S.kp_pos + e, S.kp_vel + e, (size_t)N, t_reach);
-    double* o = hum + (size_t)h * 7 * kTileEnvs + lane;
-    o[0 * kTileEnvs] = hc.p1.x; o[1 * kTileEnvs] = hc.p1.y; o[2 * kTileEnvs] = hc.p1.z;
-    o[3 * kTileEnvs] = hc.p2.x; o[4 * kTileEnvs] = hc.p2.y; o[5 * kTileEnvs] = hc.p2.z;
-    o[6 * kTileEnvs] = hc.r;
-    if (act && S.human_caps) cap_store(hc, S.human_caps + ((size_t)e * H + h) * 7);
-  }
   __syncthreads();
-  // ---- phase 3: swept capsule of link w (RobotReach::reach, robot_reach.cc:61-98) -----------------------------------
+  // ---- phase 2: swept capsule of link w into registers (RobotReach::reach, robot_reach.cc:61-98) ---------------------
   unsigned my_bits = 0;
   double m0 = INFINITY, m1 = INFINITY, m2 = INFINITY;
+  Cap rc;
+  rc.p1 = v3(0, 0, 0); rc.p2 = v3(0, 0, 0); rc.r = 0;
   if (w < J) {
     const double* b = P + ((0 * J + w) * 2) * 3 * kTileEnvs + lane;  // before: p1 xyz, p2 xyz
     const double* a = P + ((1 * J + w) * 2) * 3 * kTileEnvs + lane;  // after
@@ -160,22 +162,46 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32) k_reach_verify(DevState S
     const double alpha = act ? ri_at(S, 2 * J + w, e) : 0.0;
     const double rl = c.link_caps[w][6];
     const double grow = alpha * s_diff * s_diff / 8.0;
-    const double r_1 = vnorm(v3(bp[0] - ap[0], bp[1] - ap[1], bp[2] - ap[2])) / 2.0 + grow + rl;
-    const double r_2 = vnorm(v3(bp[3] - ap[3], bp[4] - ap[4], bp[5] - ap[5])) / 2.0 + grow + rl;
-    Cap rc;
+    const double r_1 = vnorm_z(v3(bp[0] - ap[0], bp[1] - ap[1], bp[2] - ap[2])) / 2.0 + grow + rl;  // 0 for a resting link
+    const double r_2 = vnorm_z(v3(bp[3] - ap[3], bp[4] - ap[4], bp[5] - ap[5])) / 2.0 + grow + rl;
     rc.p1 = v3((bp[0] + ap[0]) * 0.5, (bp[1] + ap[1]) * 0.5, (bp[2] + ap[2]) * 0.5);
     rc.p2 = v3((bp[3] + ap[3]) * 0.5, (bp[4] + ap[4]) * 0.5, (bp[5] + ap[5]) * 0.5);
     rc.r = fmax(r_1, r_2) + c.secure_radius;
     if (act && S.robot_caps) cap_store(rc, S.robot_caps + ((size_t)e * J + w) * 7);
+  }
+  __syncthreads();  // sc / P are dead: the human capsules take their place
+  // ---- phase 3: human capsules, capsule index h uniform per warp (HumanReach::humanReachabilityAnalysis) ------------
+  for (int h = w; h < H; h += NW) {
+    Cap hc;
+    hc.p1 = v3(0, 0, 0); hc.p2 = v3(0, 0, 1); hc.r = 0;
+    if (act) hc = human_capsule(c, h, S.kp_pos + e, S.kp_vel + e, (size_t)N, t_reach);
+    Axis ha;  // once per human capsule instead of once per (link, capsule) pair
+    ha.mag = 0.0; ha.u = v3(0, 0, 0);
+    if (act) ha = axis_of(hc);
+    double* o = hum + (size_t)h * kHumDoubles * kTileEnvs + lane;
+    o[0 * kTileEnvs] = hc.p1.x; o[1 * kTileEnvs] = hc.p1.y; o[2 * kTileEnvs] = hc.p1.z;
+    o[3 * kTileEnvs] = hc.p2.x; o[4 * kTileEnvs] = hc.p2.y; o[5 * kTileEnvs] = hc.p2.z;
+    o[6 * kTileEnvs] = hc.r;
+    o[7 * kTileEnvs] = ha.mag;
+    o[8 * kTileEnvs] = ha.u.x; o[9 * kTileEnvs] = ha.u.y; o[10 * kTileEnvs] = ha.u.z;
+    if (act && S.human_caps) cap_store(hc, S.human_caps + ((size_t)e * H + h) * 7);
+  }
+  __syncthreads();
+  if (w < J && act) {  // lanes without an env to verify sit the loop out (dummy operands would visit slow paths)
     // ---- phase 4: link w against every human capsule (VerifyISO::verify_human_reach, verify_iso.cc:5-33) -----------
     const int E = c.n_ext, B = c.n_bodies;
+    const Axis ra = axis_of(rc);
     for (int h = 0; h < H; ++h) {
-      const double* hp = hum + (size_t)h * 7 * kTileEnvs + lane;
+      const double* hp = hum + (size_t)h * kHumDoubles * kTileEnvs + lane;
       Cap hc;
       hc.p1 = v3(hp[0 * kTileEnvs], hp[1 * kTileEnvs], hp[2 * kTileEnvs]);
       hc.p2 = v3(hp[3 * kTileEnvs], hp[4 * kTileEnvs], hp[5 * kTileEnvs]);
       hc.r = hp[6 * kTileEnvs];
-      const double d = capsule_capsule_dist(rc, hc);
+      Axis ha;
+      ha.d = vsub(hc.p2, hc.p1);
+      ha.mag = hp[7 * kTileEnvs];
+      ha.u = v3(hp[8 * kTileEnvs], hp[9 * kTileEnvs], hp[10 * kTileEnvs]);
+      const double d = capsule_capsule_dist(rc, ra, hc, ha);
       const int m = h < E ? 0 : (h - E < B ? 1 : 2);  // warp-uniform
       if (d < 0.0) my_bits |= 1u << m;
       if (fabs(d) < 1e-6) my_bits |= 8u;
@@ -184,7 +210,7 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32) k_reach_verify(DevState S
       else m2 = fmin(m2, d);
     }
   }
-  __syncthreads();  // sc / P are dead from here on: reuse sc for the per-link partial minima
+  __syncthreads();  // the human capsules are dead from here on: reuse the region for the per-link partial minima
   if (w < J) {
     sc[(w * 3 + 0) * kTileEnvs + lane] = m0;
     sc[(w * 3 + 1) * kTileEnvs + lane] = m1;

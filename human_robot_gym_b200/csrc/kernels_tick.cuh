@@ -475,11 +475,12 @@ __global__ void k_stage_plan_safety_shield(double ts, int n, const double* __res
 
 __global__ void k_stage_ltp_plan(const HrgConfig* __restrict__ cfg, int n, const double* goal, const double* q0,
                                  const double* v0, const double* a0, double* traj, int32_t* length, int cap) {
+  __shared__ double mat_s[64][37];  // launched with 64 threads per block
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int J = cfg->nb_joints;
   length[i] = ltp_plan_env_seq(*cfg, goal + (size_t)i * J, q0 + (size_t)i * J, v0 + (size_t)i * J, a0 + (size_t)i * J,
-                               traj + (size_t)i * cap * 4 * J, cap);
+                               traj + (size_t)i * cap * 4 * J, cap, mat_s[threadIdx.x]);
 }
 
 }  // namespace hrg

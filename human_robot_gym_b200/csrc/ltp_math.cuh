@@ -215,9 +215,16 @@ HRG_HD void real_schur_hessenberg(SmallMat& T) {
 // roots() + getSmallestPositiveNonComplexRoot (roots.h:22-50): coef[0] is the leading coefficient, ncoef = degree+1.
 // Returns +inf if there is no real root > 1e-7.
 HRG_HD_CALL double smallest_positive_real_root(const LtpLimits& L, const double* coef, int ncoef) {
-  double local_mat[36];
   SmallMat C;
+#if defined(__CUDA_ARCH__)
+  // every device caller hands in per-lane shared-memory scratch; telling the compiler so turns the matrix accesses of the
+  // QR sweeps from generic loads (long-scoreboard latency) into LDS / STS
+  C.a = L.mat;
+  __builtin_assume(__isShared(C.a));
+#else
+  double local_mat[36];
   C.a = L.mat ? L.mat : local_mat;
+#endif
   const int n = ncoef - 1;
   C.n = n;
   for (int i = 0; i < 36; ++i) C.a[i] = 0.0;

@@ -206,13 +206,15 @@ __device__ __forceinline__ double ltp_sample_joint_warp(const LtpLimits& L, cons
 // Sequential planTrajectory for one env (:7-63) — used where one thread owns a whole env (host tests, stage entry);
 // the replan kernel runs the same per-joint calls with one lane per joint. traj layout [len][4][J].
 // Returns the trajectory length, 0 on failure, -len if len > cap (nothing is written then).
+// `mat`: 36 doubles of root-finder scratch (shared memory on the device, optional on the host).
 HRG_HD int ltp_plan_env_seq(const HrgConfig& c, const double* q_goal, const double* q_0, const double* v_0,
-                            const double* a_0, double* traj, int cap) {
+                            const double* a_0, double* traj, int cap, double* mat = nullptr) {
   const int J = c.nb_joints;
   JointPlan opt[HRG_MAX_JOINTS], sc[HRG_MAX_JOINTS];
   LtpLimits L[HRG_MAX_JOINTS];
   for (int j = 0; j < J; ++j) {
     L[j].v_max = c.v_max[j]; L[j].a_max = c.a_max_ltt[j]; L[j].j_max = c.j_max_ltt[j]; L[j].t_sample = c.sample_time;
+    L[j].mat = mat;
     if (!ltp_check_inputs_joint(L[j], c.q_min[j], c.q_max[j], q_0[j], v_0[j], a_0[j])) return 0;
   }
   for (int j = 0; j < J; ++j) {

@@ -69,3 +69,13 @@ for i in range(n):
     tot[1] += data[i][1]
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
     print(f"{k:55s} inst={v[0]/1e6:8.2f}M share={v[0]/max(tot[0],1):.3f} stall-samples={v[1]/max(tot[1],1):.3f}")
+if len(sys.argv) > 5:  # per source line detail: python sass_lines.py dump cubin kernel top by_line
+    agl = collections.defaultdict(lambda: [0, 0])
+    for i in range(n):
+        fl = lines[i]
+        k = (fl[0].split("/")[-1], fl[1]) if fl else ("?", 0)
+        agl[k][0] += data[i][0]
+        agl[k][1] += data[i][1]
+    print("--- by source line")
+    for k, v in sorted(agl.items(), key=lambda kv: -kv[1][0])[:top]:
+        print(f"{k[0]}:{k[1]:<5d} inst={v[0]/1e6:8.2f}M share={v[0]/max(tot[0],1):.3f} stall-samples={v[1]/max(tot[1],1):.3f}")
