@@ -66,9 +66,6 @@ enum { CTR_OPT = 0, CTR_SCALE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, N_CTR = 4 }
 #ifndef HRG_G_ENVS
 #define HRG_G_ENVS 4  // envs (8-lane groups) per warp in k_replan_plan
 #endif
-#ifndef HRG_G_DEEP
-#define HRG_G_DEEP 3
-#endif
 
 // Fetches G consecutive tasks for the warp; lane l < G gets task base + l (or >= ntask when the list is exhausted).
 template <int G>
@@ -185,23 +182,32 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_p
   }
 }
 
+// One (deep-list slot, polynomial candidate 2..7) task per 8-lane group, 4 groups per warp. The 8 lanes run the task's
+// scalar code redundantly (identical inputs, identical results) and share every eigen-solve of it - the candidate's own
+// polynomial and those inside optSwitchTimes - through the cooperative root finder (ltp_math.cuh).
 __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_deep(DevState S) {
-  __shared__ double mat_s[kReplanBlock / 32][HRG_G_DEEP][37];
+  __shared__ double mat_s[kReplanBlock / 32][4][37];
   const HrgConfig& c = *S.cfg;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int gl = lane & 7, grp = lane >> 3;
   const int J = S.J, N = S.N;
   const int ntask = S.replan_ctr[CTR_DEEP_COUNT] * 6;
   for (;;) {
-    const int dt = fetch_tasks<HRG_G_DEEP>(S.replan_ctr + CTR_DEEP, lane);
-    if (__shfl_sync(0xffffffffu, dt, 0) >= ntask) break;
-    if (lane >= HRG_G_DEEP || dt >= ntask) continue;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(S.replan_ctr + CTR_DEEP, 4);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= ntask) break;
+    const int dt = base + grp;
+    if (dt >= ntask) continue;  // whole 8-lane groups leave together
     const int slot = dt / 6, cand = 2 + (dt - slot * 6);
     const int task = S.deep_list[slot];
     const int idx = task / J, j = task - idx * J;
     const int e = S.replan_list[idx];
     const PlanHead h = S.plan_head[idx];
     const PlanRec opt = S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j];
-    const LtpLimits L = joint_limits(c, j, mat_s[wib][lane]);
+    LtpLimits L = joint_limits(c, j, mat_s[wib][grp]);
+    L.coop_mask = 0xFFu << (lane & 24);
+    L.coop_lane = gl;
     double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
     const double q_goal = S.goal_q[(size_t)j * N + e];
     if (opt.dir < 0) {
@@ -218,7 +224,7 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_d
     ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, opt.dir, h.t_required, A, ncoef);
     r.v_drive = ltp_scaling_vdrive(L, cand, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
     r.len = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, r.v_drive, h.t_required, r.T, r.mod) ? 1 : 0;
-    S.deep_res[(size_t)slot * 6 + (cand - 2)] = r;
+    if (gl == 0) S.deep_res[(size_t)slot * 6 + (cand - 2)] = r;
   }
 }
 
