@@ -349,7 +349,8 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
     int sgrid = grid_for(N * s->S.J, kReplanBlock / 32);
     const int per_sm = fork ? s->replan_blocks_per_sm : HRG_REPLAN_MINBLOCKS;
     if (sgrid > s->sm_count * per_sm) sgrid = s->sm_count * per_sm;
-    k_replan_plan<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_opt<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_scale<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     k_replan_deep<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     if (s->pfl)
       k_replan_sample<true><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
@@ -368,7 +369,7 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   if (prof) cudaEventRecord(ev[3], st);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
   if (prof) cudaEventRecord(ev[4], st);
-  s->launches += 7;
+  s->launches += 8;
   CK(cudaGetLastError());
   return HRG_OK;
 }

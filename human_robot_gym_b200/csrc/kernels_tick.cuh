@@ -44,37 +44,27 @@ constexpr int kReplanBlock = 64;
 // companion-matrix eigenvalue solve, each followed by an optSwitchTimes trial that may solve two more quartics). The
 // whole batch only holds a few thousand such problems per tick, so the kernel time is the LONGEST dependent chain, not
 // the instruction total: lanes that diverge serialise, and a warp that walks the whole ladder is the tail everybody
-// waits for. Hence the unit of scheduling is as small as the reference's data flow allows:
-//   k_replan_plan    8 lanes per env, 4 envs per warp    checkInputs + optSwitchTimes (:20-37); slowest joint ->
-//                                                        t_required; the two closed-form timeScaling candidates
-//                                                        (:378-436); joints that need the polynomial candidates go
-//                                                        on the `deep` list
-//   k_replan_deep    1 warp per (deep joint, candidate)  the six polynomial candidates (:449-629), all evaluated; the
+// waits for. Hence the unit of scheduling is as small as the reference's data flow allows, and every problem gets an
+// 8-lane group whose lanes split the eigen-solves (see kGroupLanes):
+//   k_replan_opt     1 group per (env, joint)            checkInputs + optSwitchTimes (:20-37)
+//   k_replan_scale   1 group per (env, joint)            slowest joint -> t_required (:39-45); the two closed-form
+//                                                        timeScaling candidates (:378-436); joints that need the
+//                                                        polynomial candidates go on the `deep` list
+//   k_replan_deep    1 group per (deep joint, candidate) the six polynomial candidates (:449-629), all evaluated; the
 //                                                        first accepted one in the reference's order is taken later,
 //                                                        which is what its sequential ladder returns
 //   k_replan_sample  1 warp per env                      getTrajectory (:706-841), joint-limit test (:59-61), LTT
 //                                                        install, and the rest of the env's step up to reach / verify.
-// Work is fetched from device counters (S.replan_ctr); grids only bound residency. How many independent problems share
-// a warp is a measured trade-off (profiles/r01_replan_packing.md): one per warp has the shortest chains but is
-// instruction-fetch bound, many per warp serialise where they diverge.
+// Work is fetched from device counters (S.replan_ctr); grids only bound residency.
 enum { CTR_OPT = 0, CTR_SCALE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, N_CTR = 4 };
 
-// Lanes per warp that carry a task in the three planning kernels. 1 = one problem per warp (shortest chains, but every
-// warp instruction is fetched for a single lane and the kernels become instruction-fetch bound); larger = several
-// independent problems share a warp and the instructions they have in common, at the price of serialising where they
-// diverge. Measured on B200 (profiles/r01_replan_packing.md).
-#ifndef HRG_G_ENVS
-#define HRG_G_ENVS 4  // envs (8-lane groups) per warp in k_replan_plan
-#endif
+// Task packing of the planning kernels: one (env, joint[, candidate]) problem per 8-lane group, four groups per warp.
+// The 8 lanes of a group run the problem's scalar code redundantly (identical inputs, identical results) and share each
+// of its eigen-solves through the cooperative root finder (ltp_math.cuh). Earlier packings - one problem per lane with
+// 1..32 problems per warp - are in profiles/r01_replan_packing.md: one problem per warp had the shortest chains but was
+// instruction-fetch bound, many per warp serialised on divergent QR iteration counts.
+constexpr int kGroupLanes = 8, kGroupsPerWarp = 4;
 
-// Fetches G consecutive tasks for the warp; lane l < G gets task base + l (or >= ntask when the list is exhausted).
-template <int G>
-__device__ __forceinline__ int fetch_tasks(int32_t* ctr, int lane) {
-  int base = 0;
-  if (lane == 0) base = atomicAdd(ctr, G);
-  base = __shfl_sync(0xffffffffu, base, 0);
-  return base + (lane < G ? lane : 0);
-}
 __device__ __forceinline__ LtpLimits joint_limits(const HrgConfig& c, int j, double* mat) {
   LtpLimits L;
   L.v_max = c.v_max[j]; L.a_max = c.a_max_ltt[j]; L.j_max = c.j_max_ltt[j]; L.t_sample = c.sample_time;
@@ -97,43 +87,76 @@ __device__ __forceinline__ void finish_scaled(const LtpLimits& L, const PlanRec&
   sc.len = ltp_joint_len(L, P);
 }
 
-// HRG_G_ENVS envs per warp, 8 lanes per env: lane j of a group plans joint j (lanes >= J shadow joint J-1 and never
-// write). Because the joints of an env sit in one group, the slowest joint is a width-8 shuffle away and the two
-// closed-form timeScaling candidates follow at once, without a kernel boundary.
-__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_plan(DevState S) {
-  __shared__ double mat_s[kReplanBlock / 32][HRG_G_ENVS * 8][37];
+// Fetches the next four tasks of counter `ctr` for the warp: group g gets base + g. Returns -1 for the whole warp when
+// the list is exhausted, -2 for a group beyond its end (whole 8-lane groups leave together).
+__device__ __forceinline__ int fetch_group_task(int32_t* ctr, int ntask, int lane) {
+  int base = 0;
+  if (lane == 0) base = atomicAdd(ctr, kGroupsPerWarp);
+  base = __shfl_sync(0xffffffffu, base, 0);
+  if (base >= ntask) return -1;
+  const int t = base + (lane >> 3);
+  return t < ntask ? t : -2;
+}
+__device__ __forceinline__ LtpLimits group_limits(const HrgConfig& c, int j, double* mat, int lane) {
+  LtpLimits L = joint_limits(c, j, mat);
+  L.coop_mask = 0xFFu << (lane & 24);
+  L.coop_lane = lane & 7;
+  return L;
+}
+
+// checkInputs + optSwitchTimes (planTrajectory :20-37) of one (replanning env, joint) per group.
+__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_opt(DevState S) {
+  __shared__ double mat_s[kReplanBlock / 32][kGroupsPerWarp][37];
   const HrgConfig& c = *S.cfg;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int gl = lane & 7, grp = lane >> 3;
-  const unsigned gmask = 0xFFu << (lane & 24);
   const int J = S.J, N = S.N;
-  const int count = *S.replan_count;
-  const int j = gl < J ? gl : J - 1;
-  const bool writer = gl < J;
+  const int ntask = *S.replan_count * J;
   for (;;) {
-    int base = 0;
-    if (lane == 0) base = atomicAdd(S.replan_ctr + CTR_OPT, HRG_G_ENVS);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= count) break;
-    const int idx = base + grp;
-    if (grp >= HRG_G_ENVS || idx >= count) continue;  // whole 8-lane groups leave together
+    const int task = fetch_group_task(S.replan_ctr + CTR_OPT, ntask, lane);
+    if (task == -1) break;
+    if (task < 0) continue;
+    const int idx = task / J, j = task - idx * J;
     const int e = S.replan_list[idx];
-    const LtpLimits L = joint_limits(c, j, mat_s[wib][lane]);
-    double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
+    const LtpLimits L = group_limits(c, j, mat_s[wib][grp], lane);
+    const double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
     const double q_goal = S.goal_q[(size_t)j * N + e];
     PlanRec opt;
     ltp_zero7(opt.T);
     opt.dir = 0.0; opt.v_drive = L.v_max; opt.mod = 0; opt.len = 0;
-    // checkInputs + optSwitchTimes (:20-37); the reference stops at the first joint that fails
     bool ok = ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0);
     if (ok) ok = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, opt.T, opt.dir, opt.mod);
-    ok = (__ballot_sync(gmask, ok) & gmask) == gmask;
-    // slowest joint (:39-45)
+    opt.len = ok ? 1 : 0;
+    if (gl == 0) S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j] = opt;
+  }
+}
+
+// Slowest joint of the env (:39-45, every group of the env derives it from the J records of k_replan_opt) and the two
+// closed-form timeScaling candidates of this group's joint (:378-436); a joint that accepts neither goes on the deep
+// list. The reference stops at the first joint whose checkInputs / optSwitchTimes fails: ok = all joints ok.
+__global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_scale(DevState S) {
+  __shared__ double mat_s[kReplanBlock / 32][kGroupsPerWarp][37];
+  const HrgConfig& c = *S.cfg;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int gl = lane & 7, grp = lane >> 3;
+  const int J = S.J, N = S.N;
+  const int ntask = *S.replan_count * J;
+  for (;;) {
+    const int task = fetch_group_task(S.replan_ctr + CTR_SCALE, ntask, lane);
+    if (task == -1) break;
+    if (task < 0) continue;
+    const int idx = task / J, j = task - idx * J;
+    const int e = S.replan_list[idx];
+    const LtpLimits L = group_limits(c, j, mat_s[wib][grp], lane);
+    const PlanRec* rec = S.plan_opt + (size_t)idx * HRG_MAX_JOINTS;
+    PlanRec opt = rec[j];
     PlanHead h;
     h.t_required = -1;
     h.slowest = -1;
+    bool ok = true;
     for (int k = 0; k < J; ++k) {
-      const double tk = __shfl_sync(gmask, opt.T[6], k, 8);
+      const double tk = rec[k].T[6];
+      ok = ok && rec[k].len != 0;
       if (tk > h.t_required) {
         h.t_required = tk;
         h.slowest = k;
@@ -144,6 +167,8 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_p
     opt.len = h.ok;
     PlanRec sc = opt;
     if (ok) {
+      double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
+      const double q_goal = S.goal_q[(size_t)j * N + e];
       double T[7];
       ltp_zero7(T);
       double v_drive = L.v_max;
@@ -156,7 +181,7 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_p
         }
         const double v_orig = opt.dir * v_0, a_orig = opt.dir * a_0;
         bool acc = false;
-        for (int cand = 0; cand < 2 && !acc; ++cand) {  // the closed-form candidates (:378-436)
+        for (int cand = 0; cand < 2 && !acc; ++cand) {
           double A[7];
           int ncoef;
           v_drive = ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, opt.dir, h.t_required, A, ncoef);
@@ -165,7 +190,7 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_p
         deep = !acc;
       }
       if (deep) {
-        if (writer) {
+        if (gl == 0) {
           const int slot = atomicAdd(S.replan_ctr + CTR_DEEP_COUNT, 1);
           S.deep_list[slot] = idx * J + j;
           sc.len = -(slot + 1);
@@ -174,11 +199,10 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_p
         finish_scaled(L, opt, T, v_drive, mod, sc);
       }
     }
-    if (writer) {
-      S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j] = opt;
+    if (gl == 0) {
       S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j] = sc;
+      if (j == 0) S.plan_head[idx] = h;
     }
-    if (gl == 0) S.plan_head[idx] = h;
   }
 }
 

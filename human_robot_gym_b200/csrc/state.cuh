@@ -76,8 +76,8 @@ struct DevState {
   int32_t* replan_list;   // [N]
   int32_t* replan_count;  // [1]
   int32_t* replan_ctr;    // [4] work counters of the replan kernels + length of the deep list (kernels_tick.cuh CTR_*)
-  PlanRec* plan_opt;      // [N][HRG_MAX_JOINTS] time-optimal plan per joint (k_replan_plan); len = planTrajectory still ok
-  PlanRec* plan_sc;       // [N][HRG_MAX_JOINTS] plan scaled to the slowest joint (k_replan_plan / k_replan_sample); len < 0 = -(deep slot + 1)
+  PlanRec* plan_opt;      // [N][HRG_MAX_JOINTS] time-optimal plan per joint (k_replan_opt); len = this joint ok
+  PlanRec* plan_sc;       // [N][HRG_MAX_JOINTS] plan scaled to the slowest joint (k_replan_scale / k_replan_sample); len < 0 = -(deep slot + 1)
   PlanHead* plan_head;    // [N]
   int32_t* deep_list;     // [N * J] (env, joint) tasks whose closed-form timeScaling candidates were rejected
   PlanRec* deep_res;      // [N * J][6] result of each polynomial candidate; len = accepted
