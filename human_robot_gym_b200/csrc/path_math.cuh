@@ -13,9 +13,14 @@
 // k_replan up to 82k SASS instructions (1.3 MB) and 36 % of its stall samples were instruction-cache misses
 // (profiles/r01_ncu_summary.md).
 #define HRG_HD_CALL __host__ __device__ __noinline__
+// Per-joint loops that only LOAD (or only compute) run over the compile-time bound with a `j < J` guard so that they
+// unroll: the thread-per-env kernels are bound by the latency of dependent global loads, and an unrolled loop has all of
+// its loads in flight at once instead of one round trip per joint.
+#define HRG_UNROLL _Pragma("unroll")
 #else
 #define HRG_HD inline
 #define HRG_HD_CALL inline
+#define HRG_UNROLL
 #endif
 
 namespace hrg {

@@ -126,9 +126,17 @@ HRG_HD void ltt_interpolate(const DevState& S, const HrgConfig& c, int e, int sl
              S.ltt_cur[(size_t)slot * S.N + e], sample, dt);
   const double* m = ltt_sample(S, e, slot, sample);
   const int J = S.J;
-  for (int j = 0; j < J; ++j)
-    ltt_interp_joint(m[j], m[J + j], m[2 * J + j], m[3 * J + j], dt, ds, dds, ddds, c.v_max[j], c.a_max[j], q[j],
-                     dq[j], ddq[j], dddq[j]);
+  double m0[HRG_MAX_JOINTS], m1[HRG_MAX_JOINTS], m2[HRG_MAX_JOINTS], m3[HRG_MAX_JOINTS];
+  HRG_UNROLL
+  for (int j = 0; j < HRG_MAX_JOINTS; ++j)
+    if (j < J) {
+      m0[j] = m[j]; m1[j] = m[J + j]; m2[j] = m[2 * J + j]; m3[j] = m[3 * J + j];
+    }
+  HRG_UNROLL
+  for (int j = 0; j < HRG_MAX_JOINTS; ++j)
+    if (j < J)
+      ltt_interp_joint(m0[j], m1[j], m2[j], m3[j], dt, ds, dds, ddds, c.v_max[j], c.a_max[j], q[j], dq[j], ddq[j],
+                       dddq[j]);
 }
 
 }  // namespace hrg

@@ -57,7 +57,9 @@ HRG_HD void potential_env(const DevState& S, const HrgConfig& c, int e, uint32_t
   }
   // :391-398
   double prev[HRG_MAX_JOINTS];
-  for (int j = 0; j < J; ++j) prev[j] = S.prev_dq[(size_t)j * N + e];
+  HRG_UNROLL
+  for (int j = 0; j < HRG_MAX_JOINTS; ++j)
+    if (j < J) prev[j] = S.prev_dq[(size_t)j * N + e];
   double a_man, j_man;
   max_acc_jerk(prev, c, a_man, j_man);
   // :402-407 plan a recovery path unless already on it
@@ -135,13 +137,23 @@ HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uin
       f |= (uint32_t)HRG_ST_JOINT_LIMIT << F_STATUS_SHIFT;
     } else {
       f |= F_VERIFY;
-      for (int j = 0; j < J; ++j) {
-        ri_at(S, j, e) = cur_at(S, j, e);
-        ri_at(S, J + j, e) = gq[j];
-        ri_at(S, 2 * J + j, e) = S.ltt_alpha[((size_t)gslot * J + j) * N + e];  // getAlphaI() (:606-610)
-      }
-      ri_at(S, 3 * J, e) = s_d - cur_at(S, 4 * J, e);          // goal_motion.getS() - current_motion.getS()
-      ri_at(S, 3 * J + 1, e) = t - S.last_meas[e] + t_brake;   // human_reach.cc:79
+      double cq[HRG_MAX_JOINTS], al[HRG_MAX_JOINTS];  // all loads first: a store in between would serialise them
+      HRG_UNROLL
+      for (int j = 0; j < HRG_MAX_JOINTS; ++j)
+        if (j < J) {
+          cq[j] = cur_at(S, j, e);
+          al[j] = S.ltt_alpha[((size_t)gslot * J + j) * N + e];  // getAlphaI() (:606-610)
+        }
+      const double cur_s = cur_at(S, 4 * J, e), last = S.last_meas[e];
+      HRG_UNROLL
+      for (int j = 0; j < HRG_MAX_JOINTS; ++j)
+        if (j < J) {
+          ri_at(S, j, e) = cq[j];
+          ri_at(S, J + j, e) = gq[j];
+          ri_at(S, 2 * J + j, e) = al[j];
+        }
+      ri_at(S, 3 * J, e) = s_d - cur_s;             // goal_motion.getS() - current_motion.getS()
+      ri_at(S, 3 * J + 1, e) = t - last + t_brake;  // human_reach.cc:79
     }
   } else {
     f |= F_IS_SAFE;
