@@ -215,7 +215,8 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   h->reach_smem_p0 = h->reach_smem;
   if (const char* v = getenv("HRG_REACH_P0_SMEM_KB"))  // residency experiment: pad pass 0's shared memory (fewer blocks / SM)
     if ((size_t)atoi(v) * 1024 > h->reach_smem_p0) h->reach_smem_p0 = (size_t)atoi(v) * 1024;
-  cudaFuncSetAttribute(k_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem_p0);
+  cudaFuncSetAttribute(k_reach_verify<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem_p0);
+  cudaFuncSetAttribute(k_reach_verify<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
   cudaFuncSetAttribute(k_measure, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->measure_smem);
   {
     int lo = 0, hi = 0;  // the replan chain is the critical path of the tick: highest priority for its blocks
@@ -359,13 +360,13 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   }
   if (fork) {
     CK(cudaEventRecord(s->ev_join, s->side));
-    k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem_p0, st>>>(s->S, 0);
+    k_reach_verify<1><<<tile_grid(N), 32 * s->S.J, s->reach_smem_p0, st>>>(s->S, 0);
     CK(cudaStreamWaitEvent(st, s->ev_join, 0));
   } else {
     if (prof) cudaEventRecord(ev[2], st);
-    k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 0);
+    k_reach_verify<1><<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 0);
   }
-  k_reach_verify<<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 1);
+  k_reach_verify<2><<<tile_grid(N), 32 * s->S.J * 2, s->reach_smem, st>>>(s->S, 1);
   if (prof) cudaEventRecord(ev[3], st);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
   if (prof) cudaEventRecord(ev[4], st);

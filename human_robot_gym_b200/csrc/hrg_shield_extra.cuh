@@ -233,9 +233,9 @@ int hrg_stage_reach_verify(const HrgConfig* cfg, int n, const double* base_pose,
   cudaError_t ce = cudaMemcpyAsync(d, cfg, sizeof(HrgConfig), cudaMemcpyHostToDevice, st);
   if (ce == cudaSuccess) {
     const size_t smem = (size_t)reach_smem_doubles(J, H) * sizeof(double);
-    cudaFuncSetAttribute(k_reach_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_reach_verify<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k_stage_pack<<<grid_for(n, 128), 128, 0, st>>>(S, base_pose, q_start, q_goal, s_diff, t_reach, alpha_i, kp_pos, kp_vel);
-    k_reach_verify<<<tile_grid(n), 32 * J, smem, st>>>(S, 0);
+    k_reach_verify<1><<<tile_grid(n), 32 * J, smem, st>>>(S, 0);
     k_stage_unpack<<<grid_for(n, 128), 128, 0, st>>>(S, min_dist, is_safe);
     ce = cudaStreamSynchronize(st);
   }

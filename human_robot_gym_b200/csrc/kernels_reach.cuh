@@ -73,11 +73,16 @@ __host__ __device__ inline int reach_smem_doubles(int J, int H) {
 }
 
 // pass 0: every env of the batch except those marked for the second pass; pass 1: the envs on this tick's replan list
-// (their goal motion only exists once k_replan has run). Grid = ceil(N / 32) tiles, block = J warps.
-__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_REACH_MINBLOCKS) k_reach_verify(DevState S, int pass) {
+// (their goal motion only exists once k_replan has run). Grid = ceil(N / 32) tiles, block = J * PARTS warps: warp w works
+// on link w % J and takes every PARTS-th human capsule. PARTS = 1 is the throughput shape of pass 0 (thousands of tiles);
+// pass 1 only has a few dozen tiles - less than one per SM - and sits on the tick's critical path, so it runs with
+// PARTS = 2 and halves the dependent chain of a tile instead.
+template <int PARTS>
+__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS, PARTS == 1 ? HRG_REACH_MINBLOCKS : 1)
+    k_reach_verify(DevState S, int pass) {
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
-  __shared__ unsigned bits_s[HRG_MAX_JOINTS][kTileEnvs];
+  __shared__ unsigned bits_s[HRG_MAX_JOINTS * PARTS][kTileEnvs];
   const int J = S.J, H = S.H, N = S.N;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NW = blockDim.x >> 5;
   int e = blockIdx.x * kTileEnvs + lane;
@@ -150,24 +155,25 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_REACH_MINBLOCKS) k_re
   double m0 = INFINITY, m1 = INFINITY, m2 = INFINITY;
   Cap rc;
   rc.p1 = v3(0, 0, 0); rc.p2 = v3(0, 0, 0); rc.r = 0;
-  if (w < J) {
-    const double* b = P + ((0 * J + w) * 2) * 3 * kTileEnvs + lane;  // before: p1 xyz, p2 xyz
-    const double* a = P + ((1 * J + w) * 2) * 3 * kTileEnvs + lane;  // after
+  const int part = w / J, link = w - part * J;  // part < PARTS for every warp of the block
+  {
+    const double* b = P + ((0 * J + link) * 2) * 3 * kTileEnvs + lane;  // before: p1 xyz, p2 xyz
+    const double* a = P + ((1 * J + link) * 2) * 3 * kTileEnvs + lane;  // after
     double bp[6], ap[6];
     for (int k = 0; k < 6; ++k) {
       bp[k] = b[k * kTileEnvs];
       ap[k] = a[k * kTileEnvs];
     }
     const double s_diff = act ? ri_at(S, 3 * J, e) : 0.0;
-    const double alpha = act ? ri_at(S, 2 * J + w, e) : 0.0;
-    const double rl = c.link_caps[w][6];
+    const double alpha = act ? ri_at(S, 2 * J + link, e) : 0.0;
+    const double rl = c.link_caps[link][6];
     const double grow = alpha * s_diff * s_diff / 8.0;
     const double r_1 = vnorm_z(v3(bp[0] - ap[0], bp[1] - ap[1], bp[2] - ap[2])) / 2.0 + grow + rl;  // 0 for a resting link
     const double r_2 = vnorm_z(v3(bp[3] - ap[3], bp[4] - ap[4], bp[5] - ap[5])) / 2.0 + grow + rl;
     rc.p1 = v3((bp[0] + ap[0]) * 0.5, (bp[1] + ap[1]) * 0.5, (bp[2] + ap[2]) * 0.5);
     rc.p2 = v3((bp[3] + ap[3]) * 0.5, (bp[4] + ap[4]) * 0.5, (bp[5] + ap[5]) * 0.5);
     rc.r = fmax(r_1, r_2) + c.secure_radius;
-    if (act && S.robot_caps) cap_store(rc, S.robot_caps + ((size_t)e * J + w) * 7);
+    if (act && part == 0 && S.robot_caps) cap_store(rc, S.robot_caps + ((size_t)e * J + link) * 7);
   }
   __syncthreads();  // sc / P are dead: the human capsules take their place
   // ---- phase 3: human capsules, capsule index h uniform per warp (HumanReach::humanReachabilityAnalysis) ------------
@@ -187,11 +193,11 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_REACH_MINBLOCKS) k_re
     if (act && S.human_caps) cap_store(hc, S.human_caps + ((size_t)e * H + h) * 7);
   }
   __syncthreads();
-  if (w < J && act) {  // lanes without an env to verify sit the loop out (dummy operands would visit slow paths)
-    // ---- phase 4: link w against every human capsule (VerifyISO::verify_human_reach, verify_iso.cc:5-33) -----------
+  if (act) {  // lanes without an env to verify sit the loop out (dummy operands would visit slow paths)
+    // ---- phase 4: the link against its share of the human capsules (VerifyISO::verify_human_reach, verify_iso.cc:5-33)
     const int E = c.n_ext, B = c.n_bodies;
     const Axis ra = axis_of(rc);
-    for (int h = 0; h < H; ++h) {
+    for (int h = part; h < H; h += PARTS) {
       const double* hp = hum + (size_t)h * kHumDoubles * kTileEnvs + lane;
       Cap hc;
       hc.p1 = v3(hp[0 * kTileEnvs], hp[1 * kTileEnvs], hp[2 * kTileEnvs]);
@@ -211,12 +217,10 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_REACH_MINBLOCKS) k_re
     }
   }
   __syncthreads();  // the human capsules are dead from here on: reuse the region for the per-link partial minima
-  if (w < J) {
-    sc[(w * 3 + 0) * kTileEnvs + lane] = m0;
-    sc[(w * 3 + 1) * kTileEnvs + lane] = m1;
-    sc[(w * 3 + 2) * kTileEnvs + lane] = m2;
-    bits_s[w][lane] = my_bits;
-  }
+  sc[(w * 3 + 0) * kTileEnvs + lane] = m0;
+  sc[(w * 3 + 1) * kTileEnvs + lane] = m1;
+  sc[(w * 3 + 2) * kTileEnvs + lane] = m2;
+  bits_s[w][lane] = my_bits;
   __syncthreads();
   // ---- phase 5: combine the links; safe iff ANY human model is collision-free (verify_iso.cc:22-27) -----------------
   if (w == 0 && in_tile) {
@@ -225,7 +229,7 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_REACH_MINBLOCKS) k_re
     } else {
       unsigned bits = 0;
       double md[3] = {INFINITY, INFINITY, INFINITY};
-      for (int l = 0; l < J; ++l) {
+      for (int l = 0; l < NW; ++l) {
         bits |= bits_s[l][lane];
         for (int m = 0; m < 3; ++m) md[m] = fmin(md[m], sc[(l * 3 + m) * kTileEnvs + lane]);
       }
