@@ -335,9 +335,10 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
     s->ev_used += 5;
     cudaEventRecord(ev[0], st);
   }
-  k_pre_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
-  if (prof) cudaEventRecord(ev[1], st);
   const bool fork = s->overlap && !prof;
+  k_pre<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S);
+  if (!fork) k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
+  if (prof) cudaEventRecord(ev[1], st);
   cudaStream_t rs = fork ? s->side : st;
   if (fork) {
     // replan || reach + verify of the envs that do not replan, then the replanned envs
@@ -360,6 +361,7 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   }
   if (fork) {
     CK(cudaEventRecord(s->ev_join, s->side));
+    k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
     k_reach_verify<1><<<tile_grid(N), 32 * s->S.J, s->reach_smem_p0, st>>>(s->S, 0);
     CK(cudaStreamWaitEvent(st, s->ev_join, 0));
   } else {
@@ -370,7 +372,7 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   if (prof) cudaEventRecord(ev[3], st);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
   if (prof) cudaEventRecord(ev[4], st);
-  s->launches += 8;
+  s->launches += 9;
   CK(cudaGetLastError());
   return HRG_OK;
 }

@@ -17,7 +17,9 @@ __global__ void k_new_goal(DevState S, const uint8_t* __restrict__ mask, const d
 }
 
 // step() up to the replan decision; envs that do not replan go straight on to the potential trajectory.
-__global__ void __launch_bounds__(kTickBlock) k_pre_plan(DevState S, const double* __restrict__ t) {
+// First part of step() for every env: current motion, LTT commit, replan trigger -> compacted replan list. Kept apart
+// from k_plan because the replan chain - the critical path of the tick - only waits for this much.
+__global__ void __launch_bounds__(kTickBlock) k_pre(DevState S) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= S.N) return;
   const HrgConfig& c = *S.cfg;
@@ -26,10 +28,19 @@ __global__ void __launch_bounds__(kTickBlock) k_pre_plan(DevState S, const doubl
   if (replan) {
     const int slot = atomicAdd(S.replan_count, 1);
     S.replan_list[slot] = e;
-  } else {
-    plan_env(S, c, e, t[e], f);
   }
   S.replan_mark[e] = replan ? 1 : 0;
+  S.flags[e] = f;
+}
+
+// Middle part of step() for the envs that do NOT replan this tick (the others get it from k_replan_sample once their
+// new trajectory exists). Runs next to the replan chain.
+__global__ void __launch_bounds__(kTickBlock) k_plan(DevState S, const double* __restrict__ t) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= S.N || S.replan_mark[e]) return;
+  const HrgConfig& c = *S.cfg;
+  uint32_t f = S.flags[e];
+  plan_env(S, c, e, t[e], f);
   S.flags[e] = f;
 }
 
@@ -64,6 +75,12 @@ enum { CTR_OPT = 0, CTR_SCALE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, N_CTR = 4 }
 // 1..32 problems per warp - are in profiles/r01_replan_packing.md: one problem per warp had the shortest chains but was
 // instruction-fetch bound, many per warp serialised on divergent QR iteration counts.
 constexpr int kGroupLanes = 8, kGroupsPerWarp = 4;
+// Groups of one warp that hold different problems diverge and are issued one after the other, so a warp's chain is up to
+// the SUM of its groups' chains. k_replan_opt / _scale have ~12 600 problems per tick and need 4 groups per warp to be
+// resident in one wave; k_replan_deep has ~3 500 and is pure tail latency at 8 % occupancy, so it spreads them thinner.
+#ifndef HRG_DEEP_GROUPS
+#define HRG_DEEP_GROUPS 2
+#endif
 
 __device__ __forceinline__ LtpLimits joint_limits(const HrgConfig& c, int j, double* mat) {
   LtpLimits L;
@@ -89,13 +106,14 @@ __device__ __forceinline__ void finish_scaled(const LtpLimits& L, const PlanRec&
 
 // Fetches the next four tasks of counter `ctr` for the warp: group g gets base + g. Returns -1 for the whole warp when
 // the list is exhausted, -2 for a group beyond its end (whole 8-lane groups leave together).
+template <int G = kGroupsPerWarp>
 __device__ __forceinline__ int fetch_group_task(int32_t* ctr, int ntask, int lane) {
   int base = 0;
-  if (lane == 0) base = atomicAdd(ctr, kGroupsPerWarp);
+  if (lane == 0) base = atomicAdd(ctr, G);
   base = __shfl_sync(0xffffffffu, base, 0);
   if (base >= ntask) return -1;
-  const int t = base + (lane >> 3);
-  return t < ntask ? t : -2;
+  const int g = lane >> 3, t = base + g;
+  return (g < G && t < ntask) ? t : -2;
 }
 __device__ __forceinline__ LtpLimits group_limits(const HrgConfig& c, int j, double* mat, int lane) {
   LtpLimits L = joint_limits(c, j, mat);
@@ -206,23 +224,20 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_s
   }
 }
 
-// One (deep-list slot, polynomial candidate 2..7) task per 8-lane group, 4 groups per warp. The 8 lanes run the task's
+// One (deep-list slot, polynomial candidate 2..7) task per 8-lane group, HRG_DEEP_GROUPS groups per warp. The 8 lanes run the task's
 // scalar code redundantly (identical inputs, identical results) and share every eigen-solve of it - the candidate's own
 // polynomial and those inside optSwitchTimes - through the cooperative root finder (ltp_math.cuh).
 __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_deep(DevState S) {
-  __shared__ double mat_s[kReplanBlock / 32][4][37];
+  __shared__ double mat_s[kReplanBlock / 32][HRG_DEEP_GROUPS][37];
   const HrgConfig& c = *S.cfg;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int gl = lane & 7, grp = lane >> 3;
   const int J = S.J, N = S.N;
   const int ntask = S.replan_ctr[CTR_DEEP_COUNT] * 6;
   for (;;) {
-    int base = 0;
-    if (lane == 0) base = atomicAdd(S.replan_ctr + CTR_DEEP, 4);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= ntask) break;
-    const int dt = base + grp;
-    if (dt >= ntask) continue;  // whole 8-lane groups leave together
+    const int dt = fetch_group_task<HRG_DEEP_GROUPS>(S.replan_ctr + CTR_DEEP, ntask, lane);
+    if (dt == -1) break;
+    if (dt < 0) continue;  // whole 8-lane groups leave together
     const int slot = dt / 6, cand = 2 + (dt - slot * 6);
     const int task = S.deep_list[slot];
     const int idx = task / J, j = task - idx * J;
