@@ -153,7 +153,7 @@ int hrg_shield_get_capsules(HrgShield* s, double* robot, double* human, double* 
 int hrg_shield_stats(HrgShield* s, HrgStats* out, int clear, void* stream);
 
 /* Per-kernel device timing of hrg_shield_step for the next `max_steps` steps (0 = off): CUDA events are recorded on the
- * step's stream around k_pre_plan, the three k_replan_* kernels, both k_reach_verify passes, k_select (the replan is not overlapped while profiling). hrg_shield_profile_read synchronises on the last
+ * step's stream around k_pre + k_plan, the four k_replan_* kernels, both k_reach_verify passes, k_select (the replan is not overlapped while profiling). hrg_shield_profile_read synchronises on the last
  * event and returns the summed milliseconds per kernel (ms_host[4]) and the number of steps they cover. */
 int hrg_shield_profile(HrgShield* s, int max_steps);
 int hrg_shield_profile_read(HrgShield* s, double* ms_host, int* steps_host);
