@@ -85,8 +85,8 @@ HRG_HD double point_segment_dist(const V3& p, const Cap& c) { return point_segme
 
 // The parallel-segments branch of min_segment_distance (RL/src/intersections.cpp:80-104), including its chained
 // comparisons: `d0 <= 0 >= d1` parses as ((d0 <= 0) ? 1.0 : 0.0) >= d1, `d0 >= magA <= d1` as
-// ((d0 >= magA) ? 1.0 : 0.0) <= d1. Rare (exactly parallel axes), so it stays a call.
-HRG_HD_CALL double parallel_segment_distance(const Cap& c1, const Axis& a1, const Cap& c2) {
+// ((d0 >= magA) ? 1.0 : 0.0) <= d1. Rare (exactly parallel axes); inlined all the same - as a real call its by-reference operands were spilled to the stack for every pair.
+HRG_HD double parallel_segment_distance(const Cap& c1, const Axis& a1, const Cap& c2) {
   const V3& _A = a1.u;
   const double magA = a1.mag;
   double d0 = vdot(_A, vsub(c2.p1, c1.p1));
