@@ -149,6 +149,60 @@ def test_closed_loop_matches_checker(robot, n_envs, ticks, seed):
     assert res["branch_hist"][0] > 0 and res["branch_hist"][2] > 0
 
 
+@pytest.mark.parametrize("n_envs", [1, 37, 95])
+def test_ragged_batches_match_checker(n_envs):
+    """Batch sizes that are not a multiple of the 32-env tile / 4-group warp: a one-env batch, partial last tiles, partial
+    replan groups."""
+    res = pu.closed_loop_compare(pu.default_files("schunk"), n_envs=n_envs, ticks=120, seed=2000 + n_envs)
+    print(res)
+    assert res["mismatch_excl_near"] == 0, res
+    assert res["max_setpoint_diff"] < 1e-5 and res["max_min_dist_diff"] < 1e-5 and res["max_capsule_diff"] < 1e-5, res
+    assert res["gpu_stats"]["n_steps"] == n_envs * 120
+    assert res["gpu_stats"]["n_replan"] > 0
+
+
+def test_full_size_batch_position_invariance():
+    """BASELINE size (65 536 shields on one GPU) through a size-independent property: every env is an exact replica of
+    one of 128 source envs, scattered over the batch by a fixed permutation. All replicas of a source env must produce
+    bit-identical setpoints and decisions on every tick (tiles, replan groups, work counters and the order in which the
+    replan list is compacted must not leak into results), and the 128 source envs must agree bit for bit with a 128-env
+    batch of their own - which the closed-loop tests above tie to the reference."""
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    from human_robot_gym_b200.config import ShieldConfig
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+    files = pu.default_files("schunk")
+    sc = ShieldConfig.from_files(0.004, *files)
+    n_src, n, ticks = 128, 65536, 60
+    scen = SyntheticScenario(n_src, pu.mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, 4242)
+    rng = np.random.default_rng(7)
+    src = rng.permutation(np.arange(n) % n_src)          # source env of every batch slot
+    src_t = torch.from_numpy(src).cuda()
+    small = BatchedSafetyShield(n_src, 0.004, *files, init_qpos=scen.init_q, device="cuda:0", ltt_capacity=512)
+    big = BatchedSafetyShield(n, 0.004, *files, init_qpos=scen.init_q[src], device="cuda:0", ltt_capacity=512)
+    phase = np.arange(n_src) % 25
+    n_unsafe = 0
+    for k in range(ticks):
+        t = k * 0.004
+        kp = torch.from_numpy(scen.keypoints(t)).cuda()
+        small.humanMeasurement(kp, t)
+        big.humanMeasurement(kp[src_t].contiguous(), t)
+        gm = phase == (k % 25)
+        if gm.any():
+            g = torch.from_numpy(scen.next_goal(gm)).cuda()
+            gm_t = torch.from_numpy(gm).cuda()
+            small.newLongTermTrajectory(g, env_mask=gm_t)
+            big.newLongTermTrajectory(g[src_t].contiguous(), env_mask=gm_t[src_t].contiguous())
+        small.step(t)
+        big.step(t)
+        for name in ("q", "dq", "ddq", "dddq", "is_safe", "branch", "status"):
+            a, b = getattr(small, name), getattr(big, name)
+            assert torch.equal(a[src_t], b), (k, name)
+        n_unsafe += int((small.is_safe == 0).sum())
+    st = big.stats()
+    assert st["n_steps"] == n * ticks and st["n_replan"] > 0
+    assert 0 < n_unsafe < n_src * ticks  # both verdicts occur
+
+
 def test_pfl_shield_matches_checker():
     """ShieldType PFL (BASELINE config 4b, robot_human_handover_cart.yaml:24): per-sample Cartesian velocities of every
     planned LTT, alpha_i from their differences, v_limit failsafe, is_safe || is_under_v_limit."""
