@@ -38,6 +38,12 @@ class HrgConfig(C.Structure):
     ]
 
 
+class HrgControllerConfig(C.Structure):
+    _fields_ = [("nb_joints", C.c_int32), ("has_position_limits", C.c_int32)] + [
+        (n, _D * MAX_JOINTS) for n in ("input_min", "input_max", "output_min", "output_max", "position_min", "position_max",
+                                       "kp", "kd", "torque_min", "torque_max")]
+
+
 class HrgStats(C.Structure):
     _fields_ = [("n_steps", C.c_int64), ("n_unsafe", C.c_int64), ("n_branch", C.c_int64 * 3), ("n_replan", C.c_int64),
                 ("n_replan_failed", C.c_int64), ("n_near_threshold", C.c_int64), ("ltt_len_sum", C.c_int64),
@@ -109,6 +115,8 @@ SYMBOLS = {
     "hrg_shield_num_human_capsules": (C.c_int, [C.c_void_p]),
     "hrg_shield_launch_count": (C.c_int64, [C.c_void_p]),
     "hrg_last_error": (C.c_char_p, []),
+    "hrg_controller_set_goal": (C.c_int, [C.c_void_p, C.POINTER(HrgControllerConfig), _u8p, _dp, _dp, _dp, _dp, _vp]),
+    "hrg_controller_torques": (C.c_int, [C.c_void_p, C.POINTER(HrgControllerConfig)] + [_dp] * 8 + [_vp]),
     "hrg_stage_capsule_dist": (C.c_int, [C.c_int, _dp, _dp, _dp, _vp]),
     "hrg_stage_plan_safety_shield": (C.c_int, [C.c_double, C.c_int, _dp, _u8p, _dp, _dp, _vp]),
     "hrg_stage_ltp_plan": (C.c_int, [C.POINTER(HrgConfig), C.c_int, _dp, _dp, _dp, _dp, _dp, _i32p, C.c_int, _vp]),

@@ -11,6 +11,7 @@
 
 #include "kernels_reach.cuh"
 #include "kernels_tick.cuh"
+#include "kernels_controller.cuh"
 
 using namespace hrg;
 

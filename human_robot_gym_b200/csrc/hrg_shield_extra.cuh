@@ -244,4 +244,36 @@ int hrg_stage_reach_verify(const HrgConfig* cfg, int n, const double* base_pose,
   return HRG_OK;
 }
 
+// ---- batched FailsafeController -------------------------------------------------------------------
+static int ctrl_check(const HrgShield* s, const HrgControllerConfig* k, const char* who) {
+  if (!s || !k) return fail(HRG_EINVAL, who);
+  if (k->nb_joints != s->S.J) return fail(HRG_EINVAL, "controller nb_joints differs from the shield's");
+  return HRG_OK;
+}
+
+int hrg_controller_set_goal(HrgShield* s, const HrgControllerConfig* cfg, const uint8_t* env_mask, const double* action,
+                            const double* joint_pos, const double* set_qpos, double* goal_out, void* stream) {
+  if (int rc = ctrl_check(s, cfg, "hrg_controller_set_goal: NULL argument")) return rc;
+  if (!set_qpos && (!action || !joint_pos)) return fail(HRG_EINVAL, "hrg_controller_set_goal: action / joint_pos NULL");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  k_ctrl_set_goal<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S, *cfg, env_mask, action, joint_pos, set_qpos, goal_out);
+  s->launches++;
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_controller_torques(HrgShield* s, const HrgControllerConfig* cfg, const double* q_des, const double* dq_des,
+                           const double* ddq_des, const double* joint_pos, const double* joint_vel,
+                           const double* mass_matrix, const double* torque_comp, double* torques, void* stream) {
+  if (int rc = ctrl_check(s, cfg, "hrg_controller_torques: NULL argument")) return rc;
+  if (!q_des || !dq_des || !ddq_des || !joint_pos || !joint_vel || !mass_matrix || !torque_comp || !torques)
+    return fail(HRG_EINVAL, "hrg_controller_torques: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  k_ctrl_torques<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S.N, s->S.J, *cfg, q_des, dq_des, ddq_des, joint_pos, joint_vel,
+                                                        mass_matrix, torque_comp, torques);
+  s->launches++;
+  CK(cudaGetLastError());
+  return HRG_OK;
+}
+
 }  // extern "C"

@@ -16,7 +16,6 @@ __global__ void k_new_goal(DevState S, const uint8_t* __restrict__ mask, const d
   new_goal_env(S, *S.cfg, e, goal_q + (size_t)e * S.J);
 }
 
-// step() up to the replan decision; envs that do not replan go straight on to the potential trajectory.
 // First part of step() for every env: current motion, LTT commit, replan trigger -> compacted replan list. Kept apart
 // from k_plan because the replan chain - the critical path of the tick - only waits for this much.
 __global__ void __launch_bounds__(kTickBlock) k_pre(DevState S) {

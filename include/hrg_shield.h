@@ -82,6 +82,18 @@ typedef struct HrgStats {
   double min_dist;          /* smallest capsule distance seen */
 } HrgStats;
 
+/* Constant tables of the batched FailsafeController: robosuite 1.3.2 Controller.scale_action ranges,
+ * position limits of set_goal_position, PD gains and actuator range of JointPositionController, all per joint. */
+typedef struct HrgControllerConfig {
+  int32_t nb_joints;
+  int32_t has_position_limits; /* 0: set_goal_position(..., position_limit=None) */
+  double input_min[HRG_MAX_JOINTS], input_max[HRG_MAX_JOINTS];
+  double output_min[HRG_MAX_JOINTS], output_max[HRG_MAX_JOINTS];
+  double position_min[HRG_MAX_JOINTS], position_max[HRG_MAX_JOINTS];
+  double kp[HRG_MAX_JOINTS], kd[HRG_MAX_JOINTS];
+  double torque_min[HRG_MAX_JOINTS], torque_max[HRG_MAX_JOINTS]; /* actuator_range */
+} HrgControllerConfig;
+
 typedef struct HrgShield HrgShield;
 
 /* SafetyShield(sample_time, trajectory_config_file, robot_config_file, mocap_config_file, init_x..init_yaw, init_qpos,
@@ -163,6 +175,21 @@ int hrg_shield_num_human_capsules(const HrgShield* s);
 /* Number of kernels this library has launched on behalf of `s` since creation (bench.py's gpu_launches claim). */
 int64_t hrg_shield_launch_count(const HrgShield* s);
 const char* hrg_last_error(void);
+
+/* ---- batched FailsafeController (the shield's immediate caller); all DEVICE pointers, cfg HOST ------- */
+/* FailsafeController.set_goal(action, set_qpos) — failsafe_controller.py:252-300: scaled = scale_action(action)
+ * (robosuite/controllers/base_controller.py: clip to the input range, affine map onto the output range),
+ * goal = set_goal_position(scaled, joint_pos, position_limit, set_pos) (robosuite/utils/control_utils.py: joint_pos +
+ * scaled, or set_pos, clipped to the limits), then newLongTermTrajectory(goal, 0) for the envs of env_mask.
+ * action, joint_pos [N,J]; set_qpos [N,J] or NULL; goal_out [N,J] or NULL. */
+int hrg_controller_set_goal(HrgShield* s, const HrgControllerConfig* cfg, const uint8_t* env_mask, const double* action,
+                            const double* joint_pos, const double* set_qpos, double* goal_out, void* stream);
+/* FailsafeController.run_controller torque law — failsafe_controller.py:352-369: tau = M (kp e + kd de + ddq_des) +
+ * torque_compensation, clipped to the actuator range (clip_torques). q_des, dq_des, ddq_des are hrg_shield_step's
+ * outputs; joint_pos, joint_vel, torque_comp, torques [N,J]; mass_matrix [N,J,J] row-major. */
+int hrg_controller_torques(HrgShield* s, const HrgControllerConfig* cfg, const double* q_des, const double* dq_des,
+                           const double* ddq_des, const double* joint_pos, const double* joint_vel,
+                           const double* mass_matrix, const double* torque_comp, double* torques, void* stream);
 
 /* ---- per-stage entry points (parity tests + ncu); all DEVICE pointers --------------------------------------- */
 /* capsule_capsule_dist (RL/include/intersections.hpp:105-124) for n independent pairs: c1,c2 [n,7] -> dist [n]. */
