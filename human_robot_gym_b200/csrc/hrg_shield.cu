@@ -82,6 +82,7 @@ struct HrgShield {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool overlap = true;
+  bool cascade = true;  // verification cascade for pass 0 (HRG_NO_CASCADE=1 or stored capsules: full kernel)
   int replan_blocks_per_sm = 12;  // resident 64-thread replan blocks per SM while overlapped with k_reach_verify pass 0 (measured best)
   // optional per-kernel timing of hrg_shield_step (bench.py's roofline leg): 5 boundary events per step
   bool prof = false;
@@ -182,6 +183,9 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   AL(S.deep_list, (size_t)N * J);
   AL(S.deep_res, (size_t)N * J * 6);
   AL(S.replan_mark, N);
+  AL(S.verify_list, (size_t)2 * N);
+  AL(S.verify_cnt, 2);
+  AL(S.link_caps_buf, (size_t)7 * J * N);
   AL(S.plan_opt, (size_t)N * HRG_MAX_JOINTS);
   AL(S.plan_sc, (size_t)N * HRG_MAX_JOINTS);
   AL(S.plan_head, N);
@@ -218,6 +222,9 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
     if ((size_t)atoi(v) * 1024 > h->reach_smem_p0) h->reach_smem_p0 = (size_t)atoi(v) * 1024;
   cudaFuncSetAttribute(k_reach_verify<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem_p0);
   cudaFuncSetAttribute(k_reach_verify<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
+  cudaFuncSetAttribute(k_reach_verify<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem_p0);
+  cudaFuncSetAttribute(k_verify_stage<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
+  cudaFuncSetAttribute(k_verify_stage<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->reach_smem);
   cudaFuncSetAttribute(k_measure, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->measure_smem);
   {
     int lo = 0, hi = 0;  // the replan chain is the critical path of the tick: highest priority for its blocks
@@ -225,6 +232,7 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
     ce = cudaStreamCreateWithPriority(&h->side, cudaStreamNonBlocking, hi);
     if (const char* v = getenv("HRG_REPLAN_BLOCKS_PER_SM")) h->replan_blocks_per_sm = atoi(v) > 0 ? atoi(v) : 12;
     if (const char* v = getenv("HRG_NO_OVERLAP")) h->overlap = !(atoi(v) > 0);
+    if (const char* v = getenv("HRG_NO_CASCADE")) h->cascade = !(atoi(v) > 0);
   }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
@@ -325,6 +333,22 @@ int hrg_shield_new_goal(HrgShield* s, const uint8_t* env_mask, const double* goa
   return HRG_OK;
 }
 
+// reach + verify of the envs that do not replan this tick: the Pos-model tile kernel plus the two cascade stages over its
+// survivors, or the full kernel when capsules / all distances are stored for the getters.
+static void verify_pass0(HrgShield* s, cudaStream_t st, size_t smem) {
+  const int N = s->S.N, J = s->S.J;
+  if (s->cascade && !s->S.human_caps) {
+    size_t stage_smem = (size_t)kHumDoubles * s->cfg.n_bodies * kTileEnvs * sizeof(double);
+    if (stage_smem < (size_t)J * kTileEnvs * sizeof(double)) stage_smem = (size_t)J * kTileEnvs * sizeof(double);
+    k_reach_verify<1, true><<<tile_grid(N), 32 * J, smem, st>>>(s->S, 0);
+    k_verify_stage<1><<<tile_grid(N), 32 * J, stage_smem, st>>>(s->S);
+    k_verify_stage<2><<<tile_grid(N), 32 * J, stage_smem, st>>>(s->S);
+    s->launches += 2;
+  } else {
+    k_reach_verify<1><<<tile_grid(N), 32 * J, smem, st>>>(s->S, 0);
+  }
+}
+
 int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
                     uint8_t* branch, uint32_t* status, void* stream) {
   if (!s || !t) return fail(HRG_EINVAL, "hrg_shield_step: NULL argument");
@@ -363,11 +387,11 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   if (fork) {
     CK(cudaEventRecord(s->ev_join, s->side));
     k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
-    k_reach_verify<1><<<tile_grid(N), 32 * s->S.J, s->reach_smem_p0, st>>>(s->S, 0);
+    verify_pass0(s, st, s->reach_smem_p0);
     CK(cudaStreamWaitEvent(st, s->ev_join, 0));
   } else {
     if (prof) cudaEventRecord(ev[2], st);
-    k_reach_verify<1><<<tile_grid(N), 32 * s->S.J, s->reach_smem, st>>>(s->S, 0);
+    verify_pass0(s, st, s->reach_smem);
   }
   k_reach_verify<2><<<tile_grid(N), 32 * s->S.J * 2, s->reach_smem, st>>>(s->S, 1);
   if (prof) cudaEventRecord(ev[3], st);

@@ -77,13 +77,21 @@ __host__ __device__ inline int reach_smem_doubles(int J, int H) {
 // on link w % J and takes every PARTS-th human capsule. PARTS = 1 is the throughput shape of pass 0 (thousands of tiles);
 // pass 1 only has a few dozen tiles - less than one per SM - and sits on the tick's critical path, so it runs with
 // PARTS = 2 and halves the dependent chain of a tile instead.
-template <int PARTS>
+//
+// CASCADE (pass 0 of the product path): VerifyISO::verify_human_reach (verify_iso.cc:19-33) returns "safe" as soon as ONE
+// human model is collision-free, and the Pos model - two spheres - already clears about half of the envs. With CASCADE the
+// tile only evaluates the Pos model; envs it does not clear go on a compact list (with their link capsules) and
+// k_verify_stage evaluates the Vel and then the Accel model on dense tiles of the survivors. Decisions are identical;
+// min_dist of a model that was not needed stays +inf. Handles that store capsules / distances for the getters run the
+// full kernel instead.
+template <int PARTS, bool CASCADE = false>
 __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS, PARTS == 1 ? HRG_REACH_MINBLOCKS : 1)
     k_reach_verify(DevState S, int pass) {
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
   __shared__ unsigned bits_s[HRG_MAX_JOINTS * PARTS][kTileEnvs];
-  const int J = S.J, H = S.H, N = S.N;
+  const int J = S.J, N = S.N;
+  const int H = CASCADE ? S.cfg->n_ext : S.H;  // human capsules this kernel looks at
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NW = blockDim.x >> 5;
   int e = blockIdx.x * kTileEnvs + lane;
   bool in_tile;
@@ -174,6 +182,12 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS, PARTS == 1 ? HRG_
     rc.p2 = v3((bp[3] + ap[3]) * 0.5, (bp[4] + ap[4]) * 0.5, (bp[5] + ap[5]) * 0.5);
     rc.r = fmax(r_1, r_2) + c.secure_radius;
     if (act && part == 0 && S.robot_caps) cap_store(rc, S.robot_caps + ((size_t)e * J + link) * 7);
+    if (CASCADE && act) {
+      double* o = S.link_caps_buf + (size_t)link * 7 * N + e;
+      o[0] = rc.p1.x; o[(size_t)N] = rc.p1.y; o[(size_t)2 * N] = rc.p1.z;
+      o[(size_t)3 * N] = rc.p2.x; o[(size_t)4 * N] = rc.p2.y; o[(size_t)5 * N] = rc.p2.z;
+      o[(size_t)6 * N] = rc.r;
+    }
   }
   __syncthreads();  // sc / P are dead: the human capsules take their place
   // ---- phase 3: human capsules, capsule index h uniform per warp (HumanReach::humanReachabilityAnalysis) ------------
@@ -233,11 +247,108 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS, PARTS == 1 ? HRG_
         bits |= bits_s[l][lane];
         for (int m = 0; m < 3; ++m) md[m] = fmin(md[m], sc[(l * 3 + m) * kTileEnvs + lane]);
       }
-      uint32_t g = ((bits & 7u) != 7u) ? (f | F_IS_SAFE) : (f & ~F_IS_SAFE);
+      uint32_t g;
+      if (CASCADE) {
+        g = (bits & 1u) ? (f & ~F_IS_SAFE) : (f | F_IS_SAFE);  // provisional when the Pos model collides
+        if (bits & 1u) S.verify_list[atomicAdd(S.verify_cnt, 1)] = e;
+      } else {
+        g = ((bits & 7u) != 7u) ? (f | F_IS_SAFE) : (f & ~F_IS_SAFE);
+      }
       if (bits & 8u) g |= (uint32_t)HRG_ST_NEAR_THRESHOLD << F_STATUS_SHIFT;
       S.flags[e] = g;
       for (int m = 0; m < 3; ++m) S.min_dist[(size_t)m * N + e] = md[m];
     }
+  }
+}
+
+// Cascade stage MODEL (1 = Vel, 2 = Accel) over the envs of verify_list[MODEL - 1]: dense tiles of 32 list entries,
+// warp = robot link (its swept capsule comes from link_caps_buf), human capsules of that model only. An env that the
+// model clears becomes safe; otherwise it goes on to the Accel stage or stays unsafe.
+template <int MODEL>
+__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_REACH_MINBLOCKS) k_verify_stage(DevState S) {
+  extern __shared__ double smem[];
+  __shared__ HrgConfig cfg_s;
+  __shared__ unsigned bits_s[HRG_MAX_JOINTS][kTileEnvs];
+  const int cnt = S.verify_cnt[MODEL - 1];
+  if (blockIdx.x * kTileEnvs >= cnt) return;
+  const int J = S.J, N = S.N;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NW = blockDim.x >> 5;
+  const int i = blockIdx.x * kTileEnvs + lane;
+  const bool act = i < cnt;
+  const int e = act ? S.verify_list[(size_t)(MODEL - 1) * N + i] : 0;
+  {
+    const int nw = sizeof(HrgConfig) / 8;
+    const double* src = reinterpret_cast<const double*>(S.cfg);
+    double* dst = reinterpret_cast<double*>(&cfg_s);
+    for (int k = threadIdx.x; k < nw; k += blockDim.x) dst[k] = src[k];
+  }
+  __syncthreads();
+  const HrgConfig& c = cfg_s;
+  const int B = c.n_bodies, h0 = c.n_ext + (MODEL - 1) * B;
+  double* hum = smem;  // [b * 11 + k][32]
+  const double t_reach = act ? ri_at(S, 3 * J + 1, e) : 0.0;
+  for (int b = w; b < B; b += NW) {
+    Cap hc;
+    hc.p1 = v3(0, 0, 0); hc.p2 = v3(0, 0, 1); hc.r = 0;
+    Axis ha;
+    ha.mag = 0.0; ha.u = v3(0, 0, 0);
+    if (act) {
+      hc = human_capsule(c, h0 + b, S.kp_pos + e, S.kp_vel + e, (size_t)N, t_reach);
+      ha = axis_of(hc);
+    }
+    double* o = hum + (size_t)b * kHumDoubles * kTileEnvs + lane;
+    o[0 * kTileEnvs] = hc.p1.x; o[1 * kTileEnvs] = hc.p1.y; o[2 * kTileEnvs] = hc.p1.z;
+    o[3 * kTileEnvs] = hc.p2.x; o[4 * kTileEnvs] = hc.p2.y; o[5 * kTileEnvs] = hc.p2.z;
+    o[6 * kTileEnvs] = hc.r;
+    o[7 * kTileEnvs] = ha.mag;
+    o[8 * kTileEnvs] = ha.u.x; o[9 * kTileEnvs] = ha.u.y; o[10 * kTileEnvs] = ha.u.z;
+  }
+  unsigned my_bits = 0;
+  double md = INFINITY;
+  Cap rc;
+  rc.p1 = v3(0, 0, 0); rc.p2 = v3(0, 0, 0); rc.r = 0;
+  if (act) {
+    const double* o = S.link_caps_buf + (size_t)w * 7 * N + e;
+    rc.p1 = v3(o[0], o[(size_t)N], o[(size_t)2 * N]);
+    rc.p2 = v3(o[(size_t)3 * N], o[(size_t)4 * N], o[(size_t)5 * N]);
+    rc.r = o[(size_t)6 * N];
+  }
+  __syncthreads();
+  if (act) {
+    const Axis ra = axis_of(rc);
+    for (int b = 0; b < B; ++b) {
+      const double* hp = hum + (size_t)b * kHumDoubles * kTileEnvs + lane;
+      Cap hc;
+      hc.p1 = v3(hp[0 * kTileEnvs], hp[1 * kTileEnvs], hp[2 * kTileEnvs]);
+      hc.p2 = v3(hp[3 * kTileEnvs], hp[4 * kTileEnvs], hp[5 * kTileEnvs]);
+      hc.r = hp[6 * kTileEnvs];
+      Axis ha;
+      ha.d = vsub(hc.p2, hc.p1);
+      ha.mag = hp[7 * kTileEnvs];
+      ha.u = v3(hp[8 * kTileEnvs], hp[9 * kTileEnvs], hp[10 * kTileEnvs]);
+      const double d = capsule_capsule_dist(rc, ra, hc, ha);
+      if (d < 0.0) my_bits |= 1u;
+      if (fabs(d) < 1e-6) my_bits |= 8u;
+      md = fmin(md, d);
+    }
+  }
+  __syncthreads();  // the human capsules are dead: reuse the region for the per-link minima
+  smem[w * kTileEnvs + lane] = md;
+  bits_s[w][lane] = my_bits;
+  __syncthreads();
+  if (w == 0 && act) {
+    unsigned bits = 0;
+    double m = INFINITY;
+    for (int l = 0; l < J; ++l) {
+      bits |= bits_s[l][lane];
+      m = fmin(m, smem[l * kTileEnvs + lane]);
+    }
+    uint32_t g = S.flags[e];
+    if (!(bits & 1u)) g |= F_IS_SAFE;
+    else if (MODEL == 1) S.verify_list[(size_t)N + atomicAdd(S.verify_cnt + 1, 1)] = e;
+    if (bits & 8u) g |= (uint32_t)HRG_ST_NEAR_THRESHOLD << F_STATUS_SHIFT;
+    S.flags[e] = g;
+    S.min_dist[(size_t)MODEL * N + e] = m;
   }
 }
 

@@ -379,6 +379,7 @@ __global__ void __launch_bounds__(kTickBlock)
   if (e == 0) {
     *S.replan_count = 0;
     for (int k = 0; k < N_CTR; ++k) S.replan_ctr[k] = 0;
+    S.verify_cnt[0] = S.verify_cnt[1] = 0;
   }
   unsigned long long my[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum
   double my_min = INFINITY;

@@ -82,6 +82,10 @@ struct DevState {
   int32_t* deep_list;     // [N * J] (env, joint) tasks whose closed-form timeScaling candidates were rejected
   PlanRec* deep_res;      // [N * J][6] result of each polynomial candidate; len = accepted
   uint8_t* replan_mark;   // [N] 1 = this tick's reach + verify of the env runs after k_replan (second pass)
+  // verification cascade (kernels_reach.cuh): envs whose Pos / Vel model collides go on to the next model
+  int32_t* verify_list;   // [2][N] envs that still need the Vel (0) / Accel (1) model this tick
+  int32_t* verify_cnt;    // [2]
+  double* link_caps_buf;  // [7J][N] this tick's swept link capsules of the envs on verify_list, field-major
   // optional per-step capsule dump (drop-in getters); NULL = not stored
   double* robot_caps;  // [N][J][7]
   double* human_caps;  // [N][H][7]

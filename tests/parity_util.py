@@ -74,12 +74,17 @@ def make_checker(files, n, base_pose, init_q, sample_time=0.004, shield_type=1, 
 
 
 def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0", sample_time=0.004, shield_type=1,
-                        goal_period=25, stagger=True, ltt_capacity=1024, base_pose=None, collect=None):
+                        goal_period=25, stagger=True, ltt_capacity=1024, base_pose=None, collect=None,
+                        store_capsules=True):
     """Drives BatchedSafetyShield (CUDA) and the CPU checker in lockstep on identical synthetic inputs.
 
     Decisions (is_safe, branch) must match exactly; an env whose FIRST mismatch happens on a tick where either side
     reports a capsule distance within 1e-6 m of 0 is counted as near-threshold and excluded (north_star). Envs are
     dropped from the comparison after their first mismatch (their closed loops have diverged).
+
+    store_capsules=False is the product configuration: reach + verify then runs as the model cascade (a human model that
+    is not needed for the verdict is not evaluated, its min_dist stays +inf), and only the distances of the models that
+    were evaluated are compared.
     """
     import torch
 
@@ -93,7 +98,7 @@ def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0"
     pose = np.ascontiguousarray(pose)
     chk, kind = make_checker(files, n_envs, pose, scen.init_q, sample_time, shield_type)
     gpu = BatchedSafetyShield(n_envs, sample_time, *files, base_pose=pose, init_qpos=scen.init_q,
-                              shield_type=shield_type, device=device, ltt_capacity=ltt_capacity, store_capsules=True)
+                              shield_type=shield_type, device=device, ltt_capacity=ltt_capacity, store_capsules=store_capsules)
     H = gpu.H
     alive = np.ones(n_envs, bool)
     n_mis, n_near, max_sp, max_md, max_caps = 0, 0, 0.0, 0.0, 0.0
@@ -115,7 +120,7 @@ def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0"
         b = {"q": gpu.q.cpu().numpy(), "dq": gpu.dq.cpu().numpy(), "ddq": gpu.ddq.cpu().numpy(),
              "dddq": gpu.dddq.cpu().numpy(), "is_safe": gpu.is_safe.cpu().numpy(), "branch": gpu.branch.cpu().numpy(),
              "status": gpu.status.cpu().numpy()}
-        r_g, h_g, md_g = [x.cpu().numpy() for x in gpu.capsules()]
+        r_g, h_g, md_g = [None if x is None else x.cpu().numpy() for x in gpu.capsules()]
         r_c, h_c, md_c = chk.capsules(H)
         bad = ((a["is_safe"] != b["is_safe"]) | (a["branch"] != b["branch"])) & alive
         if bad.any():
@@ -126,10 +131,16 @@ def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0"
         if alive.any():
             for key in ("q", "dq", "ddq", "dddq"):
                 max_sp = max(max_sp, float(np.abs(a[key][alive] - b[key][alive]).max()))
-            ver = alive & np.isfinite(md_g).all(axis=1) & np.isfinite(md_c).all(axis=1)
-            if ver.any():
-                max_md = max(max_md, float(np.abs(md_g[ver] - md_c[ver]).max()))
-                max_caps = max(max_caps, float(np.abs(r_g[ver] - r_c[ver]).max()), float(np.abs(h_g[ver] - h_c[ver]).max()))
+            if store_capsules:
+                ver = alive & np.isfinite(md_g).all(axis=1) & np.isfinite(md_c).all(axis=1)
+                if ver.any():
+                    max_md = max(max_md, float(np.abs(md_g[ver] - md_c[ver]).max()))
+                    max_caps = max(max_caps, float(np.abs(r_g[ver] - r_c[ver]).max()),
+                                   float(np.abs(h_g[ver] - h_c[ver]).max()))
+            else:
+                both = alive[:, None] & np.isfinite(md_g) & np.isfinite(md_c)
+                if both.any():
+                    max_md = max(max_md, float(np.abs(md_g[both] - md_c[both]).max()))
             hist += np.bincount(a["branch"][alive], minlength=3)[:3]
             unsafe += int((a["is_safe"][alive] == 0).sum())
         if collect is not None:

@@ -149,6 +149,21 @@ def test_closed_loop_matches_checker(robot, n_envs, ticks, seed):
     assert res["branch_hist"][0] > 0 and res["branch_hist"][2] > 0
 
 
+@pytest.mark.parametrize("robot,n_envs,ticks,seed,shield_type", [("schunk", 1024, 150, 3001, 1), ("panda", 517, 150, 3002, 1),
+                                                                  ("schunk", 384, 150, 3004, 2)])
+def test_verification_cascade_matches_checker(robot, n_envs, ticks, seed, shield_type):
+    """Product configuration (no stored capsules): pass 0 of reach + verify runs as the Pos -> Vel -> Accel cascade over
+    compacted survivor lists. Decisions and setpoints against the reference; distances of the evaluated models."""
+    res = pu.closed_loop_compare(pu.default_files(robot), n_envs=n_envs, ticks=ticks, seed=seed, shield_type=shield_type,
+                                 store_capsules=False)
+    print(res)
+    assert res["mismatch_excl_near"] == 0, res
+    assert res["max_setpoint_diff"] < 1e-5 and res["max_min_dist_diff"] < 1e-5, res
+    assert res["near_threshold_excluded"] <= n_envs // 100
+    assert res["gpu_stats"]["n_steps"] == n_envs * ticks
+    assert 0.02 < res["unsafe_frac"] < 0.6, res  # both verdicts, i.e. all three cascade outcomes occur
+
+
 @pytest.mark.parametrize("n_envs", [1, 37, 95])
 def test_ragged_batches_match_checker(n_envs):
     """Batch sizes that are not a multiple of the 32-env tile / 4-group warp: a one-env batch, partial last tiles, partial
