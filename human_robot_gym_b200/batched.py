@@ -172,16 +172,14 @@ class BatchedSafetyShield:
 
     def tick_device(self, kp: torch.Tensor, t: torch.Tensor, goal_mask: Optional[torch.Tensor] = None,
                     goal_q: Optional[torch.Tensor] = None):
-        """humanMeasurement + [newLongTermTrajectory on goal_mask] + step on already-resident, correctly typed device
-        tensors (kp [N,K,3] f64, t [N] f64, goal_mask [N] u8, goal_q [N,J] f64): three ABI calls, no conversions."""
-        st = self._stream()
-        L, h = self.lib, self._h
-        cabi.check(L.hrg_shield_human_measurement(h, None, kp.data_ptr(), t.data_ptr(), st), "human_measurement")
-        if goal_mask is not None:
-            cabi.check(L.hrg_shield_new_goal(h, goal_mask.data_ptr(), goal_q.data_ptr(), None, st), "new_goal")
-        cabi.check(L.hrg_shield_step(h, t.data_ptr(), self.q.data_ptr(), self.dq.data_ptr(), self.ddq.data_ptr(),
-                                     self.dddq.data_ptr(), self.is_safe.data_ptr(), self.branch.data_ptr(),
-                                     self.status.data_ptr(), st), "step")
+        """[newLongTermTrajectory on goal_mask] + humanMeasurement + step on already-resident, correctly typed device
+        tensors (kp [N,K,3] f64, t [N] f64, goal_mask [N] u8, goal_q [N,J] f64): one ABI call, no conversions."""
+        gm = None if goal_mask is None else goal_mask.data_ptr()
+        gq = None if goal_mask is None else goal_q.data_ptr()
+        cabi.check(self.lib.hrg_shield_tick_device(self._h, kp.data_ptr(), t.data_ptr(), gm, gq, self.q.data_ptr(),
+                                                   self.dq.data_ptr(), self.ddq.data_ptr(), self.dddq.data_ptr(),
+                                                   self.is_safe.data_ptr(), self.branch.data_ptr(),
+                                                   self.status.data_ptr(), self._stream()), "tick_device")
 
     def tick_host(self, kp_host: torch.Tensor, t_host: torch.Tensor, goal_mask_host, goal_q_host, q_host, dq_host,
                   ddq_host, flags_host):

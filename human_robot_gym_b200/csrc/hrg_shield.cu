@@ -80,7 +80,7 @@ struct HrgShield {
   size_t measure_smem = 0;
   // k_replan runs on its own stream, concurrently with the first reach + verify pass (envs that do not replan)
   cudaStream_t side = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_meas = nullptr;
   bool overlap = true;
   bool cascade = true;  // verification cascade for pass 0 (HRG_NO_CASCADE=1 or stored capsules: full kernel)
   int replan_blocks_per_sm = 12;  // resident 64-thread replan blocks per SM while overlapped with k_reach_verify pass 0 (measured best)
@@ -236,6 +236,7 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
+  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_meas, cudaEventDisableTiming);
   for (int k = 0; k < 2 && ce == cudaSuccess; ++k) {
     ce = cudaEventCreateWithFlags(&h->ev_up[k], cudaEventDisableTiming);
     if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_done[k], cudaEventDisableTiming);
@@ -279,6 +280,7 @@ int hrg_shield_destroy(HrgShield* s) {
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
   if (s->ev_fork) cudaEventDestroy(s->ev_fork);
   if (s->ev_join) cudaEventDestroy(s->ev_join);
+  if (s->ev_meas) cudaEventDestroy(s->ev_meas);
   for (int k = 0; k < 2; ++k) {
     if (s->ev_up[k]) cudaEventDestroy(s->ev_up[k]);
     if (s->ev_done[k]) cudaEventDestroy(s->ev_done[k]);
@@ -349,9 +351,11 @@ static void verify_pass0(HrgShield* s, cudaStream_t st, size_t smem) {
   }
 }
 
-int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
-                    uint8_t* branch, uint32_t* status, void* stream) {
-  if (!s || !t) return fail(HRG_EINVAL, "hrg_shield_step: NULL argument");
+// One tick's launches. `kp` != NULL folds humanMeasurement(kp, t) into the tick: the keypoints are only read by reach +
+// verify (and last_meas by the path planning), so k_measure runs on the main stream next to the start of the replan chain
+// instead of in front of it.
+static int step_impl(HrgShield* s, const double* kp, const double* t, double* q, double* dq, double* ddq, double* dddq,
+                     uint8_t* is_safe, uint8_t* branch, uint32_t* status, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int N = s->S.N;
   const bool prof = s->prof && s->ev_used + 5 <= s->ev.size();
@@ -361,6 +365,10 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
     cudaEventRecord(ev[0], st);
   }
   const bool fork = s->overlap && !prof;
+  if (kp && !fork) {
+    k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
+    s->launches++;
+  }
   k_pre<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S);
   if (!fork) k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
   if (prof) cudaEventRecord(ev[1], st);
@@ -379,6 +387,13 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
     k_replan_opt<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     k_replan_scale<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
     k_replan_deep<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
+    if (fork && kp) {
+      // lane 0's tail of k_replan_sample reads last_meas: k_measure (main stream) must be through by then
+      k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
+      s->launches++;
+      CK(cudaEventRecord(s->ev_meas, st));
+      CK(cudaStreamWaitEvent(s->side, s->ev_meas, 0));
+    }
     if (s->pfl)
       k_replan_sample<true><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
     else
@@ -402,6 +417,23 @@ int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double
   return HRG_OK;
 }
 
+int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
+                    uint8_t* branch, uint32_t* status, void* stream) {
+  if (!s || !t) return fail(HRG_EINVAL, "hrg_shield_step: NULL argument");
+  return step_impl(s, nullptr, t, q, dq, ddq, dddq, is_safe, branch, status, stream);
+}
+
+int hrg_shield_tick_device(HrgShield* s, const double* keypoints, const double* t, const uint8_t* goal_mask,
+                           const double* goal_q, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
+                           uint8_t* branch, uint32_t* status, void* stream) {
+  if (!s || !keypoints || !t) return fail(HRG_EINVAL, "hrg_shield_tick_device: NULL argument");
+  if (goal_mask && goal_q) {
+    const int rc = hrg_shield_new_goal(s, goal_mask, goal_q, nullptr, stream);
+    if (rc) return rc;
+  }
+  return step_impl(s, keypoints, t, q, dq, ddq, dddq, is_safe, branch, status, stream);
+}
+
 int hrg_shield_tick_host(HrgShield* s, const double* keypoints_host, const double* t_host,
                          const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
                          double* ddq_host, uint8_t* flags_host, void* stream) {
@@ -410,15 +442,13 @@ int hrg_shield_tick_host(HrgShield* s, const double* keypoints_host, const doubl
   const size_t N = s->S.N, J = s->S.J, K3 = (size_t)s->S.K * 3;
   CK(cudaMemcpyAsync(s->d_kp, keypoints_host, N * K3 * sizeof(double), cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(s->d_t, t_host, N * sizeof(double), cudaMemcpyHostToDevice, st));
-  int rc = hrg_shield_human_measurement(s, nullptr, s->d_kp, s->d_t, stream);
-  if (rc) return rc;
-  if (goal_mask_host && goal_q_host) {
+  const bool goal = goal_mask_host && goal_q_host;
+  if (goal) {
     CK(cudaMemcpyAsync(s->d_goal_mask, goal_mask_host, N, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(s->d_goal, goal_q_host, N * J * sizeof(double), cudaMemcpyHostToDevice, st));
-    rc = hrg_shield_new_goal(s, s->d_goal_mask, s->d_goal, nullptr, stream);
-    if (rc) return rc;
   }
-  rc = hrg_shield_step(s, s->d_t, s->d_q, s->d_dq, s->d_ddq, nullptr, s->d_safe, s->d_branch, nullptr, stream);
+  const int rc = hrg_shield_tick_device(s, s->d_kp, s->d_t, goal ? s->d_goal_mask : nullptr, goal ? s->d_goal : nullptr,
+                                        s->d_q, s->d_dq, s->d_ddq, nullptr, s->d_safe, s->d_branch, nullptr, stream);
   if (rc) return rc;
   if (q_host) CK(cudaMemcpyAsync(q_host, s->d_q, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
   if (dq_host) CK(cudaMemcpyAsync(dq_host, s->d_dq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -456,13 +486,10 @@ int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_ho
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t N = s->S.N, J = s->S.J;
   CK(cudaStreamWaitEvent(st, s->ev_up[slot], 0));
-  int rc = hrg_shield_human_measurement(s, nullptr, s->d_kp2[slot], s->d_t2[slot], stream);
-  if (rc) return rc;
-  if (s->slot_has_goal[slot]) {
-    rc = hrg_shield_new_goal(s, s->d_goal_mask2[slot], s->d_goal2[slot], nullptr, stream);
-    if (rc) return rc;
-  }
-  rc = hrg_shield_step(s, s->d_t2[slot], s->d_q, s->d_dq, s->d_ddq, nullptr, s->d_safe, s->d_branch, nullptr, stream);
+  const bool goal = s->slot_has_goal[slot];
+  const int rc = hrg_shield_tick_device(s, s->d_kp2[slot], s->d_t2[slot], goal ? s->d_goal_mask2[slot] : nullptr,
+                                        goal ? s->d_goal2[slot] : nullptr, s->d_q, s->d_dq, s->d_ddq, nullptr, s->d_safe,
+                                        s->d_branch, nullptr, stream);
   if (rc) return rc;
   CK(cudaEventRecord(s->ev_done[slot], st));
   s->slot_used[slot] = true;

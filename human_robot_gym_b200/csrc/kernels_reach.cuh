@@ -20,6 +20,13 @@ constexpr int kHumDoubles = 11;
 // 0.750 ms / tick).
 #define HRG_REACH_MINBLOCKS 2
 #endif
+// The cascade kernels hold fewer live values (two spheres / one model) and are latency bound: more, leaner blocks.
+#ifndef HRG_CASCADE_MINBLOCKS
+#define HRG_CASCADE_MINBLOCKS 3
+#endif
+#ifndef HRG_STAGE_MINBLOCKS
+#define HRG_STAGE_MINBLOCKS 3
+#endif
 
 // HumanReach::measurement (SS/src/human_reach.cc:52-74): vel = (new - old) * (1 / dt) when a previous measurement
 // exists and dt >= 1e-7; pos = new; last_meas = t. kp_in is the caller's [N][K][3] array; one block transposes a tile
@@ -85,7 +92,8 @@ __host__ __device__ inline int reach_smem_doubles(int J, int H) {
 // min_dist of a model that was not needed stays +inf. Handles that store capsules / distances for the getters run the
 // full kernel instead.
 template <int PARTS, bool CASCADE = false>
-__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS, PARTS == 1 ? HRG_REACH_MINBLOCKS : 1)
+__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS,
+                                  PARTS == 1 ? (CASCADE ? HRG_CASCADE_MINBLOCKS : HRG_REACH_MINBLOCKS) : 1)
     k_reach_verify(DevState S, int pass) {
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
@@ -265,7 +273,7 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS, PARTS == 1 ? HRG_
 // warp = robot link (its swept capsule comes from link_caps_buf), human capsules of that model only. An env that the
 // model clears becomes safe; otherwise it goes on to the Accel stage or stays unsafe.
 template <int MODEL>
-__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_REACH_MINBLOCKS) k_verify_stage(DevState S) {
+__global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_STAGE_MINBLOCKS) k_verify_stage(DevState S) {
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
   __shared__ unsigned bits_s[HRG_MAX_JOINTS][kTileEnvs];

@@ -136,6 +136,14 @@ int hrg_shield_store_capsules(HrgShield* s, int on);
 int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double* ddq, double* dddq,
                     uint8_t* is_safe, uint8_t* branch, uint32_t* status, void* stream);
 
+/* One control tick on DEVICE-resident inputs: [newLongTermTrajectory(goal_q) for the envs of goal_mask] +
+ * humanMeasurement(keypoints, t) + step(t) — failsafe_controller.py:300,310,329. Same results as the three separate calls;
+ * the measurement kernel is scheduled next to the start of the replan chain instead of in front of it (only reach + verify
+ * read the keypoints). goal_mask / goal_q may be NULL (no new goals this tick). Outputs as hrg_shield_step. */
+int hrg_shield_tick_device(HrgShield* s, const double* keypoints, const double* t, const uint8_t* goal_mask,
+                           const double* goal_q, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
+                           uint8_t* branch, uint32_t* status, void* stream);
+
 /* humanMeasurement + [newLongTermTrajectory for masked envs] + step with HOST buffers: one H2D of the inputs, the
  * kernels, one D2H of the setpoints, all on `stream`; the caller synchronises the stream. goal_mask/goal_q may be NULL.
  * out_host [N, 3J+1] doubles per env: q[J], dq[J], ddq[J], then is_safe + 2*branch packed as a double is NOT used —
