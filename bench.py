@@ -330,13 +330,15 @@ def main():
         L_mean = counts[8] / n_ok
         replans_per_step = counts[5] / max(1, S) / world
         # ALGORITHMIC bytes per launch group (FP64 state, nothing recomputable counted):
-        #   k_pre_plan      3 paths in/out 480, scalars/flags 40, prev dq 8J, 2 LTT samples 64J; writes the current motion
-        #                   32J+8 and the reach inputs 24J+16
+        #   k_pre_plan      = k_measure + k_pre + k_plan (the measurement is part of hrg_shield_tick_device): new keypoints
+        #                   in 24K, previous positions in 24K, positions + velocities out 48K; 3 paths in/out 480,
+        #                   scalars/flags 40, prev dq 8J, 2 LTT samples 64J; writes the current motion 32J+8 and the reach
+        #                   inputs 24J+16
         #   k_replan_*      per REPLANNING env: the new LTT 32*J*L plus goal/current state 40J
         #   k_reach_verify  keypoint positions + velocities 48K, reach inputs 24J+16, base pose 96, flags 8; writes 24+4
         #   k_select        3 paths in 240, one out 80, one LTT sample 32J, outputs 32J, prev dq 8J, flags 16
         alg_bytes = {
-            "k_pre_plan": N * (544 + 128 * J),
+            "k_pre_plan": N * (544 + 128 * J + 96 * K),
             "k_replan": replans_per_step * (32 * J * L_mean + 40 * J),
             "k_reach_verify": N * (48 * K + 24 * J + 148),
             "k_select": N * (336 + 72 * J),
