@@ -354,7 +354,8 @@ static void verify_pass0(HrgShield* s, cudaStream_t st, size_t smem) {
 // One tick's launches. `kp` != NULL folds humanMeasurement(kp, t) into the tick: the keypoints are only read by reach +
 // verify (and last_meas by the path planning), so k_measure runs on the main stream next to the start of the replan chain
 // instead of in front of it.
-static int step_impl(HrgShield* s, const double* kp, const double* t, double* q, double* dq, double* ddq, double* dddq,
+static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, const double* goal_q, const double* t,
+                     double* q, double* dq, double* ddq, double* dddq,
                      uint8_t* is_safe, uint8_t* branch, uint32_t* status, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int N = s->S.N;
@@ -369,7 +370,7 @@ static int step_impl(HrgShield* s, const double* kp, const double* t, double* q,
     k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
     s->launches++;
   }
-  k_pre<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S);
+  k_pre<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, goal_mask, goal_q);
   if (!fork) k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
   if (prof) cudaEventRecord(ev[1], st);
   cudaStream_t rs = fork ? s->side : st;
@@ -420,18 +421,16 @@ static int step_impl(HrgShield* s, const double* kp, const double* t, double* q,
 int hrg_shield_step(HrgShield* s, const double* t, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
                     uint8_t* branch, uint32_t* status, void* stream) {
   if (!s || !t) return fail(HRG_EINVAL, "hrg_shield_step: NULL argument");
-  return step_impl(s, nullptr, t, q, dq, ddq, dddq, is_safe, branch, status, stream);
+  return step_impl(s, nullptr, nullptr, nullptr, t, q, dq, ddq, dddq, is_safe, branch, status, stream);
 }
 
 int hrg_shield_tick_device(HrgShield* s, const double* keypoints, const double* t, const uint8_t* goal_mask,
                            const double* goal_q, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe,
                            uint8_t* branch, uint32_t* status, void* stream) {
   if (!s || !keypoints || !t) return fail(HRG_EINVAL, "hrg_shield_tick_device: NULL argument");
-  if (goal_mask && goal_q) {
-    const int rc = hrg_shield_new_goal(s, goal_mask, goal_q, nullptr, stream);
-    if (rc) return rc;
-  }
-  return step_impl(s, keypoints, t, q, dq, ddq, dddq, is_safe, branch, status, stream);
+  const bool goal = goal_mask && goal_q;
+  return step_impl(s, keypoints, goal ? goal_mask : nullptr, goal ? goal_q : nullptr, t, q, dq, ddq, dddq, is_safe, branch,
+                   status, stream);
 }
 
 int hrg_shield_tick_host(HrgShield* s, const double* keypoints_host, const double* t_host,

@@ -18,10 +18,13 @@ __global__ void k_new_goal(DevState S, const uint8_t* __restrict__ mask, const d
 
 // First part of step() for every env: current motion, LTT commit, replan trigger -> compacted replan list. Kept apart
 // from k_plan because the replan chain - the critical path of the tick - only waits for this much.
-__global__ void __launch_bounds__(kTickBlock) k_pre(DevState S) {
+// goal_mask / goal_q != NULL: newLongTermTrajectory for the masked envs first (the tick entry points fold k_new_goal in).
+__global__ void __launch_bounds__(kTickBlock) k_pre(DevState S, const uint8_t* __restrict__ goal_mask,
+                                                    const double* __restrict__ goal_q) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= S.N) return;
   const HrgConfig& c = *S.cfg;
+  if (goal_mask && goal_mask[e]) new_goal_env(S, c, e, goal_q + (size_t)e * S.J);
   uint32_t f = S.flags[e];
   const bool replan = pre_env(S, c, e, f);
   if (replan) {
