@@ -118,6 +118,12 @@ SYMBOLS = {
     "hrg_last_error": (C.c_char_p, []),
     "hrg_controller_set_goal": (C.c_int, [C.c_void_p, C.POINTER(HrgControllerConfig), _u8p, _dp, _dp, _dp, _dp, _vp]),
     "hrg_controller_torques": (C.c_int, [C.c_void_p, C.POINTER(HrgControllerConfig)] + [_dp] * 8 + [_vp]),
+    "hrg_human_create": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "hrg_human_destroy": (C.c_int, [C.c_void_p]),
+    "hrg_human_reset": (C.c_int, [C.c_void_p, _u8p, _dp, _i32p, _vp]),
+    "hrg_human_keypoints": (C.c_int, [C.c_void_p, C.c_void_p, _dp, _i32p, _i32p, _vp]),
+    "hrg_human_launch_count": (C.c_int64, [C.c_void_p]),
     "hrg_stage_capsule_dist": (C.c_int, [C.c_int, _dp, _dp, _dp, _vp]),
     "hrg_stage_plan_safety_shield": (C.c_int, [C.c_double, C.c_int, _dp, _u8p, _dp, _dp, _vp]),
     "hrg_stage_ltp_plan": (C.c_int, [C.POINTER(HrgConfig), C.c_int, _dp, _dp, _dp, _dp, _dp, _i32p, C.c_int, _vp]),

@@ -199,6 +199,38 @@ int hrg_controller_torques(HrgShield* s, const HrgControllerConfig* cfg, const d
                            const double* ddq_des, const double* joint_pos, const double* joint_vel,
                            const double* mass_matrix, const double* torque_comp, double* torques, void* stream);
 
+/* ---- animation -> keypoints: the human of human-robot-gym is a replay of recorded clips ---------------
+ * Replaces, for the shield's input, `_control_human` + `sim.forward()` + `sim.data.get_site_xpos("Human_" + element)`
+ * (HRG/environments/manipulation/human_env.py:1710-1767, :459-463): the kinematic tree of
+ * HRG/models/assets/human/human.xml (mocap Pelvis, then per body three hinges z, y, x about the body's site) evaluated on
+ * the device for N envs, each replaying its own list of clips with its own placement.
+ * Only the placement depends on the env, so hrg_human_create walks the tree ONCE per frame of the clip bank (k_human_bake)
+ * and hrg_human_keypoints is a gather + rigid transform per env per tick (csrc/kernels_human.cuh). */
+typedef struct HrgHuman HrgHuman;
+
+/* Tree: n_bodies bodies below the Pelvis in parent-before-child order (the order of HumanObject.joint_elements,
+ * HRG/models/objects/human/human.py:58-82, = the keypoint order of mujoco_mocap.yaml); parent[b] = -1 for children of the
+ * Pelvis; anchor [n_bodies,3] = joint/site position in the (common, untransformed) body frame. All HOST pointers.
+ * Clips: frames [sum(clip_len), 7 + 3 n_bodies] = Pelvis_pos xyz, Pelvis_quat xyzw, then angle x,y,z per body (radians);
+ * clip_info [n_clips,7] = position_offset xyz + orientation_quat xyzw of the clip's *_info.json.
+ * step_length = simulation_step_freq / human_animation_freq (human_env.py:1462-1465); list_len = clips per env list
+ * (`_n_animations_to_sample_at_resets`). */
+int hrg_human_create(int n_bodies, const int32_t* parent_host, const double* anchor_host, int n_clips,
+                     const int32_t* clip_len_host, const double* frames_host, const double* clip_info_host,
+                     double step_length, int n_envs, int list_len, int device, HrgHuman** out);
+int hrg_human_destroy(HrgHuman* h);
+/* Env reset (human_env.py:1640-1657): placement [N,7] = human_pos_offset xyz + human_rot_offset quat wxyz; clip_list
+ * [N,list_len] = the env's `_human_animation_ids`; index, animation_start_time := 0. DEVICE pointers, env_mask [N] u8 or
+ * NULL (all). Envs replay clip 0 at the origin until their first reset. */
+int hrg_human_reset(HrgHuman* h, const uint8_t* env_mask, const double* placement, const int32_t* clip_list,
+                    void* stream);
+/* `_control_human(force_update=True)` at low_level_time [N] (i64, DEVICE) for every env, then the site positions:
+ * keypoints [N,n_bodies,3] (DEVICE) in the layout hrg_shield_human_measurement / hrg_shield_tick_device consume.
+ * clip_out, frame_out [N] i32 or NULL: which clip / frame each env showed. */
+int hrg_human_keypoints(HrgHuman* h, const int64_t* low_level_time, double* keypoints, int32_t* clip_out,
+                        int32_t* frame_out, void* stream);
+int64_t hrg_human_launch_count(const HrgHuman* h);
+
 /* ---- per-stage entry points (parity tests + ncu); all DEVICE pointers --------------------------------------- */
 /* capsule_capsule_dist (RL/include/intersections.hpp:105-124) for n independent pairs: c1,c2 [n,7] -> dist [n]. */
 int hrg_stage_capsule_dist(int n, const double* c1, const double* c2, double* dist, void* stream);

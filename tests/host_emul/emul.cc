@@ -14,6 +14,7 @@
 #include "../../human_robot_gym_b200/csrc/ltp_math.cuh"
 #include "../../human_robot_gym_b200/csrc/step_logic.cuh"
 #include "../../human_robot_gym_b200/csrc/pfl_math.cuh"
+#include "../../human_robot_gym_b200/csrc/kernels_human.cuh"
 
 using namespace hrg;
 
@@ -341,4 +342,22 @@ int emul_human_capsules(const HrgConfig* cfg, const double* kp, const double* kv
   for (int h = 0; h < H; ++h) cap_store(human_capsule(*cfg, h, kp, kv, 1, t_reach), out + 7 * h);
   return H;
 }
+// Animation -> keypoints for n (frame row, clip info, placement) triples through the functions k_human_keypoints calls.
+int emul_human_keypoints(int K, const int32_t* parent, const double* anchor, int n, const double* rows,
+                         const double* info, const double* place, double* out) {
+  HumanTreeDev T;
+  if (int rc = human_build_tree(K, parent, anchor, &T)) return rc;
+  const int C = 7 + 3 * K;
+  std::vector<double> baked(3 + 3 * K);
+  for (int i = 0; i < n; ++i) {  // bake the row (k_human_bake), then place it (k_human_reset + k_human_keypoints)
+    double tab[12], P[12];
+    human_clip_table(info + (size_t)i * 7, tab);
+    human_bake_row(T, rows + (size_t)i * C, tab, baked.data());
+    human_placement(place + (size_t)i * 7, P);
+    for (int k = 0; k < 3; ++k) P[k] = P[k] + baked[k];
+    for (int c = 0; c < 3 * K; ++c) out[(size_t)i * 3 * K + c] = human_apply(P, baked.data() + 3 + 3 * (c / 3), c % 3);
+  }
+  return 0;
+}
+
 }

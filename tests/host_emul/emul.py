@@ -39,6 +39,8 @@ def lib():
         L.emul_ltp_time_scaling.argtypes = [D, _p, D, D, D, D, D, D, _p, _p, _p]
         L.emul_ltt_interpolate.argtypes = [C.c_int, C.c_int, _p, D, C.c_int, C.c_int, _p, _p, _p, _p]
         L.emul_human_capsules.argtypes = [C.POINTER(HrgConfig), _p, _p, D, _p]
+        L.emul_human_keypoints.restype = C.c_int
+        L.emul_human_keypoints.argtypes = [C.c_int, _p, _p, C.c_int, _p, _p, _p, _p]
         L.emul_poly_root.restype = C.c_double
         L.emul_poly_root.argtypes = [_p, C.c_int]
         _lib = L
@@ -165,4 +167,17 @@ def human_capsules(cfg, kp, kv, t_reach):
     H = cfg.n_ext + 2 * cfg.n_bodies
     out = np.zeros((H, 7))
     lib().emul_human_capsules(C.byref(cfg), _ptr(_a(kp)), _ptr(_a(kv)), t_reach, _ptr(out))
+    return out
+
+
+def human_keypoints(tree, rows, info, place):
+    """[n,K,3] site positions from frame rows [n,7+3K], clip info [n,7] and placements [n,7] (kernels_human.cuh on the host)."""
+    K = len(tree["names"])
+    rows, info, place = _a(rows), _a(info), _a(place)
+    n = rows.shape[0]
+    out = np.zeros((n, K, 3))
+    parent, anchor = _a(tree["parent"], np.int32), _a(tree["anchor"])
+    rc = lib().emul_human_keypoints(K, _ptr(parent), _ptr(anchor), n, _ptr(rows), _ptr(info), _ptr(place), _ptr(out))
+    if rc:
+        raise ValueError(f"human_build_tree failed with {rc}")
     return out

@@ -75,7 +75,7 @@ def make_checker(files, n, base_pose, init_q, sample_time=0.004, shield_type=1, 
 
 def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0", sample_time=0.004, shield_type=1,
                         goal_period=25, stagger=True, ltt_capacity=1024, base_pose=None, collect=None,
-                        store_capsules=True):
+                        store_capsules=True, human=None):
     """Drives BatchedSafetyShield (CUDA) and the CPU checker in lockstep on identical synthetic inputs.
 
     Decisions (is_safe, branch) must match exactly; an env whose FIRST mismatch happens on a tick where either side
@@ -85,6 +85,9 @@ def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0"
     store_capsules=False is the product configuration: reach + verify then runs as the model cascade (a human model that
     is not needed for the verdict is not evaluated, its min_dist stays +inf), and only the distances of the models that
     were evaluated are compared.
+
+    human: None for the synthetic human, else an object with checker_keypoints(k) -> [n,K,3] numpy (the checker's input)
+    and device_keypoints(k) -> [n,K,3] CUDA tensor (the CUDA path's input), e.g. the recorded-animation replay.
     """
     import torch
 
@@ -107,9 +110,9 @@ def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0"
     phase = (np.arange(n_envs) % goal_period) if stagger else np.zeros(n_envs, int)
     for k in range(ticks):
         t = k * sample_time
-        kp = scen.keypoints(t)
+        kp = scen.keypoints(t) if human is None else human.checker_keypoints(k)
         chk.human_measurement(kp, t)
-        gpu.humanMeasurement(torch.from_numpy(kp), t)
+        gpu.humanMeasurement(torch.from_numpy(kp) if human is None else human.device_keypoints(k), t)
         gmask = (phase == (k % goal_period))
         if gmask.any():
             g = scen.next_goal(gmask)
