@@ -144,6 +144,17 @@ class BatchedSafetyShield:
                    "hrg_shield_set_ltt")
         return verdict.value
 
+    def ltt_max_window(self, index=None, window_k: int = 0):
+        """getMaxAccelerationWindow(index) / getMaxJerkWindow(index) of every env's live LTT -> ([N,J], [N,J]).
+        index: [N] int32 tensor, or None for each env's path_s_discrete_; window_k 0 = the shield's sliding_window_k_."""
+        f64 = dict(dtype=torch.float64, device=self.device)
+        acc, jerk = torch.empty(self.n_envs, self.J, **f64), torch.empty(self.n_envs, self.J, **f64)
+        idx = None if index is None else torch.as_tensor(index, dtype=torch.int32, device=self.device).contiguous()
+        with torch.cuda.device(self.device):
+            cabi.check(self.lib.hrg_shield_ltt_max_window(self._h, _ptr(idx), int(window_k), _ptr(acc), _ptr(jerk),
+                                                          self._stream()), "hrg_shield_ltt_max_window")
+        return acc, jerk
+
     def stats(self, clear=False) -> dict:
         cabi.check(self.lib.hrg_shield_stats(self._h, _ptr(self._stats), int(clear), self._stream()), "hrg_shield_stats")
         v = self._stats.cpu()

@@ -109,6 +109,7 @@ SYMBOLS = {
     "hrg_shield_upload_inputs": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [_vp]),
     "hrg_shield_tick_staged": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [_vp]),
     "hrg_shield_get_capsules": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _vp]),
+    "hrg_shield_ltt_max_window": (C.c_int, [C.c_void_p, _i32p, C.c_int, _dp, _dp, _vp]),
     "hrg_shield_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _vp]),
     "hrg_shield_profile": (C.c_int, [C.c_void_p, C.c_int]),
     "hrg_shield_profile_read": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

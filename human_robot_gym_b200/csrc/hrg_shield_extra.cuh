@@ -17,6 +17,43 @@ __global__ void k_copy_stats(HrgStats* dst, HrgStats* src, int clear) {
   }
 }
 
+// LongTermTraj::getMaxAccelerationWindow / getMaxJerkWindow (SS/include/safety_shield/long_term_traj.h:243-259) of every env's
+// live LTT. The reference fills max_acceleration_window_ / max_jerk_window_ for ALL samples whenever an LTT is built
+// (calculate_max_acc_jerk_window, SS/src/long_term_traj.cc:79-159: entry t = max over samples [t, min(t + k, L)) of the
+// signed ddq / dddq) although nothing on the step path reads them (safety_shield.cc:392); here the window that is asked for
+// is evaluated on demand - a maximum is exact, so the values are bit-identical. Warp per env: lanes = (sample group,
+// column of the contiguous [ddq | dddq] half of a sample), groups merged by shuffle.
+__global__ void k_ltt_max_window(DevState S, const int32_t* __restrict__ index, int window_k, double* __restrict__ max_acc,
+                                 double* __restrict__ max_jerk) {
+  const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (e >= S.N) return;
+  const int J = S.J, W = 2 * J, G = 32 / W;
+  const int live = (S.flags[e] & F_LIVE_SLOT) ? 1 : 0;
+  const size_t m = (size_t)live * S.N + e;
+  const int len = S.ltt_len[m];
+  const int k = min(len, window_k);  // long_term_traj.cc:82
+  const int t = ltt_index(index ? index[e] : S.path_sd[e], S.ltt_start[m], len, S.ltt_cur[m]);
+  const int g = lane / W, c = lane - g * W;
+  double best = -INFINITY;
+  if (g < G)
+    for (int i = t + g; i < min(t + k, len); i += G) best = fmax(best, ltt_sample(S, e, live, i)[W + c]);
+  for (int h = G >> 1; h >= 1; h >>= 1) {  // G is 2 for J = 6..8, 4 for J = 4, ...: fold the groups onto group 0
+    const double o = __shfl_down_sync(0xffffffffu, best, h * W);
+    if (g < h) best = fmax(best, o);
+  }
+  if (G > 1 && (G & (G - 1))) {  // G not a power of two (J = 5: G = 3): fold the last group explicitly
+    const double o = __shfl_down_sync(0xffffffffu, best, (G - 1) * W);
+    if (g == 0) best = fmax(best, o);
+  }
+  if (g == 0) {
+    if (c < J) {
+      if (max_acc) max_acc[(size_t)e * J + c] = best;
+    } else if (max_jerk) {
+      max_jerk[(size_t)e * J + (c - J)] = best;
+    }
+  }
+}
+
 // SafetyShield::setLongTermTrajectory (SS/src/safety_shield.cc:699-730) for one env; traj already on the device.
 __global__ void k_set_ltt(DevState S, int e, const double* __restrict__ traj, int length, double sample_time,
                           int starting_index, const double* __restrict__ alpha, int32_t* verdict) {
@@ -248,6 +285,16 @@ int hrg_stage_reach_verify(const HrgConfig* cfg, int n, const double* base_pose,
 static int ctrl_check(const HrgShield* s, const HrgControllerConfig* k, const char* who) {
   if (!s || !k) return fail(HRG_EINVAL, who);
   if (k->nb_joints != s->S.J) return fail(HRG_EINVAL, "controller nb_joints differs from the shield's");
+  return HRG_OK;
+}
+
+int hrg_shield_ltt_max_window(HrgShield* s, const int32_t* index, int window_k, double* max_acc, double* max_jerk,
+                              void* stream) {
+  if (!s) return fail(HRG_EINVAL, "hrg_shield_ltt_max_window: NULL handle");
+  if (window_k <= 0) window_k = (int)floor(s->cfg.max_s_stop / s->cfg.sample_time);  // sliding_window_k_ (safety_shield.cc:88)
+  k_ltt_max_window<<<grid_for(s->S.N, 4), 128, 0, static_cast<cudaStream_t>(stream)>>>(s->S, index, window_k, max_acc, max_jerk);
+  s->launches++;
+  CK(cudaGetLastError());
   return HRG_OK;
 }
 

@@ -169,6 +169,14 @@ int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_ho
  * Any pointer may be NULL. */
 int hrg_shield_get_capsules(HrgShield* s, double* robot, double* human, double* min_dist, void* stream);
 
+/* LongTermTraj.getMaxAccelerationWindow(index) / getMaxJerkWindow(index) - SS/include/safety_shield/long_term_traj.h:243-259,
+ * SS/src/long_term_traj.cc:79-159 - of every env's live long-term trajectory: per joint the maximum of the signed
+ * acceleration / jerk over samples [t, min(t + k, L)), t = getTrajectoryIndex(index). index [N] i32 or NULL (each env's
+ * path_s_discrete_); window_k <= 0: the shield's sliding_window_k_ = floor(max_s_stop / sample_time). max_acc, max_jerk [N,J]
+ * (either may be NULL). Evaluated on demand (the step path never reads the windows, safety_shield.cc:392). */
+int hrg_shield_ltt_max_window(HrgShield* s, const int32_t* index, int window_k, double* max_acc, double* max_jerk,
+                              void* stream);
+
 /* Accumulated statistics since the last clear; `out` is a DEVICE pointer to one HrgStats. */
 int hrg_shield_stats(HrgShield* s, HrgStats* out, int clear, void* stream);
 

@@ -46,6 +46,8 @@ def lib():
         L.ref_ltp_time_scaling.argtypes = [C.c_double, _dp] + [C.c_double] * 6 + [_dp, _dp, C.POINTER(C.c_int)]
         L.ref_ltt_interpolate.argtypes = [C.c_int, C.c_int, _dp, C.c_double, C.c_int, C.c_int, _dp, _dp, _dp, _dp, _dp]
         L.ref_human_reach.restype = C.c_int
+        L.ref_ltt_max_window.argtypes = [C.c_int, C.c_int, _dp, C.c_double, C.c_int, _dp, _dp]
+        L.ref_live_max_window.argtypes = [C.c_void_p, C.c_void_p, _dp, _dp]
         L.ref_human_reach.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, _dp, C.c_int]
         L.ref_poly_roots.restype = C.c_double
         L.ref_poly_roots.argtypes = [C.c_int, _dp, _dp, _dp]
@@ -125,6 +127,15 @@ class RefBatch:
         lib().ref_get_capsules(self.h, _d(robot), _d(human), int(H), _d(md))
         return robot, human, md
 
+    def live_max_window(self, index=None):
+        """getMaxAccelerationWindow / getMaxJerkWindow(index) of every env's live LTT -> ([n,J], [n,J]);
+        index [n] int32 or None (each env's path_s_discrete_)."""
+        J = lib().ref_num_joints(self.h)
+        acc, jerk = np.zeros((self.n, J)), np.zeros((self.n, J))
+        idx = None if index is None else np.ascontiguousarray(index, dtype=np.int32)
+        lib().ref_live_max_window(self.h, None if idx is None else idx.ctypes.data, _d(acc), _d(jerk))
+        return acc, jerk
+
     def state(self, i):
         out = np.zeros(63)
         lib().ref_get_state(self.h, int(i), _d(out))
@@ -198,3 +209,12 @@ def ltt_interpolate(traj, sample_time, sdd, v_max, a_max, j_max, starting_index=
     lib().ref_ltt_interpolate(J, L, _d(traj), float(sample_time), int(starting_index), sdd.shape[0], _d(sdd),
                               _d(_f64(v_max)), _d(_f64(a_max)), _d(_f64(j_max)), _d(out))
     return out
+
+
+def ltt_max_window(traj, sample_time, k):
+    """LongTermTraj(traj, sample_time, 0, k).max_acceleration_window_ / max_jerk_window_ -> ([L,J], [L,J])."""
+    traj = _f64(traj)
+    L, _, J = traj.shape
+    acc, jerk = np.zeros((L, J)), np.zeros((L, J))
+    lib().ref_ltt_max_window(J, L, _d(traj), float(sample_time), int(k), _d(acc), _d(jerk))
+    return acc, jerk

@@ -281,6 +281,39 @@ void ref_ltt_interpolate(int J, int L, const double* traj, double sample_time, i
   }
 }
 
+// LongTermTraj::calculate_max_acc_jerk_window (SS/src/long_term_traj.cc:79-159) through the constructor, on a caller-supplied
+// trajectory [L][4][J]: the full tables max_acceleration_window_ / max_jerk_window_ [L][J].
+void ref_ltt_max_window(int J, int L, const double* traj, double sample_time, int k, double* out_acc, double* out_jerk) {
+  std::vector<Motion> ms;
+  for (int i = 0; i < L; ++i) {
+    const double* p = traj + static_cast<size_t>(i) * 4 * J;
+    ms.emplace_back(i * sample_time, std::vector<double>(p, p + J), std::vector<double>(p + J, p + 2 * J),
+                    std::vector<double>(p + 2 * J, p + 3 * J), std::vector<double>(p + 3 * J, p + 4 * J));
+  }
+  safety_shield::LongTermTraj ltt(ms, sample_time, 0, k);
+  for (int i = 0; i < L; ++i)
+    for (int j = 0; j < J; ++j) {
+      out_acc[static_cast<size_t>(i) * J + j] = ltt.max_acceleration_window_[i][j];
+      out_jerk[static_cast<size_t>(i) * J + j] = ltt.max_jerk_window_[i][j];
+    }
+}
+
+// getMaxAccelerationWindow(index) / getMaxJerkWindow(index) of the live LTT of every env (index = path_s_discrete_).
+void ref_live_max_window(void* h, const int32_t* index /*[n] or NULL*/, double* out_acc /*[n,J]*/, double* out_jerk /*[n,J]*/) {
+  RefBatch* B = static_cast<RefBatch*>(h);
+  for (size_t i = 0; i < B->env.size(); ++i) {
+    SafetyShield& s = *B->env[i];
+    const int J = s.nb_joints_;
+    const int idx = index ? index[i] : s.path_s_discrete_;
+    std::vector<double> a = s.long_term_trajectory_.getMaxAccelerationWindow(idx);
+    std::vector<double> jk = s.long_term_trajectory_.getMaxJerkWindow(idx);
+    for (int j = 0; j < J; ++j) {
+      out_acc[i * J + j] = a[j];
+      out_jerk[i * J + j] = jk[j];
+    }
+  }
+}
+
 // HumanReach::humanReachabilityAnalysis (SS/src/human_reach.cc:76-87) of env i on its stored measurement; returns the
 // number of capsules written as Pos, Vel, Accel (7 doubles each).
 int ref_human_reach(void* h, int i, double t_command, double t_brake, double* out, int max_caps) {

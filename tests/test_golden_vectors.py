@@ -348,3 +348,38 @@ def test_tick_logic_matches_oracle_closed_loop(robot, mocap, traj, n, ticks, see
     assert near <= 1
     assert worst < 1e-9            # north_star tolerance is 1e-5; same IEEE operations give ~1e-13
     assert hist[0] > 0 and hist[2] > 0
+
+
+# ---- sliding-window maxima of a LongTermTraj ----------------------------------------------------------
+def _window_golden():
+    """long_term_traj_tests.cc:66-193 (MaxAccWindowTest / MaxJerkWindowTest): 7 samples, 2 joints, k = 3."""
+    a = np.zeros((7, 4, 2))
+    a[:, 2, 0] = [12, 1, 78, 90, 57, 89, 56]
+    a[:, 2, 1] = [13, 2, 79, 91, 58, 90, 57]
+    a[:, 3] = a[:, 2]  # the jerk test uses the same numbers
+    want = np.array([[78, 79], [90, 91], [90, 91], [90, 91], [89, 90], [89, 90], [56, 57]], dtype=float)
+    return a, want
+
+
+@needs_ref
+def test_max_window_reference_reproduces_its_own_test():
+    a, want = _window_golden()
+    acc, jerk = ref.ltt_max_window(a, 0.001, 3)
+    assert (acc == want).all() and (jerk == want).all()
+
+
+def test_max_window_host_class_matches_golden_and_reference():
+    from human_robot_gym_b200.safety_shield_py import LongTermTraj, Motion
+    a, want = _window_golden()
+    ms = [Motion(i * 0.001, a[i, 0], a[i, 1], a[i, 2], a[i, 3]) for i in range(7)]
+    ltt = LongTermTraj(ms, 0.001, sliding_window_k=3)
+    for i in range(7):
+        assert ltt.getMaxAccelerationWindow(i) == want[i].tolist() and ltt.getMaxJerkWindow(i) == want[i].tolist()
+    if ref.available():  # random trajectories, windows shorter and longer than the trajectory, signed values
+        rng = np.random.default_rng(3)
+        for L, k in ((1, 5), (9, 1), (40, 50), (137, 50)):
+            tr = rng.normal(size=(L, 4, 3))
+            ltt = LongTermTraj([Motion(i * 0.004, *tr[i]) for i in range(L)], 0.004, sliding_window_k=k)
+            acc, jerk = ref.ltt_max_window(tr, 0.004, k)
+            assert (np.array([ltt.getMaxAccelerationWindow(i) for i in range(L)]) == acc).all()
+            assert (np.array([ltt.getMaxJerkWindow(i) for i in range(L)]) == jerk).all()

@@ -276,3 +276,50 @@ def test_host_buffer_ticks_agree():
     assert a.stats()["n_replan"] > 0 and a.stats() == b.stats() == c.stats()
     for x in (a, b, c, d):
         x.close()
+
+
+def test_ltt_max_window_matches_reference():
+    """getMaxAccelerationWindow / getMaxJerkWindow of the live LTT of every env: at the shield's own
+    index, and at explicit indices (before the start, inside, past the end). A maximum adds no rounding of its own, so the
+    values agree as well as the planned trajectories themselves do (tolerance 1e-5, north_star; observed ~1e-12)."""
+    from oracle import ref
+    if not ref.available():
+        pytest.skip("needs oracle/_ref (the window tables are the reference's own)")
+    seen = {"n": 0}
+    rng = np.random.default_rng(5)
+    holder = {}
+
+    def collect(k, a, b):
+        if k % 20 != 19:
+            return
+        gpu, chk = holder["gpu"], holder["chk"]
+        for idx in (None, rng.integers(-5, 400, gpu.n_envs).astype(np.int32)):
+            acc, jerk = gpu.ltt_max_window(index=None if idx is None else torch.from_numpy(idx))
+            ra, rj = chk.live_max_window(idx)
+            d = max(float(np.abs(acc.cpu().numpy() - ra).max()), float(np.abs(jerk.cpu().numpy() - rj).max()))
+            seen["max_diff"] = max(seen.get("max_diff", 0.0), d)
+            seen["nonzero"] = seen.get("nonzero", 0) + int((ra != 0).sum())
+        seen["n"] += 1
+
+    # closed_loop_compare owns both shields; reach them through the factory hooks
+    import human_robot_gym_b200.batched as batched
+    orig_gpu, orig_chk = batched.BatchedSafetyShield, pu.make_checker
+
+    class Spy(orig_gpu):
+        def __init__(self, *a, **kw):
+            super().__init__(*a, **kw)
+            holder["gpu"] = self
+
+    def spy_checker(*a, **kw):
+        c, kind = orig_chk(*a, **kw)
+        holder["chk"] = c
+        return c, kind
+
+    batched.BatchedSafetyShield, pu.make_checker = Spy, spy_checker
+    try:
+        res = pu.closed_loop_compare(pu.default_files("schunk"), n_envs=203, ticks=120, seed=77, collect=collect)
+    finally:
+        batched.BatchedSafetyShield, pu.make_checker = orig_gpu, orig_chk
+    print("ltt_max_window:", seen)
+    assert res["mismatch_excl_near"] == 0 and seen["n"] == 6 and seen["nonzero"] > 1000, (res, seen)
+    assert seen["max_diff"] < 1e-5, seen
