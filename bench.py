@@ -179,14 +179,88 @@ def run_reference(args, files, sc, names, rank):
     print(json.dumps(line), flush=True)
 
 
+def _golden_human():
+    from human_robot_gym_b200.human_animation import load_clips_npz, load_tree_json
+    g = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden")
+    return load_tree_json(os.path.join(g, "human_tree.json")), load_clips_npz(os.path.join(g, "cmu_clips.npz"))
+
+
+def bench_e2e_recorded(shield, args, n, J, dev, goals_h, masks_h, steps, warm, k0, sync_all, world):
+    """Shield-steps/s through the public host API when the human is a clip replay on the device (module docstring of
+    human_robot_gym_b200/human_animation.py). Host wall clock, one stream sync per tick."""
+    import torch
+    import torch.distributed as dist
+    from human_robot_gym_b200.human_animation import BatchedHumanAnimation
+    tree, clips = _golden_human()
+    rng = np.random.default_rng(11)
+    human = BatchedHumanAnimation(tree, clips, n, device=dev, n_animations_per_env=2)
+    yaw = rng.uniform(0, 2 * np.pi, n)
+    quat = np.stack([np.cos(yaw / 2), 0 * yaw, 0 * yaw, np.sin(yaw / 2)], axis=1)
+    place = np.stack([rng.uniform(-2.9, -0.9, n), rng.uniform(-1.0, 1.0, n), np.zeros(n)], axis=1)  # 0.3 .. 1.7 m from the base
+    human.reset(place, quat, rng.integers(0, len(clips), (n, 2)))
+    pin = dict(pin_memory=True)
+    clock_p = torch.zeros(n, dtype=torch.int64, **pin)
+    t_p = torch.zeros(n, dtype=torch.float64, **pin)
+    goals_p, masks_p = torch.from_numpy(goals_h).pin_memory(), torch.from_numpy(masks_h).pin_memory()
+    clock_d, t_d = clock_p.to(dev), t_p.to(dev)
+    goal_d, mask_d = goals_p[0].to(dev), masks_p[0].to(dev)
+    kp_d = torch.zeros(n, human.K, 3, dtype=torch.float64, device=dev)
+    q_p, dq_p, ddq_p = (torch.zeros(n, J, dtype=torch.float64, **pin) for _ in range(3))
+    safe_p, branch_p = (torch.zeros(n, dtype=torch.uint8, **pin) for _ in range(2))
+    main = torch.cuda.current_stream(dev)
+    phase = torch.from_numpy(np.random.default_rng(12).integers(0, 400, n))  # every env on its own animation clock
+
+    def tick(kk):
+        torch.add(phase, kk, out=clock_p)
+        t_p.fill_(kk * SAMPLE_TIME)
+        clock_d.copy_(clock_p, non_blocking=True)
+        t_d.copy_(t_p, non_blocking=True)
+        mask_d.copy_(masks_p[kk % GOAL_PERIOD], non_blocking=True)
+        goal_d.copy_(goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], non_blocking=True)
+        human.human_measurement(clock_d, out=kp_d)
+        shield.tick_device(kp_d, t_d, mask_d, goal_d)
+        q_p.copy_(shield.q, non_blocking=True)
+        dq_p.copy_(shield.dq, non_blocking=True)
+        ddq_p.copy_(shield.ddq, non_blocking=True)
+        safe_p.copy_(shield.is_safe, non_blocking=True)
+        branch_p.copy_(shield.branch, non_blocking=True)
+        main.synchronize()
+
+    kk = k0
+    for _ in range(warm):
+        tick(kk)
+        kk += 1
+    sync_all()
+    shield.stats(clear=True)
+    l0 = shield.launch_count() + human.launch_count
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        tick(kk)
+        kk += 1
+    sync_all()
+    ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    st = shield.stats(clear=True)
+    out = {"value": n * world * steps / (ms / 1e3), "unit": METRIC, "ms_per_step": ms / steps,
+           "h2d_bytes_per_step": n * (8 + 8 + 1 + 8 * J), "d2h_bytes_per_step": n * (3 * J * 8 + 2),
+           "gpu_launches": shield.launch_count() + human.launch_count - l0,
+           "human": "2 recorded CMU clips (tests/golden/cmu_clips.npz) replayed per env at its own clock and placement, "
+                    "hrg_human_keypoints -> hrg_shield_tick_device; no keypoints cross PCIe",
+           "unsafe_frac": st["n_unsafe"] / max(1, st["n_steps"]), "branch_hist": st["n_branch"],
+           "checksum": float(q_p.sum().item()) + float(safe_p.sum().item())}
+    human.close()
+    return out
+
+
 def bench_human_fk(n, dev, launches=50):
     """k_human_keypoints alone: n humans replaying the recorded CMU clips of tests/golden, CUDA events on torch's current
     stream (the stream the C ABI launches on). Algorithmic bytes per env: baked frame row 8(3+3K) in, keypoints 24K out,
     placement 96, clock 8, replay state 12 + one clip-list entry 4."""
     import torch
-    from human_robot_gym_b200.human_animation import BatchedHumanAnimation, load_clips_npz, load_tree_json
-    g = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden")
-    tree, clips = load_tree_json(os.path.join(g, "human_tree.json")), load_clips_npz(os.path.join(g, "cmu_clips.npz"))
+    from human_robot_gym_b200.human_animation import BatchedHumanAnimation
+    tree, clips = _golden_human()
     rng = np.random.default_rng(5)
     h = BatchedHumanAnimation(tree, clips, n, device=dev, n_animations_per_env=2)
     yaw = rng.uniform(0, 2 * np.pi, n)
@@ -362,6 +436,16 @@ def main():
                "unpipelined": {"value": N * world * S / (ms_plain / 1e3), "ms_per_step": ms_plain / S},
                "checksum": checksum}
 
+    # ---- end to end with the RECORDED human (the reference's own workload: the human is a clip replay, BASELINE config 1) -----
+    # The keypoints never exist on the host: per tick the host sends the clock and the goals (pinned -> device), the device
+    # replays the clips (hrg_human_keypoints), runs the tick on its output and the setpoints come back to pinned memory.
+    e2e_rec = None
+    if not args.no_e2e and K == 23:
+        try:
+            e2e_rec = bench_e2e_recorded(shield, args, N, J, dev, goals_h, masks_h, S, max(3, min(W, 10)), k, sync_all, world)
+        except Exception as ex:
+            e2e_rec = {"error": repr(ex)}
+
     # ---- animation -> keypoints kernel, timed alone: N replaying humans, one launch per tick ------------
     human_fk = None
     if rank == 0 and K == 23:
@@ -426,6 +510,8 @@ def main():
         }
         if e2e:
             line["e2e"] = e2e
+        if e2e_rec:
+            line["e2e_recorded_human"] = e2e_rec
         if human_fk:
             if "ms" in human_fk:
                 human_fk["frac_of_hbm_peak"] = human_fk["GBps"] / peak
