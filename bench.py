@@ -202,28 +202,16 @@ def bench_e2e_recorded(shield, args, n, J, dev, goals_h, masks_h, steps, warm, k
     clock_p = torch.zeros(n, dtype=torch.int64, **pin)
     t_p = torch.zeros(n, dtype=torch.float64, **pin)
     goals_p, masks_p = torch.from_numpy(goals_h).pin_memory(), torch.from_numpy(masks_h).pin_memory()
-    clock_d, t_d = clock_p.to(dev), t_p.to(dev)
-    goal_d, mask_d = goals_p[0].to(dev), masks_p[0].to(dev)
-    kp_d = torch.zeros(n, human.K, 3, dtype=torch.float64, device=dev)
     q_p, dq_p, ddq_p = (torch.zeros(n, J, dtype=torch.float64, **pin) for _ in range(3))
-    safe_p, branch_p = (torch.zeros(n, dtype=torch.uint8, **pin) for _ in range(2))
+    fl_p = torch.zeros(n, dtype=torch.uint8, **pin)
     main = torch.cuda.current_stream(dev)
     phase = torch.from_numpy(np.random.default_rng(12).integers(0, 400, n))  # every env on its own animation clock
 
     def tick(kk):
         torch.add(phase, kk, out=clock_p)
         t_p.fill_(kk * SAMPLE_TIME)
-        clock_d.copy_(clock_p, non_blocking=True)
-        t_d.copy_(t_p, non_blocking=True)
-        mask_d.copy_(masks_p[kk % GOAL_PERIOD], non_blocking=True)
-        goal_d.copy_(goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], non_blocking=True)
-        human.human_measurement(clock_d, out=kp_d)
-        shield.tick_device(kp_d, t_d, mask_d, goal_d)
-        q_p.copy_(shield.q, non_blocking=True)
-        dq_p.copy_(shield.dq, non_blocking=True)
-        ddq_p.copy_(shield.ddq, non_blocking=True)
-        safe_p.copy_(shield.is_safe, non_blocking=True)
-        branch_p.copy_(shield.branch, non_blocking=True)
+        human.tick_replay_host(shield, clock_p, t_p, masks_p[kk % GOAL_PERIOD], goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]],
+                               q_p, dq_p, ddq_p, fl_p)
         main.synchronize()
 
     kk = k0
@@ -244,12 +232,13 @@ def bench_e2e_recorded(shield, args, n, J, dev, goals_h, masks_h, steps, warm, k
     ms = float(ms.item())
     st = shield.stats(clear=True)
     out = {"value": n * world * steps / (ms / 1e3), "unit": METRIC, "ms_per_step": ms / steps,
-           "h2d_bytes_per_step": n * (8 + 8 + 1 + 8 * J), "d2h_bytes_per_step": n * (3 * J * 8 + 2),
+           "h2d_bytes_per_step": n * (8 + 8 + 1 + 8 * J), "d2h_bytes_per_step": n * (3 * J * 8 + 1),
            "gpu_launches": shield.launch_count() + human.launch_count - l0,
            "human": "2 recorded CMU clips (tests/golden/cmu_clips.npz) replayed per env at its own clock and placement, "
-                    "hrg_human_keypoints -> hrg_shield_tick_device; no keypoints cross PCIe",
+                    "one hrg_shield_tick_replay_host per tick (clock + goals up, keypoints made and consumed on the device, "
+                    "setpoints down); no keypoints cross PCIe",
            "unsafe_frac": st["n_unsafe"] / max(1, st["n_steps"]), "branch_hist": st["n_branch"],
-           "checksum": float(q_p.sum().item()) + float(safe_p.sum().item())}
+           "checksum": float(q_p.sum().item()) + float(fl_p.sum().item())}
     human.close()
     return out
 

@@ -144,6 +144,23 @@ class BatchedSafetyShield:
                    "hrg_shield_set_ltt")
         return verdict.value
 
+    def plot_capsules(self):
+        """FailsafeController.get_robot_capsules / get_human_capsules (failsafe_controller.py:383-427) for every env:
+        ((pos [N,J,3], size [N,J,3], mat [N,J,3,3]), (pos [N,H,3], size, mat)) of the last step's capsules
+        (needs store_capsules=True). Device tensors: the marker buffers a viewer would consume, no viewer here."""
+        robot, human, _ = self.capsules()
+        out = []
+        for caps in (robot, human):
+            n = caps.shape[0] * caps.shape[1]
+            f64 = dict(dtype=torch.float64, device=self.device)
+            pos, size, mat = torch.empty(n, 3, **f64), torch.empty(n, 3, **f64), torch.empty(n, 9, **f64)
+            with torch.cuda.device(self.device):
+                cabi.check(self.lib.hrg_capsule_markers(n, _ptr(caps.contiguous()), _ptr(pos), _ptr(size), _ptr(mat),
+                                                        self._stream()), "hrg_capsule_markers")
+            shp = caps.shape[:2]
+            out.append((pos.view(*shp, 3), size.view(*shp, 3), mat.view(*shp, 3, 3)))
+        return tuple(out)
+
     def ltt_max_window(self, index=None, window_k: int = 0):
         """getMaxAccelerationWindow(index) / getMaxJerkWindow(index) of every env's live LTT -> ([N,J], [N,J]).
         index: [N] int32 tensor, or None for each env's path_s_discrete_; window_k 0 = the shield's sliding_window_k_."""

@@ -109,6 +109,7 @@ SYMBOLS = {
     "hrg_shield_upload_inputs": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [_vp]),
     "hrg_shield_tick_staged": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [_vp]),
     "hrg_shield_get_capsules": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _vp]),
+    "hrg_capsule_markers": (C.c_int, [C.c_int, _dp, _dp, _dp, _dp, _vp]),
     "hrg_shield_ltt_max_window": (C.c_int, [C.c_void_p, _i32p, C.c_int, _dp, _dp, _vp]),
     "hrg_shield_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _vp]),
     "hrg_shield_profile": (C.c_int, [C.c_void_p, C.c_int]),
@@ -124,6 +125,7 @@ SYMBOLS = {
     "hrg_human_destroy": (C.c_int, [C.c_void_p]),
     "hrg_human_reset": (C.c_int, [C.c_void_p, _u8p, _dp, _i32p, _vp]),
     "hrg_human_keypoints": (C.c_int, [C.c_void_p, C.c_void_p, _dp, _i32p, _i32p, _vp]),
+    "hrg_shield_tick_replay_host": (C.c_int, [C.c_void_p, C.c_void_p] + [C.c_void_p] * 8 + [_vp]),
     "hrg_human_launch_count": (C.c_int64, [C.c_void_p]),
     "hrg_stage_capsule_dist": (C.c_int, [C.c_int, _dp, _dp, _dp, _vp]),
     "hrg_stage_plan_safety_shield": (C.c_int, [C.c_double, C.c_int, _dp, _u8p, _dp, _dp, _vp]),

@@ -323,4 +323,33 @@ HRG_HD void base_pose_matrix(double x, double y, double z, double roll, double p
 // model index (0 Pos, 1 Vel, 2 Accel) of human capsule h
 HRG_HD int human_model_of(const HrgConfig& c, int h) { return h < c.n_ext ? 0 : ((h - c.n_ext) < c.n_bodies ? 1 : 2); }
 
+// PlotCapsule.update_pos (HRG/controllers/failsafe_controller/failsafe_controller/plot_capsule.py:30-86): a capsule
+// (p1, p2, r) as the pos / size / mat triple of a MuJoCo marker - centre, (r, r, half length), and the rotation that takes
+// the z axis onto the capsule axis (shortest-arc quaternion, normalised twice as the reference and scipy do).
+HRG_HD void capsule_marker(const double* c, double* pos, double* size, double* mat) {
+  const double vx = c[3] - c[0], vy = c[4] - c[1], vz = c[5] - c[2];
+  const double norm = sqrt(vx * vx + vy * vy + vz * vz);
+  pos[0] = (c[0] + c[3]) / 2; pos[1] = (c[1] + c[4]) / 2; pos[2] = (c[2] + c[5]) / 2;
+  size[0] = c[6]; size[1] = c[6];
+  double x = 0.0, y = 0.0, z = 0.0, w = 1.0;
+  if (norm > 1e-6) {
+    size[2] = norm / 2;
+    const double ax = -vy / norm, ay = vx / norm, aw = 1 + vz / norm;
+    const double nq = sqrt(aw * aw + ax * ax + ay * ay);
+    if (nq > 1e-6) {
+      x = ax / nq; y = ay / nq; w = aw / nq;
+      const double n2 = sqrt(x * x + y * y + z * z + w * w);  // Rotation.from_quat normalises again
+      x /= n2; y /= n2; w /= n2;
+    }
+  } else {
+    size[2] = 0.00001;
+  }
+  // scipy Rotation.as_matrix
+  const double x2 = x * x, y2 = y * y, z2 = z * z, w2 = w * w, xy = x * y, zw = z * w, xz = x * z, yw = y * w, yz = y * z,
+               xw = x * w;
+  mat[0] = x2 - y2 - z2 + w2; mat[1] = 2 * (xy - zw);       mat[2] = 2 * (xz + yw);
+  mat[3] = 2 * (xy + zw);     mat[4] = -x2 + y2 - z2 + w2;  mat[5] = 2 * (yz - xw);
+  mat[6] = 2 * (xz - yw);     mat[7] = 2 * (yz + xw);       mat[8] = -x2 - y2 + z2 + w2;
+}
+
 }  // namespace hrg

@@ -7,6 +7,7 @@ struct HrgHuman {
   hrg::HumanTreeDev T;
   int device = 0;
   long long launches = 0;
+  int64_t* d_clock = nullptr;  // staging of hrg_shield_tick_replay_host
   std::vector<void*> allocs;
 
   template <class X>
@@ -98,6 +99,7 @@ int hrg_human_create(int n_bodies, const int32_t* parent_host, const double* anc
   if (rc == HRG_OK) rc = h->upload<int32_t>(&H.clip_list, nullptr, 0, (size_t)n_envs * list_len);
   if (rc == HRG_OK) rc = h->upload<int32_t>(&H.list_idx, nullptr, 0, (size_t)n_envs);
   if (rc == HRG_OK) rc = h->upload<int64_t>(&H.anim_start, nullptr, 0, (size_t)n_envs);
+  if (rc == HRG_OK) rc = h->upload<int64_t>(&h->d_clock, nullptr, 0, (size_t)n_envs);
   H.baked = d_baked; H.clip_off = d_off; H.clip_len = d_len; H.clip_tab = d_tab;
   if (rc != HRG_OK) {
     for (void* p : h->allocs) cudaFree(p);
@@ -133,6 +135,37 @@ int hrg_human_keypoints(HrgHuman* h, const int64_t* low_level_time, double* keyp
                            static_cast<cudaStream_t>(stream)>>>(h->H, low_level_time, keypoints, clip_out, frame_out);
   h->launches++;
   CK(cudaGetLastError());
+  return HRG_OK;
+}
+
+int hrg_shield_tick_replay_host(HrgShield* s, HrgHuman* h, const int64_t* low_level_time_host, const double* t_host,
+                                const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
+                                double* ddq_host, uint8_t* flags_host, void* stream) {
+  if (!s || !h || !low_level_time_host || !t_host) return fail(HRG_EINVAL, "hrg_shield_tick_replay_host: NULL argument");
+  if (h->H.N != s->S.N || h->H.K != s->S.K || h->device != s->device)
+    return fail(HRG_EINVAL, "hrg_shield_tick_replay_host: the human batch and the shield batch differ (envs, keypoints or device)");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t N = s->S.N, J = s->S.J;
+  CK(cudaMemcpyAsync(h->d_clock, low_level_time_host, N * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(s->d_t, t_host, N * sizeof(double), cudaMemcpyHostToDevice, st));
+  const bool goal = goal_mask_host && goal_q_host;
+  if (goal) {
+    CK(cudaMemcpyAsync(s->d_goal_mask, goal_mask_host, N, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(s->d_goal, goal_q_host, N * J * sizeof(double), cudaMemcpyHostToDevice, st));
+  }
+  int rc = hrg_human_keypoints(h, h->d_clock, s->d_kp, nullptr, nullptr, stream);
+  if (rc) return rc;
+  rc = hrg_shield_tick_device(s, s->d_kp, s->d_t, goal ? s->d_goal_mask : nullptr, goal ? s->d_goal : nullptr, s->d_q,
+                              s->d_dq, s->d_ddq, nullptr, s->d_safe, s->d_branch, nullptr, stream);
+  if (rc) return rc;
+  if (q_host) CK(cudaMemcpyAsync(q_host, s->d_q, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (dq_host) CK(cudaMemcpyAsync(dq_host, s->d_dq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (ddq_host) CK(cudaMemcpyAsync(ddq_host, s->d_ddq, N * J * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (flags_host) {
+    k_pack_flags<<<grid_for((int)N, 256), 256, 0, st>>>((int)N, s->d_safe, s->d_branch, s->d_flags8);
+    s->launches++;
+    CK(cudaMemcpyAsync(flags_host, s->d_flags8, N, cudaMemcpyDeviceToHost, st));
+  }
   return HRG_OK;
 }
 

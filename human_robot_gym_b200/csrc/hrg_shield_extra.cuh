@@ -17,6 +17,20 @@ __global__ void k_copy_stats(HrgStats* dst, HrgStats* src, int clear) {
   }
 }
 
+__global__ void k_capsule_markers(int n, const double* __restrict__ caps, double* __restrict__ pos,
+                                  double* __restrict__ size, double* __restrict__ mat) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double c[7], p[3], sz[3], m[9];
+  for (int k = 0; k < 7; ++k) c[k] = caps[(size_t)i * 7 + k];
+  capsule_marker(c, p, sz, m);
+  for (int k = 0; k < 3; ++k) {
+    pos[(size_t)i * 3 + k] = p[k];
+    size[(size_t)i * 3 + k] = sz[k];
+  }
+  for (int k = 0; k < 9; ++k) mat[(size_t)i * 9 + k] = m[k];
+}
+
 // LongTermTraj::getMaxAccelerationWindow / getMaxJerkWindow (SS/include/safety_shield/long_term_traj.h:243-259) of every env's
 // live LTT. The reference fills max_acceleration_window_ / max_jerk_window_ for ALL samples whenever an LTT is built
 // (calculate_max_acc_jerk_window, SS/src/long_term_traj.cc:79-159: entry t = max over samples [t, min(t + k, L)) of the
@@ -285,6 +299,14 @@ int hrg_stage_reach_verify(const HrgConfig* cfg, int n, const double* base_pose,
 static int ctrl_check(const HrgShield* s, const HrgControllerConfig* k, const char* who) {
   if (!s || !k) return fail(HRG_EINVAL, who);
   if (k->nb_joints != s->S.J) return fail(HRG_EINVAL, "controller nb_joints differs from the shield's");
+  return HRG_OK;
+}
+
+int hrg_capsule_markers(int n, const double* caps, double* pos, double* size, double* mat, void* stream) {
+  if (n < 0 || !caps || !pos || !size || !mat) return fail(HRG_EINVAL, "hrg_capsule_markers: bad argument");
+  if (n == 0) return HRG_OK;
+  k_capsule_markers<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(n, caps, pos, size, mat);
+  CK(cudaGetLastError());
   return HRG_OK;
 }
 

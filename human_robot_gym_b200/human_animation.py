@@ -183,6 +183,15 @@ class BatchedHumanAnimation:
                                                     self._stream()), "hrg_human_keypoints")
         return kp
 
+    def tick_replay_host(self, shield, low_level_time_host, t_host, goal_mask_host, goal_q_host, q_host, dq_host, ddq_host,
+                         flags_host):
+        """One control tick with page-locked HOST tensors when the human is this replay: clock + goals up, keypoints made and
+        consumed on the device, setpoints down (hrg_shield_tick_replay_host). The caller synchronises the stream."""
+        with torch.cuda.device(self.device):
+            cabi.check(self.lib.hrg_shield_tick_replay_host(
+                shield._h, self._h, _ptr(low_level_time_host), _ptr(t_host), _ptr(goal_mask_host), _ptr(goal_q_host),
+                _ptr(q_host), _ptr(dq_host), _ptr(ddq_host), _ptr(flags_host), self._stream()), "hrg_shield_tick_replay_host")
+
     @property
     def launch_count(self) -> int:
         return int(self.lib.hrg_human_launch_count(self._h))

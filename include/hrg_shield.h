@@ -169,6 +169,12 @@ int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_ho
  * Any pointer may be NULL. */
 int hrg_shield_get_capsules(HrgShield* s, double* robot, double* human, double* min_dist, void* stream);
 
+/* PlotCapsule(p1, p2, r).pos / .size / .mat - HRG/controllers/failsafe_controller/failsafe_controller/plot_capsule.py:30-86,
+ * what FailsafeController.get_robot_capsules / get_human_capsules (failsafe_controller.py:383-427) hand to the MuJoCo
+ * viewer - for n capsules: caps [n,7] (e.g. the output of hrg_shield_get_capsules) -> pos [n,3], size [n,3] = (r, r, half
+ * length), mat [n,9] row-major rotation of the z axis onto the capsule axis. A headless device buffer: no viewer here. */
+int hrg_capsule_markers(int n, const double* caps, double* pos, double* size, double* mat, void* stream);
+
 /* LongTermTraj.getMaxAccelerationWindow(index) / getMaxJerkWindow(index) - SS/include/safety_shield/long_term_traj.h:243-259,
  * SS/src/long_term_traj.cc:79-159 - of every env's live long-term trajectory: per joint the maximum of the signed
  * acceleration / jerk over samples [t, min(t + k, L)), t = getTrajectoryIndex(index). index [N] i32 or NULL (each env's
@@ -237,6 +243,13 @@ int hrg_human_reset(HrgHuman* h, const uint8_t* env_mask, const double* placemen
  * clip_out, frame_out [N] i32 or NULL: which clip / frame each env showed. */
 int hrg_human_keypoints(HrgHuman* h, const int64_t* low_level_time, double* keypoints, int32_t* clip_out,
                         int32_t* frame_out, void* stream);
+/* One control tick of envs whose human is a clip replay, with HOST buffers: `_control_human` + `human_measurement` +
+ * [newLongTermTrajectory] + humanMeasurement + step (human_env.py:503-524) - the clock low_level_time_host [N] i64, t_host [N]
+ * and the goals go up, the keypoints are produced and consumed on the device, the setpoints come back (as
+ * hrg_shield_tick_host). `h` and `s` must hold the same number of envs and keypoints on the same device. */
+int hrg_shield_tick_replay_host(HrgShield* s, HrgHuman* h, const int64_t* low_level_time_host, const double* t_host,
+                                const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
+                                double* ddq_host, uint8_t* flags_host, void* stream);
 int64_t hrg_human_launch_count(const HrgHuman* h);
 
 /* ---- per-stage entry points (parity tests + ncu); all DEVICE pointers --------------------------------------- */

@@ -342,6 +342,9 @@ int emul_human_capsules(const HrgConfig* cfg, const double* kp, const double* kv
   for (int h = 0; h < H; ++h) cap_store(human_capsule(*cfg, h, kp, kv, 1, t_reach), out + 7 * h);
   return H;
 }
+void emul_capsule_markers(int n, const double* caps, double* pos, double* size, double* mat) {
+  for (int i = 0; i < n; ++i) capsule_marker(caps + 7 * (size_t)i, pos + 3 * (size_t)i, size + 3 * (size_t)i, mat + 9 * (size_t)i);
+}
 // Animation -> keypoints for n (frame row, clip info, placement) triples through the functions k_human_keypoints calls.
 int emul_human_keypoints(int K, const int32_t* parent, const double* anchor, int n, const double* rows,
                          const double* info, const double* place, double* out) {

@@ -39,6 +39,7 @@ def lib():
         L.emul_ltp_time_scaling.argtypes = [D, _p, D, D, D, D, D, D, _p, _p, _p]
         L.emul_ltt_interpolate.argtypes = [C.c_int, C.c_int, _p, D, C.c_int, C.c_int, _p, _p, _p, _p]
         L.emul_human_capsules.argtypes = [C.POINTER(HrgConfig), _p, _p, D, _p]
+        L.emul_capsule_markers.argtypes = [C.c_int, _p, _p, _p, _p]
         L.emul_human_keypoints.restype = C.c_int
         L.emul_human_keypoints.argtypes = [C.c_int, _p, _p, C.c_int, _p, _p, _p, _p]
         L.emul_poly_root.restype = C.c_double
@@ -181,3 +182,12 @@ def human_keypoints(tree, rows, info, place):
     if rc:
         raise ValueError(f"human_build_tree failed with {rc}")
     return out
+
+
+def capsule_markers(caps):
+    """PlotCapsule pos / size / mat for caps [n,7] (geom_math.cuh capsule_marker on the host)."""
+    caps = _a(caps)
+    n = caps.shape[0]
+    pos, size, mat = np.zeros((n, 3)), np.zeros((n, 3)), np.zeros((n, 3, 3))
+    lib().emul_capsule_markers(n, _ptr(caps), _ptr(pos), _ptr(size), _ptr(mat))
+    return pos, size, mat

@@ -4,6 +4,8 @@ ships for this path. Every vector below is quoted from the cited reference test;
 
 SS = human_robot_gym/controllers/failsafe_controller/sara-shield/safety_shield, LTP = SS/external/LongTermPlanner.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -383,3 +385,12 @@ def test_max_window_host_class_matches_golden_and_reference():
             acc, jerk = ref.ltt_max_window(tr, 0.004, k)
             assert (np.array([ltt.getMaxAccelerationWindow(i) for i in range(L)]) == acc).all()
             assert (np.array([ltt.getMaxJerkWindow(i) for i in range(L)]) == jerk).all()
+
+
+# ---- capsule -> MuJoCo marker (PlotCapsule), golden outputs of the imported reference (tests/golden/make_plot_capsule_fixture.py)
+def test_capsule_markers_match_reference_plot_capsule():
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "plot_capsules.npz"))
+    pos, size, mat = emul.capsule_markers(z["caps"])
+    assert np.array_equal(pos, z["pos"]) and np.array_equal(size, z["size"])
+    assert np.abs(mat - z["mat"]).max() < 1e-15
+    assert (z["size"][200:210, 2] == 0.00001).all() and np.array_equal(z["mat"][225], np.eye(3))  # sphere / -z branches hit

@@ -323,3 +323,18 @@ def test_ltt_max_window_matches_reference():
     print("ltt_max_window:", seen)
     assert res["mismatch_excl_near"] == 0 and seen["n"] == 6 and seen["nonzero"] > 1000, (res, seen)
     assert seen["max_diff"] < 1e-5, seen
+
+
+def test_capsule_markers_match_reference_plot_capsule():
+    """hrg_capsule_markers against PlotCapsule outputs generated by importing the reference (tests/golden)."""
+    import os
+    cabi, lib = _lib()
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "plot_capsules.npz"))
+    n = z["caps"].shape[0]
+    caps = _dev(z["caps"])
+    pos, size = torch.zeros(n, 3, dtype=torch.float64, device="cuda:0"), torch.zeros(n, 3, dtype=torch.float64, device="cuda:0")
+    mat = torch.zeros(n, 9, dtype=torch.float64, device="cuda:0")
+    cabi.check(lib.hrg_capsule_markers(n, caps.data_ptr(), pos.data_ptr(), size.data_ptr(), mat.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert np.array_equal(pos.cpu().numpy(), z["pos"]) and np.array_equal(size.cpu().numpy(), z["size"])
+    assert np.abs(mat.cpu().numpy().reshape(n, 3, 3) - z["mat"]).max() < 1e-14

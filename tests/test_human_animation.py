@@ -184,3 +184,50 @@ def test_recorded_human_closed_loop_matches_checker():
     assert res["max_setpoint_diff"] < TOL and res["max_min_dist_diff"] < TOL and pair.max_diff < 1e-11, res
     assert res["branch_hist"][0] > 0 and res["branch_hist"][2] > 0, res  # the human does come close
     pair.gpu.close()
+
+
+@pytest.mark.gpu
+def test_tick_replay_host_equals_keypoints_then_tick():
+    """hrg_shield_tick_replay_host (host clock + goals in, setpoints out) = hrg_human_keypoints + the three shield calls."""
+    import torch
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    from human_robot_gym_b200.config import ShieldConfig
+    from human_robot_gym_b200.human_animation import BatchedHumanAnimation
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+    from tests.parity_util import default_files, mocap_joint_names
+    tree, clips = load_fixture()
+    files = default_files("schunk")
+    sc = ShieldConfig.from_files(0.004, *files)
+    n = 77
+    scen = SyntheticScenario(n, mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, 31)
+    rng = np.random.default_rng(31)
+    pos, quat = random_placements(rng, n, (-1.5, 0.0, 0.0), 0.7)
+    ids = rng.integers(0, 2, (n, 2)).astype(np.int32)
+    sh = [BatchedSafetyShield(n, 0.004, *files, init_qpos=scen.init_q, device="cuda:0") for _ in range(2)]
+    hu = [BatchedHumanAnimation(tree, clips, n, device="cuda:0", n_animations_per_env=2) for _ in range(2)]
+    for h in hu:
+        h.reset(pos, quat, ids)
+    pin = dict(pin_memory=True)
+    clock_p, t_p = torch.zeros(n, dtype=torch.int64, **pin), torch.zeros(n, dtype=torch.float64, **pin)
+    q_p, dq_p, ddq_p = (torch.zeros(n, 6, dtype=torch.float64, **pin) for _ in range(3))
+    fl_p = torch.zeros(n, dtype=torch.uint8, **pin)
+    for k in range(70):
+        t = k * 0.004
+        gmask = (np.arange(n) % 25) == (k % 25)
+        g = scen.next_goal(gmask)
+        kp = hu[0].human_measurement(k + 230)  # the clip change of the 60-frame clip falls into the run
+        sh[0].humanMeasurement(kp, t)
+        if gmask.any():
+            sh[0].newLongTermTrajectory(torch.from_numpy(g), env_mask=torch.from_numpy(gmask))
+        sh[0].step(t)
+        clock_p.fill_(k + 230)
+        t_p.fill_(t)
+        gm_p, gq_p = torch.from_numpy(gmask.astype(np.uint8)).pin_memory(), torch.from_numpy(g).pin_memory()
+        hu[1].tick_replay_host(sh[1], clock_p, t_p, gm_p if gmask.any() else None, gq_p if gmask.any() else None,
+                               q_p, dq_p, ddq_p, fl_p)
+        torch.cuda.synchronize()
+        assert np.array_equal(q_p.numpy(), sh[0].q.cpu().numpy()) and np.array_equal(ddq_p.numpy(), sh[0].ddq.cpu().numpy())
+        assert np.array_equal(fl_p.numpy() & 1, sh[0].is_safe.cpu().numpy())
+    assert int((fl_p.numpy() >> 1).max()) <= 2
+    for x in sh + hu:
+        x.close()
