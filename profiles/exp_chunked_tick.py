@@ -1,6 +1,6 @@
 """Experiment: one tick of 65 536 envs as C independent env blocks, each on its own stream (replan chains overlap)."""
 import sys, os, json
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # repo root
 import numpy as np, torch
 import bench
 from human_robot_gym_b200.batched import BatchedSafetyShield
