@@ -104,7 +104,56 @@ def cpu_loop(args, files, sc, names, n_cpu, warmup, steps, threads, budget_s=25.
 
 
 class ClockSampler:
-    def __init__(self, index):
+    """SM clock and throttle reasons of the device DURING the timed region: an in-process NVML poller (10 ms period, no
+    start-up latency - the timed region of the default run is only about 50 ms), `nvidia-smi -lms` as the fallback."""
+    _REASONS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+
+    def __init__(self, index, uuid=None):
+        import threading
+        self.sm, self.mx, self.reasons = [], [], set()
+        self.p = self.f = self.thread = None
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            if uuid is not None:
+                for cand in (f"GPU-{uuid}", str(uuid)):
+                    try:
+                        h = pynvml.nvmlDeviceGetHandleByUUID(cand.encode() if isinstance(cand, str) else cand)
+                        break
+                    except Exception:
+                        try:
+                            h = pynvml.nvmlDeviceGetHandleByUUID(cand)
+                            break
+                        except Exception:
+                            h = None
+            if h is None:
+                h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.source = "nvml"
+
+            def poll():
+                mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+                while not self._stop.is_set():
+                    try:
+                        self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                        self.mx.append(mx)
+                        bits = int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)) if hasattr(
+                            pynvml, "nvmlDeviceGetCurrentClocksEventReasons") else int(
+                            pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                        for nme, bit in self._REASONS.items():
+                            if bits & bit:
+                                self.reasons.add(nme)
+                    except Exception:
+                        pass
+                    self._stop.wait(0.01)
+
+            self.thread = threading.Thread(target=poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.thread = None
+        self.source = "nvidia-smi"
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -115,34 +164,35 @@ class ClockSampler:
             self.p = None
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        if self.p is None:
-            return out
-        self.p.terminate()
-        try:
-            self.p.wait(timeout=5)
-        except Exception:
-            self.p.kill()
-        self.f.flush()
-        self.f.seek(0)
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.f.read().splitlines():
-            c = [x.strip() for x in line.split(",")]
-            if len(c) < 7:
-                continue
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "source": self.source}
+        if self.thread is not None:
+            self._stop.set()
+            self.thread.join(timeout=2)
+        elif self.p is not None:
+            self.p.terminate()
             try:
-                sm.append(float(c[0]))
-                mx.append(float(c[1]))
-            except ValueError:
-                continue
-            for nme, v in zip(names, c[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nme)
-        os.unlink(self.f.name)
-        if sm:
-            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                   "samples": len(sm)}
+                self.p.wait(timeout=5)
+            except Exception:
+                self.p.kill()
+            self.f.flush()
+            self.f.seek(0)
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            for line in self.f.read().splitlines():
+                c = [x.strip() for x in line.split(",")]
+                if len(c) < 7:
+                    continue
+                try:
+                    self.sm.append(float(c[0]))
+                    self.mx.append(float(c[1]))
+                except ValueError:
+                    continue
+                for nme, v in zip(names, c[3:7]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(nme)
+            os.unlink(self.f.name)
+        if self.sm:
+            out.update({"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": float(max(self.mx)),
+                        "reasons": sorted(self.reasons), "samples": len(self.sm)})
         return out
 
 
@@ -333,7 +383,7 @@ def main():
     sync_all()
     shield.stats(clear=True)
     launches0 = shield.launch_count()
-    clocks = ClockSampler(local_rank) if rank == 0 else None
+    clocks = ClockSampler(local_rank, getattr(torch.cuda.get_device_properties(dev), "uuid", None)) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     e0.record()

@@ -144,6 +144,29 @@ class BatchedSafetyShield:
                    "hrg_shield_set_ltt")
         return verdict.value
 
+    def set_ltt_batch(self, env_index, traj, length, sample_time: float, starting_index=None, alpha_i=None) -> torch.Tensor:
+        """setLongTermTrajectory for many envs in one launch: traj [M, Lmax, 4, J], length [M], env_index [M] (distinct),
+        starting_index [M] or None, alpha_i [M, J] (default alpha_i_max of the config). Returns the verdicts [M] (int32,
+        device): 0 installed, 1..4 the reference's exceptions (see set_ltt), -1 env / length out of range."""
+        f64 = dict(dtype=torch.float64, device=self.device)
+        i32 = dict(dtype=torch.int32, device=self.device)
+        traj = torch.as_tensor(traj, **f64).contiguous()
+        M, Lmax = traj.shape[0], traj.shape[1]
+        if tuple(traj.shape[2:]) != (4, self.J):
+            raise ValueError(f"traj must be [M, Lmax, 4, {self.J}], got {tuple(traj.shape)}")
+        env_index = torch.as_tensor(env_index, **i32).contiguous()
+        length = torch.as_tensor(length, **i32).contiguous()
+        start = None if starting_index is None else torch.as_tensor(starting_index, **i32).contiguous()
+        if alpha_i is None:
+            alpha_i = torch.full((M, self.J), float(self.config.traj.alpha_i_max), **f64)
+        alpha = torch.as_tensor(alpha_i, **f64).expand(M, self.J).contiguous()
+        verdict = torch.full((M,), -2, **i32)
+        with torch.cuda.device(self.device):
+            cabi.check(self.lib.hrg_shield_set_ltt_batch(self._h, M, _ptr(env_index), _ptr(traj), Lmax, _ptr(length),
+                                                         float(sample_time), _ptr(start), _ptr(alpha), _ptr(verdict),
+                                                         self._stream()), "hrg_shield_set_ltt_batch")
+        return verdict
+
     def plot_capsules(self):
         """FailsafeController.get_robot_capsules / get_human_capsules (failsafe_controller.py:383-427) for every env:
         ((pos [N,J,3], size [N,J,3], mat [N,J,3,3]), (pos [N,H,3], size, mat)) of the last step's capsules

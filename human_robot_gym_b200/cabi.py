@@ -102,6 +102,8 @@ SYMBOLS = {
     "hrg_shield_new_goal": (C.c_int, [C.c_void_p, _u8p, _dp, _dp, _vp]),
     "hrg_shield_set_ltt": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p,
                                      C.c_void_p]),
+    "hrg_shield_set_ltt_batch": (C.c_int, [C.c_void_p, C.c_int, _i32p, _dp, C.c_int, _i32p, C.c_double, _i32p, _dp, _i32p,
+                                           _vp]),
     "hrg_shield_store_capsules": (C.c_int, [C.c_void_p, C.c_int]),
     "hrg_shield_step": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp, _dp, _u8p, _u8p, _u32p, _vp]),
     "hrg_shield_tick_device": (C.c_int, [C.c_void_p, _dp, _dp, _u8p, _dp, _dp, _dp, _dp, _dp, _u8p, _u8p, _u32p, _vp]),

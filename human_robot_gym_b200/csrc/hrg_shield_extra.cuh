@@ -69,8 +69,9 @@ __global__ void k_ltt_max_window(DevState S, const int32_t* __restrict__ index, 
 }
 
 // SafetyShield::setLongTermTrajectory (SS/src/safety_shield.cc:699-730) for one env; traj already on the device.
-__global__ void k_set_ltt(DevState S, int e, const double* __restrict__ traj, int length, double sample_time,
-                          int starting_index, const double* __restrict__ alpha, int32_t* verdict) {
+__device__ __forceinline__ void set_ltt_block(const DevState& S, int e, const double* __restrict__ traj, int length,
+                                              double sample_time, int starting_index, const double* __restrict__ alpha,
+                                              int32_t* verdict) {
   __shared__ int s_verdict;
   const HrgConfig& c = *S.cfg;
   const int J = S.J, N = S.N;
@@ -117,6 +118,26 @@ __global__ void k_set_ltt(DevState S, int e, const double* __restrict__ traj, in
         S.ltt_time[((size_t)e * 2 + pend) * S.L + i] = i * sample_time;
       }
   }
+}
+
+__global__ void k_set_ltt(DevState S, int e, const double* __restrict__ traj, int length, double sample_time,
+                          int starting_index, const double* __restrict__ alpha, int32_t* verdict) {
+  set_ltt_block(S, e, traj, length, sample_time, starting_index, alpha, verdict);
+}
+
+// One block per user trajectory: block m installs traj[m] into env env_index[m] (the envs must be distinct).
+__global__ void k_set_ltt_batch(DevState S, int max_len, const int32_t* __restrict__ env_index,
+                                const double* __restrict__ traj, const int32_t* __restrict__ length, double sample_time,
+                                const int32_t* __restrict__ starting_index, const double* __restrict__ alpha,
+                                int32_t* __restrict__ verdict) {
+  const int m = blockIdx.x;
+  const int e = env_index[m], len = length[m];
+  if (e < 0 || e >= S.N || len < 1 || len > S.L || len > max_len) {  // block-uniform
+    if (threadIdx.x == 0) verdict[m] = -1;
+    return;
+  }
+  set_ltt_block(S, e, traj + (size_t)m * max_len * 4 * S.J, len, sample_time, starting_index ? starting_index[m] : 0,
+                alpha + (size_t)m * S.J, verdict + m);
 }
 }  // namespace
 
@@ -180,6 +201,21 @@ int hrg_shield_set_ltt(HrgShield* s, int env, const double* traj_host, int lengt
   }
   cudaFree(d);
   if (ce != cudaSuccess) return fail(HRG_ECUDA, "hrg_shield_set_ltt", ce);
+  return HRG_OK;
+}
+
+int hrg_shield_set_ltt_batch(HrgShield* s, int n_traj, const int32_t* env_index, const double* traj, int max_len,
+                             const int32_t* length, double sample_time, const int32_t* starting_index,
+                             const double* alpha_i, int32_t* verdict, void* stream) {
+  if (!s || !env_index || !traj || !length || !alpha_i || !verdict)
+    return fail(HRG_EINVAL, "hrg_shield_set_ltt_batch: NULL argument");
+  if (n_traj < 0 || max_len < 1) return fail(HRG_EINVAL, "hrg_shield_set_ltt_batch: n_traj < 0 or max_len < 1");
+  if (!(sample_time > 0)) return fail(HRG_EINVAL, "hrg_shield_set_ltt_batch: sample_time must be > 0");
+  if (n_traj == 0) return HRG_OK;
+  k_set_ltt_batch<<<n_traj, 128, 0, static_cast<cudaStream_t>(stream)>>>(s->S, max_len, env_index, traj, length, sample_time,
+                                                                         starting_index, alpha_i, verdict);
+  s->launches++;
+  CK(cudaGetLastError());
   return HRG_OK;
 }
 

@@ -126,6 +126,13 @@ int hrg_shield_new_goal(HrgShield* s, const uint8_t* env_mask, const double* goa
 int hrg_shield_set_ltt(HrgShield* s, int env, const double* traj_host, int length, double sample_time,
                        int starting_index, const double* alpha_i_host, int32_t* verdict_host);
 
+/* setLongTermTrajectory for MANY envs at once, DEVICE pointers, asynchronous on `stream`: trajectory m
+ * (traj [n_traj, max_len, 4, J], its first length[m] samples) goes to env env_index[m] (distinct envs); starting_index [n_traj]
+ * or NULL (0), alpha_i [n_traj, J]; verdict [n_traj] as hrg_shield_set_ltt, -1 = env or length out of range. */
+int hrg_shield_set_ltt_batch(HrgShield* s, int n_traj, const int32_t* env_index, const double* traj, int max_len,
+                             const int32_t* length, double sample_time, const int32_t* starting_index,
+                             const double* alpha_i, int32_t* verdict, void* stream);
+
 /* Keep the robot/human capsules of every step for hrg_shield_get_capsules (off by default: it adds 56(J+H) bytes of
  * writes per env-step that only the visualisation getters need). Takes effect from the next step. */
 int hrg_shield_store_capsules(HrgShield* s, int on);

@@ -338,3 +338,41 @@ def test_capsule_markers_match_reference_plot_capsule():
     torch.cuda.synchronize()
     assert np.array_equal(pos.cpu().numpy(), z["pos"]) and np.array_equal(size.cpu().numpy(), z["size"])
     assert np.abs(mat.cpu().numpy().reshape(n, 3, 3) - z["mat"]).max() < 1e-14
+
+
+def test_set_ltt_batch_equals_one_by_one():
+    """hrg_shield_set_ltt_batch: verdicts and the following closed loop identical to installing the same
+    user trajectories env by env with hrg_shield_set_ltt; the verdict cases are those of test_setLTT
+    (SS/tests/bindings/test_safety_shield.py:115-131) and safety_shield.cc:699-730."""
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    files = pu.default_files("schunk")
+    n, J = 40, 6
+    a = BatchedSafetyShield(n, 0.004, *files, device="cuda:0")
+    b = BatchedSafetyShield(n, 0.004, *files, device="cuda:0")
+    z = np.zeros(J)
+    good = np.array([[z, z, z, z], [z, z, np.r_[1.0, z[1:]], z], [np.r_[0.5, z[1:]], np.r_[1.0, z[1:]], np.r_[-1.0, z[1:]], z],
+                     [np.r_[1.0, z[1:]], z, z, z]])                      # [4 samples, 4, J]
+    bad_start = good.copy(); bad_start[0, 0, 0] = 0.5                    # start position differs -> 2
+    bad_end = good.copy(); bad_end[3] = good[2]                          # does not end stopped -> 4
+    kinds = [good, bad_start, bad_end]
+    envs = np.array([3, 7, 8, 21, 39, 0], dtype=np.int32)
+    which = [0, 1, 0, 2, 0, 0]
+    lengths = np.array([4, 4, 4, 4, 4, 3], dtype=np.int32)               # the last one is truncated: moving at its end -> 4
+    traj = np.zeros((len(envs), 5, 4, J))                                 # Lmax 5 > every length
+    for m, k in enumerate(which):
+        traj[m, :4] = kinds[k]
+    want = [a.set_ltt(int(e), traj[m, :lengths[m]], 1.0, 0, 1.0) for m, e in enumerate(envs)]
+    got = b.set_ltt_batch(envs, traj, lengths, 1.0, alpha_i=1.0).cpu().numpy().tolist()
+    assert got == want == [0, 2, 0, 4, 0, 4]
+    bad = b.set_ltt_batch(np.array([n + 5], dtype=np.int32), traj[:1], lengths[:1], 1.0).cpu().numpy().tolist()
+    assert bad == [-1]
+    kp = np.tile(np.array([3.0, 3.0, 1.0]), (n, a.K, 1))
+    for k in range(40):
+        t = k * 0.004
+        for s in (a, b):
+            s.humanMeasurement(torch.from_numpy(kp), t)
+            s.step(t)
+        assert torch.equal(a.q, b.q) and torch.equal(a.ddq, b.ddq) and torch.equal(a.is_safe, b.is_safe)
+    assert float(a.q[3].abs().max()) > 0 and float(a.q[1].abs().max()) == 0  # env 3 follows its user trajectory, env 1 rests
+    a.close()
+    b.close()
