@@ -536,8 +536,9 @@ def main():
                          "frac": achieved / peak, "traffic": traffic_per_launch(dom), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg, "kernel_ms": dom_ms,
                          "note": "k_replan = the four k_replan_* launches of one tick, timed serially (in the timed "
-                                 "region they overlap k_reach_verify pass 0 on a second stream); latency bound, see "
-                                 "profiles/"},
+                                 "region they overlap k_reach_verify pass 0 on a second stream); latency bound: FP64 pipe "
+                                 "24 / 23 / 14 / 15 % busy in opt / scale / deep / sample (ncu, "
+                                 "profiles/r01l_replan_ncu_summary.md)"},
             "kernel_ms_per_step": {kk: v / max(ksteps, 1) for kk, v in kms.items()},
             "roofline_per_kernel": per_kernel,
             "roofline_tick": {"algorithmic_bytes_per_step": b_step, "achieved": b_step * N / (ms_total / S / 1e3) / 1e9,

@@ -303,7 +303,10 @@ __global__ void k_human_reset(HumanDev H, const uint8_t* __restrict__ mask, cons
   if (e >= H.N) return;
   if (mask && !mask[e]) return;
   human_placement(placement + (size_t)e * 7, H.placement + (size_t)e * 12);
-  for (int i = 0; i < H.M; ++i) H.clip_list[(size_t)e * H.M + i] = clip_list[(size_t)e * H.M + i];
+  for (int i = 0; i < H.M; ++i) {  // ids outside the bank are clamped (the host layer rejects them before they get here)
+    const int c = clip_list[(size_t)e * H.M + i];
+    H.clip_list[(size_t)e * H.M + i] = c < 0 ? 0 : (c >= H.n_clips ? H.n_clips - 1 : c);
+  }
   H.list_idx[e] = 0;
   H.anim_start[e] = 0;
 }

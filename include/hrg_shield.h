@@ -242,7 +242,7 @@ int hrg_human_create(int n_bodies, const int32_t* parent_host, const double* anc
 int hrg_human_destroy(HrgHuman* h);
 /* Env reset (human_env.py:1640-1657): placement [N,7] = human_pos_offset xyz + human_rot_offset quat wxyz; clip_list
  * [N,list_len] = the env's `_human_animation_ids`; index, animation_start_time := 0. DEVICE pointers, env_mask [N] u8 or
- * NULL (all). Envs replay clip 0 at the origin until their first reset. */
+ * NULL (all). Envs replay clip 0 at the origin until their first reset; clip ids outside [0, n_clips) are clamped. */
 int hrg_human_reset(HrgHuman* h, const uint8_t* env_mask, const double* placement, const int32_t* clip_list,
                     void* stream);
 /* `_control_human(force_update=True)` at low_level_time [N] (i64, DEVICE) for every env, then the site positions:
