@@ -46,12 +46,13 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--seed", type=int, default=1003)
+    ap.add_argument("--shield", default="ssm", choices=["ssm", "pfl"], help="ShieldType of every env (config 4 runs both)")
     return ap.parse_args()
 
 
 def workload_name(args, sc):
     h = sc.human
-    return (f"{args.robot} {sc.robot.nb_joints}-DoF SSM, {args.mocap} human (K={h.n_keypoints}, H={h.n_capsules}), "
+    return (f"{args.robot} {sc.robot.nb_joints}-DoF {args.shield.upper()}, {args.mocap} human (K={h.n_keypoints}, H={h.n_capsules}), "
             f"{args.envs} shields per GPU, synthetic keypoints+goals, replans staggered over {GOAL_PERIOD} ticks")
 
 
@@ -78,7 +79,8 @@ def cpu_loop(args, files, sc, names, n_cpu, warmup, steps, threads, budget_s=25.
     """The reference's own per-env CPU shield loop (SS/src/debug.cc:38-55 shape) on `threads` host threads."""
     from tests.parity_util import make_checker
     scen, kp, goals, masks = make_inputs(args, sc, n_cpu, args.seed + 7919, names)
-    chk, kind = make_checker(files, n_cpu, np.zeros((n_cpu, 6)), scen.init_q, SAMPLE_TIME, 1, threads)
+    chk, kind = make_checker(files, n_cpu, np.zeros((n_cpu, 6)), scen.init_q, SAMPLE_TIME, 2 if args.shield == "pfl" else 1,
+                             threads)
     mb = masks.astype(bool)
 
     def tick(k):
@@ -359,7 +361,7 @@ def main():
     W, S = args.warmup, args.steps
     scen, kp_h, goals_h, masks_h = make_inputs(args, sc, N, args.seed + rank, names)
     shield = BatchedSafetyShield(N, SAMPLE_TIME, *files, init_qpos=scen.init_q, device=dev,
-                                 ltt_capacity=args.ltt_capacity, config=sc)
+                                 ltt_capacity=args.ltt_capacity, config=sc, shield_type=2 if args.shield == "pfl" else 1)
     kp_d = torch.from_numpy(kp_h).to(dev)            # [R,N,K,3]
     goals_d = torch.from_numpy(goals_h).to(dev)      # [G,N,J]
     masks_d = torch.from_numpy(masks_h).to(dev)      # [25,N]

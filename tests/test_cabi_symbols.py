@@ -88,3 +88,24 @@ def test_argument_validation_without_device():
     assert lib.hrg_shield_step(None, None, None, None, None, None, None, None, None, None) == cabi.EINVAL
     assert lib.hrg_shield_num_envs(None) == 0
     assert lib.hrg_stage_capsule_dist(-1, None, None, None, None) == cabi.EINVAL
+
+
+@pytest.mark.skipif(_has_cuda(), reason="checks the no-device error path")
+def test_human_replay_has_no_cpu_fallback_either():
+    """hrg_human_create validates its arguments, then fails with HRG_ENODEVICE without a GPU: nothing is computed on the host."""
+    lib = cabi.load_library()
+    parent = np.array([-1, 0], dtype=np.int32)
+    anchor, frames = np.zeros((2, 3)), np.zeros((3, 13))
+    frames[:, 6] = 1.0
+    clip_len, info = np.array([3], dtype=np.int32), np.array([[0, 0, 0, 0, 0, 0, 1.0]])
+    h = C.c_void_p()
+
+    def create(n_bodies, step):
+        return lib.hrg_human_create(n_bodies, parent.ctypes.data, anchor.ctypes.data, 1, clip_len.ctypes.data,
+                                    frames.ctypes.data, info.ctypes.data, step, 4, 1, 0, C.byref(h))
+    assert create(2, 500 / 120.0) == cabi.ENODEVICE and not h.value
+    assert b"no CPU fallback" in lib.hrg_last_error()
+    assert create(0, 500 / 120.0) == cabi.EINVAL       # n_bodies out of range
+    assert create(2, 0.5) == cabi.EINVAL               # animation faster than the simulation (human_env.py:1466)
+    assert lib.hrg_human_keypoints(None, None, None, None, None, None) == cabi.EINVAL
+    assert lib.hrg_capsule_markers(-1, None, None, None, None, None) == cabi.EINVAL
