@@ -395,10 +395,16 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
       CK(cudaEventRecord(s->ev_meas, st));
       CK(cudaStreamWaitEvent(s->side, s->ev_meas, 0));
     }
-    if (s->pfl)
-      k_replan_sample<true><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
-    else
-      k_replan_sample<false><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t);
+    if (s->pfl) {
+      k_replan_sample<true><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t, 1);
+      int pgrid = s->sm_count * 8;
+      if (pgrid > N) pgrid = N;
+      k_pfl_ltt<<<pgrid, kPflBlock, 0, rs>>>(s->S);
+      k_replan_sample<true><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t, 2);
+      s->launches += 2;
+    } else {
+      k_replan_sample<false><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t, 0);
+    }
   }
   if (fork) {
     CK(cudaEventRecord(s->ev_join, s->side));

@@ -274,8 +274,10 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_REPLAN_MINBLOCKS) k_replan_d
 // sums). Lane 0 then finishes the env's step up to the reach / verify hand-over.
 // WITH_PFL = false is the build every SSM/OFF-only handle launches: the PFL branch is compiled out of it (its call would
 // otherwise cost the sampler registers even when never taken).
+// PFL handles run it twice around k_pfl_ltt: phase 1 = sampling only (verdict and length parked in plan_head), phase 2 = the
+// env tail only; phase 0 (SSM / OFF handles) does both in one launch.
 template <bool WITH_PFL>
-__global__ void __launch_bounds__(128) k_replan_sample(DevState S, const double* __restrict__ t) {
+__global__ void __launch_bounds__(128) k_replan_sample(DevState S, const double* __restrict__ t, int phase) {
   __shared__ JerkSampler samp_s[4][8];
   __shared__ double jbuf_s[4][8 * 32];
   const HrgConfig& c = *S.cfg;
@@ -297,7 +299,11 @@ __global__ void __launch_bounds__(128) k_replan_sample(DevState S, const double*
   LtpLimits L;
   L.v_max = c.v_max[j]; L.a_max = c.a_max_ltt[j]; L.j_max = c.j_max_ltt[j]; L.t_sample = c.sample_time;
   const double q_0 = cur_at(S, j, e), v_0 = cur_at(S, J + j, e), a_0 = cur_at(S, 2 * J + j, e);
-  if (ok) {
+  if (WITH_PFL && phase == 2) {  // phase 1 left: bit 0 = trajectory installed, bit 1 = longer than the slot; slowest = its length
+    ok = (h.ok & 1) != 0;
+    if (h.ok & 2) status |= HRG_ST_LTT_TRUNCATED;
+    len = h.slowest;
+  } else if (ok) {
     PlanRec rec = S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j];
     if (rec.len < 0) {
       // a joint from the deep list: first accepted polynomial candidate in the reference's order, else "no valid
@@ -338,11 +344,16 @@ __global__ void __launch_bounds__(128) k_replan_sample(DevState S, const double*
       ok = __all_sync(full, in);
     }
   }
-  const bool pfl = WITH_PFL && ((f & F_TYPE_MASK) >> F_TYPE_SHIFT) == HRG_SHIELD_PFL;
-  if (WITH_PFL && ok && pfl) {
-    __syncwarp(full);
-    pfl_ltt_warp(S, c, e, pend, len, lane);  // PFL LongTermTraj ctor: Cartesian velocities + alpha_i (long_term_traj.cc:5-39)
+  if (WITH_PFL && phase == 1) {
+    if (lane == 0) {
+      PlanHead o = h;
+      o.ok = (ok ? 1 : 0) | ((status & HRG_ST_LTT_TRUNCATED) ? 2 : 0);
+      o.slowest = len;
+      S.plan_head[idx] = o;
+    }
+    return;  // k_pfl_ltt builds the PFL part of the trajectory (long_term_traj.cc:5-39), phase 2 finishes the env
   }
+  const bool pfl = WITH_PFL && ((f & F_TYPE_MASK) >> F_TYPE_SHIFT) == HRG_SHIELD_PFL;
   if (ok && joint_lane && sub == 0) {
     S.replan_q[(size_t)j * N + e] = q_0;  // last_replan_start_motion_ = current_motion (:593)
     // SSM/OFF: alpha_i_ = alpha_i_max (long_term_traj.h:108-116)

@@ -97,55 +97,77 @@ HRG_HD void pfl_ltt_env_seq(const HrgConfig& c, const double* base, size_t bs, c
 }
 
 #if defined(__CUDACC__)
-// Warp form for k_replan_sample: lane = sample within a chunk of 32 (samples are independent except for the
-// neighbour difference of alpha_i, which travels by shuffle). `len` warp-uniform; the trajectory was just written by
-// this warp. Writes ltt_time / ltt_cart of the slot and alpha_i of the env.
-__device__ __noinline__ void pfl_ltt_warp(const DevState& S, const HrgConfig& c, int e, int slot, int len, int lane) {
-  const int J = S.J, N = S.N;
-  double* tm = S.ltt_time + ((size_t)e * 2 + slot) * S.L;
-  double* cv = S.ltt_cart + ((size_t)e * 2 + slot) * S.L;
-  if (lane == 0) {
-    double t = S.path_s[e];
-    for (int i = 0; i < len; ++i) {
-      tm[i] = t;
-      t += c.sample_time;
-    }
-  }
-  __syncwarp();
-  double amax[HRG_MAX_JOINTS], c1[HRG_MAX_JOINTS], c2[HRG_MAX_JOINTS];
-  for (int j = 0; j < HRG_MAX_JOINTS; ++j) amax[j] = c1[j] = c2[j] = 0.0;
-  for (int c0 = 0; c0 < len; c0 += 32) {
-    const int i = c0 + lane;
-    const bool valid = i < len;
-    double n1[HRG_MAX_JOINTS], n2[HRG_MAX_JOINTS];
-    for (int j = 0; j < HRG_MAX_JOINTS; ++j) n1[j] = n2[j] = 0.0;
-    if (valid) {
-      const double* m = ltt_sample(S, e, slot, i);
-      double q[HRG_MAX_JOINTS], qd[HRG_MAX_JOINTS];
-      for (int j = 0; j < J; ++j) {
-        q[j] = m[j];
-        qd[j] = m[J + j];
+// The PFL LongTermTraj constructor (long_term_traj.cc:5-39) of the trajectories k_replan_sample<true> phase 1 has just
+// written: block = replanning env (grid-stride over the replan list), thread = sample within a chunk of kPflBlock. The
+// samples are independent except for the neighbour difference of alpha_i, which goes through shared memory (row 0 carries
+// the last sample of the previous chunk). The first form ran inside the sampler with lane = sample, one warp per env:
+// ~7 sequential rounds of this ~2 500-instruction routine per warp added 0.43 ms to the replan chain
+// (profiles/r01j_summary.md); here the ~480 k samples of a tick spread over the whole GPU.
+constexpr int kPflBlock = 128;
+__global__ void __launch_bounds__(kPflBlock) k_pfl_ltt(DevState S) {
+  __shared__ double n_s[kPflBlock + 1][2 * HRG_MAX_JOINTS];
+  __shared__ double amax_s[kPflBlock / 32][HRG_MAX_JOINTS];
+  const HrgConfig& c = *S.cfg;
+  const int J = S.J, N = S.N, tid = threadIdx.x;
+  const int count = *S.replan_count;
+  for (int idx = blockIdx.x; idx < count; idx += gridDim.x) {
+    const int e = S.replan_list[idx];
+    const uint32_t f = S.flags[e];
+    const PlanHead h = S.plan_head[idx];
+    if (((f & F_TYPE_MASK) >> F_TYPE_SHIFT) != HRG_SHIELD_PFL || !(h.ok & 1)) continue;  // block-uniform
+    const int slot = (f & F_LIVE_SLOT) ? 0 : 1, len = h.slowest;
+    double* tm = S.ltt_time + ((size_t)e * 2 + slot) * S.L;
+    double* cv = S.ltt_cart + ((size_t)e * 2 + slot) * S.L;
+    if (tid == 0) {  // Motion times of calculateLongTermTrajectory (safety_shield.cc:739-752): new_time accumulates
+      double t = S.path_s[e];
+      for (int i = 0; i < len; ++i) {
+        tm[i] = t;
+        t += c.sample_time;
       }
-      cv[i] = pfl_sample_velocity(c, S.base_T + e, (size_t)N, q, qd, n1, n2);
     }
-    const double dt = (valid && i > 0) ? tm[i] - tm[i - 1] : 1.0;
+    __syncthreads();
+    double amax[HRG_MAX_JOINTS];
+    for (int j = 0; j < HRG_MAX_JOINTS; ++j) amax[j] = 0.0;
+    for (int c0 = 0; c0 < len; c0 += kPflBlock) {
+      const int i = c0 + tid;
+      const bool valid = i < len;
+      if (valid) {
+        const double* m = ltt_sample(S, e, slot, i);
+        double q[HRG_MAX_JOINTS], qd[HRG_MAX_JOINTS], n1[HRG_MAX_JOINTS], n2[HRG_MAX_JOINTS];
+        for (int j = 0; j < J; ++j) {
+          q[j] = m[j];
+          qd[j] = m[J + j];
+        }
+        cv[i] = pfl_sample_velocity(c, S.base_T + e, (size_t)N, q, qd, n1, n2);
+        for (int j = 0; j < J; ++j) {
+          n_s[tid + 1][j] = n1[j];
+          n_s[tid + 1][J + j] = n2[j];
+        }
+      }
+      __syncthreads();
+      if (valid && i > 0) {
+        const double dt = tm[i] - tm[i - 1];
+        for (int j = 0; j < J; ++j)
+          amax[j] = fmax(amax[j], fmax(fabs(n_s[tid + 1][j] - n_s[tid][j]) / dt, fabs(n_s[tid + 1][J + j] - n_s[tid][J + j]) / dt));
+      }
+      __syncthreads();
+      if (tid == kPflBlock - 1 && valid)
+        for (int j = 0; j < 2 * J; ++j) n_s[0][j] = n_s[kPflBlock][j];
+      __syncthreads();
+    }
     for (int j = 0; j < J; ++j) {
-      double p1 = __shfl_up_sync(0xffffffffu, n1[j], 1), p2 = __shfl_up_sync(0xffffffffu, n2[j], 1);
-      if (lane == 0) {
-        p1 = c1[j];
-        p2 = c2[j];
-      }
-      if (valid && i > 0) amax[j] = fmax(amax[j], fmax(fabs(n1[j] - p1) / dt, fabs(n2[j] - p2) / dt));
-      c1[j] = __shfl_sync(0xffffffffu, n1[j], 31);
-      c2[j] = __shfl_sync(0xffffffffu, n2[j], 31);
+      double a = amax[j];
+      for (int o = 16; o > 0; o >>= 1) a = fmax(a, __shfl_xor_sync(0xffffffffu, a, o));
+      if ((tid & 31) == 0) amax_s[tid >> 5][j] = a;
     }
+    __syncthreads();
+    if (tid < J) {
+      double a = amax_s[0][tid];
+      for (int w = 1; w < kPflBlock / 32; ++w) a = fmax(a, amax_s[w][tid]);
+      S.ltt_alpha[((size_t)slot * J + tid) * N + e] = a;
+    }
+    __syncthreads();
   }
-  for (int j = 0; j < J; ++j) {
-    double a = amax[j];
-    for (int o = 16; o > 0; o >>= 1) a = fmax(a, __shfl_xor_sync(0xffffffffu, a, o));
-    if (lane == j) S.ltt_alpha[((size_t)slot * J + j) * N + e] = a;
-  }
-  __syncwarp();
 }
 #endif
 
