@@ -21,7 +21,8 @@ HRG_HD_CALL double pfl_sample_velocity(const HrgConfig& c, const double* base, s
   z[0][0] = T[2]; z[0][1] = T[6]; z[0][2] = T[10];
   for (int i = 0; i < J; ++i) {  // RobotReach::forwardKinematic (robot_reach.h:136-142) + transformCapsule (:54-59)
     const double* F = c.link_T[i];
-    const double cs = cos(q[i]), sn = sin(q[i]);
+    double sn, cs;
+    sincos(q[i], &sn, &cs);  // one range reduction for both (20 % of k_pfl_ltt's instructions were the two separate calls)
     for (int r = 0; r < 3; ++r) {
       const double r0 = T[r * 4 + 0], r1 = T[r * 4 + 1], r2 = T[r * 4 + 2], r3 = T[r * 4 + 3];
       const double t0 = r0 * F[0] + r1 * F[4] + r2 * F[8] + r3 * F[12];
