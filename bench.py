@@ -77,10 +77,12 @@ def make_inputs(args, sc, n, seed, names):
 
 def cpu_loop(args, files, sc, names, n_cpu, warmup, steps, threads, budget_s=25.0):
     """The reference's own per-env CPU shield loop (SS/src/debug.cc:38-55 shape) on `threads` host threads."""
-    from tests.parity_util import make_checker
+    from oracle import ref  # the one place bench.py executes oracle/: the reported CPU baseline / --impl reference
+    if not ref.available():
+        raise RuntimeError("oracle/_ref/libsara_ref.so is not built (python __graft_entry__.py where /root/reference exists)")
     scen, kp, goals, masks = make_inputs(args, sc, n_cpu, args.seed + 7919, names)
-    chk, kind = make_checker(files, n_cpu, np.zeros((n_cpu, 6)), scen.init_q, SAMPLE_TIME, 2 if args.shield == "pfl" else 1,
-                             threads)
+    chk, kind = ref.RefBatch(n_cpu, SAMPLE_TIME, files[0], files[1], files[2], np.zeros((n_cpu, 6)), scen.init_q,
+                             shield_type=2 if args.shield == "pfl" else 1, threads=threads), "reference"
     mb = masks.astype(bool)
 
     def tick(k):
@@ -336,7 +338,7 @@ def bench_human_fk(n, dev, launches=50):
 def main():
     args = parse_args()
     from human_robot_gym_b200.config import ShieldConfig
-    from tests.parity_util import default_files, mocap_joint_names
+    from human_robot_gym_b200.workloads import default_files, mocap_joint_names
     files = default_files(args.robot, args.mocap, args.traj)
     sc = ShieldConfig.from_files(SAMPLE_TIME, *files)
     names = mocap_joint_names(files[2])

@@ -32,36 +32,55 @@ def _vec(x) -> List[float]:
 
 
 class Motion:
-    """SS/include/safety_shield/motion.h:30-275 / SS/src/motion.cc (all six constructors)."""
+    """SS/include/safety_shield/motion.h:30-275 / SS/src/motion.cc (all six constructors). Defaults are the BINDING's
+    (SS/bindings/safety_shield_bindings.cpp:41-44: every threshold 1e-4; the C++ header default of hasSamePos is 1e-3)."""
 
-    def __init__(self, *args, s: Optional[float] = None):
+    def __init__(self, *args, **kw):
+        # pybind overloads (bindings :30-40): (), (nb_modules), (time, q[, dq[, ddq[, dddq]]], s=0.0); keywords as named there
         self._time, self._s = 0.0, 0.0
-        if len(args) == 0:
+        unknown = set(kw) - {"nb_modules", "time", "q", "dq", "ddq", "dddq", "s"}
+        if unknown:
+            raise TypeError(f"Motion(): incompatible constructor arguments {sorted(unknown)}")
+        if not args and not kw:
             self._q, self._dq, self._ddq, self._dddq = [], [], [], []
-        elif len(args) == 1 and isinstance(args[0], (int, np.integer)):
-            n = int(args[0])
+            return
+        if "nb_modules" in kw or (len(args) == 1 and not kw and isinstance(args[0], (int, np.integer))
+                                  and not isinstance(args[0], bool)):
+            if len(args) + len(kw) != 1:
+                raise TypeError("Motion(nb_modules)")
+            n = int(kw["nb_modules"] if kw else args[0])
             self._q, self._dq, self._ddq, self._dddq = ([0.0] * n for _ in range(4))
-        else:
-            a = list(args)
+            return
+        a = list(args)
+        if a:
             self._time = float(a.pop(0))
-            if a and np.isscalar(a[-1]) and len(a) >= 2:   # trailing positional s
-                self._s = float(a.pop())
-            if not 1 <= len(a) <= 4:
-                raise TypeError("Motion(time, q[, dq[, ddq[, dddq]]][, s])")
-            vs = [_vec(v) for v in a]
-            n = len(vs[0])
-            while len(vs) < 4:
-                vs.append([0.0] * n)
-            self._q, self._dq, self._ddq, self._dddq = vs
-        if s is not None:
-            self._s = float(s)
+        elif "time" in kw:
+            self._time = float(kw["time"])
+        else:
+            raise TypeError("Motion(time, q[, dq[, ddq[, dddq]]][, s])")
+        if len(a) >= 2 and np.isscalar(a[-1]):   # trailing positional s
+            self._s = float(a.pop())
+        for name in ("q", "dq", "ddq", "dddq")[len(a):]:
+            if name in kw:
+                a.append(kw[name])
+            else:
+                break
+        if not 1 <= len(a) <= 4:
+            raise TypeError("Motion(time, q[, dq[, ddq[, dddq]]][, s])")
+        vs = [_vec(v) for v in a]
+        n = len(vs[0])
+        while len(vs) < 4:
+            vs.append([0.0] * n)
+        self._q, self._dq, self._ddq, self._dddq = vs
+        if "s" in kw:
+            self._s = float(kw["s"])
 
     # motion.h:142-179
     def isStopped(self, threshold: float = 1e-4) -> bool:
         return all(abs(a) <= threshold and abs(b) <= threshold and abs(c) <= threshold
                    for a, b, c in zip(self._dq, self._ddq, self._dddq))
 
-    def hasSamePos(self, motion: "Motion", threshold: float = 1e-3) -> bool:
+    def hasSamePos(self, motion: "Motion", threshold: float = 1e-4) -> bool:
         return all(abs(a - b) <= threshold for a, b in zip(self._q, motion._q))
 
     def hasSameVel(self, motion: "Motion", threshold: float = 1e-4) -> bool:

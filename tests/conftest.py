@@ -17,7 +17,7 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def configs():
     """Parsed reference SS/config/*.yaml (tests/golden/make_configs.py)."""
-    with open(os.path.join(ROOT, "tests", "golden", "configs.json")) as f:
+    with open(os.path.join(ROOT, "human_robot_gym_b200", "data", "shield_configs.json")) as f:
         return json.load(f)
 
 

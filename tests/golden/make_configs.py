@@ -1,4 +1,4 @@
-"""Regenerates tests/golden/configs.json from the reference's YAML config files (run in the build container only).
+"""Regenerates human_robot_gym_b200/data/shield_configs.json from the reference's YAML config files (run in the build container only).
 
 The reference ships robot kinematics/capsules, trajectory limits and human models as YAML under
 SS/config/*.yaml. /root/reference does not exist on the GPU box, so the PARSED content
@@ -26,7 +26,8 @@ def main():
         with open(path) as f:
             pass
         out[os.path.basename(path)[:-5]] = load_yaml(path)
-    dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "configs.json")
+    dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "human_robot_gym_b200", "data",
+                       "shield_configs.json")
     with open(dst, "w") as f:
         json.dump(out, f, indent=0, sort_keys=True)
     print("wrote", dst, len(out), "configs")

@@ -1,76 +1,24 @@
 """Shared helpers of the parity tests, smoke() and bench.py's checker legs (test infrastructure)."""
 from __future__ import annotations
 
-import json
 import os
-import tempfile
 
 import numpy as np
-import yaml
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-_CFG_DIR = None
 
-
-def configs() -> dict:
-    with open(os.path.join(ROOT, "tests", "golden", "configs.json")) as f:
-        return json.load(f)
-
-
-def config_dir() -> str:
-    """The golden configs written back out as YAML files in the reference schema (once per process)."""
-    global _CFG_DIR
-    if _CFG_DIR is None:
-        d = tempfile.mkdtemp(prefix="shield_cfg_")
-        for name, content in configs().items():
-            with open(os.path.join(d, name + ".yaml"), "w") as f:
-                yaml.safe_dump(content, f, default_flow_style=None)
-        # builder-supplied "full body, long horizon" variants for BASELINE config 4
-        full = full_body_mocap(configs()["mujoco_mocap"])
-        with open(os.path.join(d, "mujoco_mocap_full_body.yaml"), "w") as f:
-            yaml.safe_dump(full, f, default_flow_style=None)
-        long_h = dict(configs()["trajectory_parameters_schunk"])
-        long_h["max_s_stop"] = 0.5
-        with open(os.path.join(d, "trajectory_parameters_schunk_long.yaml"), "w") as f:
-            yaml.safe_dump(long_h, f, default_flow_style=None)
-        _CFG_DIR = d
-    return _CFG_DIR
-
-
-def full_body_mocap(base: dict) -> dict:
-    """mujoco_mocap.yaml + legs, pelvis and spine: 16 bodies, 4 extremities -> H = 4 + 16 + 16 = 36 capsules."""
-    m = json.loads(json.dumps(base))
-    extra = [("L_UpperLeg", "L_Hip", "L_Knee", 0.2), ("R_UpperLeg", "R_Hip", "R_Knee", 0.2),
-             ("L_LowerLeg", "L_Knee", "L_Ankle", 0.132), ("R_LowerLeg", "R_Knee", "R_Ankle", 0.132),
-             ("L_Foot", "L_Ankle", "L_Toe", 0.1), ("R_Foot", "R_Ankle", "R_Toe", 0.1),
-             ("Pelvis", "L_Hip", "R_Hip", 0.3), ("Spine", "Torso", "Chest", 0.434)]
-    for name, p, d, th in extra:
-        m["bodies"].append({"name": name, "proximal": p, "distal": d, "thickness": th})
-    m["extremities"].append({"name": "L_Leg", "base": "L_Hip", "end": "L_Toe", "length": 1.0, "thickness": 0.0})
-    m["extremities"].append({"name": "R_Leg", "base": "R_Hip", "end": "R_Toe", "length": 1.0, "thickness": 0.0})
-    return m
-
-
-def default_files(robot="schunk", mocap="mujoco_mocap", traj=None):
-    d = config_dir()
-    traj = traj or f"trajectory_parameters_{robot}"
-    return (os.path.join(d, traj + ".yaml"), os.path.join(d, f"robot_parameters_{robot}.yaml"),
-            os.path.join(d, mocap + ".yaml"))
-
-
-def mocap_joint_names(mocap_file: str):
-    from human_robot_gym_b200.config import load_yaml
-    return load_yaml(mocap_file)["joint_names"]
+from human_robot_gym_b200.workloads import (config_dir, configs, default_files, full_body_mocap,  # noqa: E402,F401
+                                            mocap_joint_names)
 
 
 def make_checker(files, n, base_pose, init_q, sample_time=0.004, shield_type=1, threads=8):
-    """The CPU checker for a batch: the reference build (oracle/_ref) when present, else the C restatement."""
+    """The CPU checker for a batch: the reference build (oracle/_ref). There is no second checker."""
     from oracle import ref
-    if ref.available():
-        return ref.RefBatch(n, sample_time, files[0], files[1], files[2], base_pose, init_q, shield_type=shield_type,
-                            threads=threads), "reference"
-    from oracle import port
-    return port.PortBatch(n, sample_time, files, base_pose, init_q, shield_type=shield_type), "port"
+    if not ref.available():
+        raise RuntimeError("oracle/_ref/libsara_ref.so is not built: run `python __graft_entry__.py` (or `make -C oracle "
+                           "ref`) in a container that has /root/reference; the prebuilt library travels to the GPU box")
+    return ref.RefBatch(n, sample_time, files[0], files[1], files[2], base_pose, init_q, shield_type=shield_type,
+                        threads=threads), "reference"
 
 
 def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0", sample_time=0.004, shield_type=1,

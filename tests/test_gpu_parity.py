@@ -56,7 +56,7 @@ def test_capsule_distance_matches_reference():
     from oracle import ref
     cabi, L = _lib()
     c1, c2 = capsule_cases()
-    want = ref.capsule_dist(c1, c2) if ref.available() else __import__("oracle.port", fromlist=["x"]).capsule_dist(c1, c2)
+    want = ref.capsule_dist(c1, c2)
     d1, d2 = _dev(c1), _dev(c2)
     out = torch.zeros(c1.shape[0], dtype=torch.float64, device="cuda:0")
     cabi.check(L.hrg_stage_capsule_dist(c1.shape[0], d1.data_ptr(), d2.data_ptr(), out.data_ptr(), None))

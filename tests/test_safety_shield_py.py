@@ -15,8 +15,9 @@ def test_motion_constructors_and_predicates():
     assert m.getS() == 0.5 and m.getVelocity() == [0.0, 0.0]
     m = Motion(0.0, [0.0, 0.0], [1.0, 0.0], [0.0, 0.0], [0.0, 0.0], 0.25)
     assert not m.isStopped() and m.getS() == 0.25
-    n = Motion(0.0, [0.0005, 0.0], [1.00005, 0.0])
-    assert m.hasSamePos(n) and m.hasSameVel(n) and not m.hasSameVel(Motion(0.0, [0, 0], [1.1, 0]))
+    n = Motion(0.0, [0.00005, 0.0], [1.00005, 0.0])
+    assert m.hasSamePos(n) and not m.hasSamePos(Motion(0.0, [0.0005, 0.0]))   # binding default 1e-4 (bindings :41)
+    assert m.hasSamePos(Motion(time=0.0, q=[0.0005, 0.0], s=1.0), threshold=1e-3) and m.hasSameVel(n) and not m.hasSameVel(Motion(0.0, [0, 0], [1.1, 0]))
     m.setTime(2.0); m.setS(3.0); m.setAngle([1, 1]); m.setJerk(np.array([0.5, 0.5]))
     assert (m.getTime(), m.getS(), m.getAngle(), m.getJerk()) == (2.0, 3.0, [1.0, 1.0], [0.5, 0.5])
     assert int(ShieldType.PFL) == 2 and eval("ShieldType." + "SSM") == ShieldType.SSM   # failsafe_controller.py:173
