@@ -23,8 +23,13 @@ def _ptr(t: Optional[torch.Tensor]):
 class BatchedSafetyShield:
     def __init__(self, n_envs: int, sample_time: float, trajectory_config_file: str, robot_config_file: str,
                  mocap_config_file: str, base_pose=None, init_qpos=None, shield_type=cabi.SHIELD_SSM,
-                 device: Optional[torch.device] = None, ltt_capacity: int = 1024, store_capsules: bool = False,
+                 device: Optional[torch.device] = None, ltt_capacity: Optional[int] = None, store_capsules: bool = False,
                  config: Optional[ShieldConfig] = None):
+        """ltt_capacity: samples per long-term-trajectory slot (two slots per env, 32 J bytes per sample). None = the bound
+        of cabi.ltt_capacity_bound(): no plan inside the joint limits can be longer, so behaviour equals the reference's
+        unbounded LTT. A smaller explicit capacity saves HBM (a FailsafeController goal is at most 0.2 rad away, ~230
+        samples); a plan that does not fit is then rejected (HRG_ST_LTT_TRUNCATED) and counted in
+        stats()["n_ltt_truncated"] - see check_health()."""
         self.lib = cabi.load_library()  # raises if the CUDA extension is missing
         if not torch.cuda.is_available():
             raise cabi.ShieldLibraryError("BatchedSafetyShield needs a CUDA device; there is no CPU fallback")
@@ -32,7 +37,10 @@ class BatchedSafetyShield:
                                                         mocap_config_file)
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.n_envs = int(n_envs)
-        self.cfg = cabi.make_cfg(self.config, ltt_capacity)
+        if ltt_capacity is None:
+            ltt_capacity = cabi.ltt_capacity_bound(self.config)
+        self.ltt_capacity = int(ltt_capacity)
+        self.cfg = cabi.make_cfg(self.config, self.ltt_capacity)
         self.J, self.K = self.cfg.nb_joints, self.cfg.n_keypoints
         self.H = self.cfg.n_ext + 2 * self.cfg.n_bodies
         N, J = self.n_envs, self.J
@@ -53,7 +61,7 @@ class BatchedSafetyShield:
         self.is_safe = torch.zeros(N, dtype=torch.uint8, device=self.device)
         self.branch = torch.zeros(N, dtype=torch.uint8, device=self.device)
         self.status = torch.zeros(N, dtype=torch.int32, device=self.device)
-        self._stats = torch.zeros(10, dtype=torch.int64, device=self.device)
+        self._stats = torch.zeros(cabi.STATS_WORDS, dtype=torch.int64, device=self.device)
         self._store = False
         if store_capsules:
             self.store_capsules(True)
@@ -88,9 +96,17 @@ class BatchedSafetyShield:
         N, J = self.n_envs, self.J
         pose, q0 = self._f64(base_pose, (N, 6)), self._f64(init_qpos, (N, J))
         t = self._f64(current_time, (N,))
-        ty = None  # NULL = all SSM (the library then does not need its PFL buffers)
-        if np.any(np.asarray(shield_type) != cabi.SHIELD_SSM):
-            ty = torch.as_tensor(shield_type, dtype=torch.int32, device=self.device).expand(N).contiguous()
+        ty = None  # NULL = all SSM
+        if isinstance(shield_type, torch.Tensor):
+            ty = shield_type.to(device=self.device, dtype=torch.int32).expand(N).contiguous()
+            any_pfl = bool((ty == cabi.SHIELD_PFL).any().item())
+        else:
+            st = np.asarray(shield_type)
+            any_pfl = bool(np.any(st == cabi.SHIELD_PFL))
+            if np.any(st != cabi.SHIELD_SSM):
+                ty = torch.as_tensor(st.astype(np.int32), device=self.device).expand(N).contiguous()
+        if any_pfl:  # PFL needs the per-sample Cartesian velocity buffers; allocate them before the first PFL reset
+            cabi.check(self.lib.hrg_shield_enable_pfl(self._h), "hrg_shield_enable_pfl")
         m = self._mask(env_mask)
         cabi.check(self.lib.hrg_shield_reset(self._h, _ptr(m), _ptr(pose), _ptr(q0), _ptr(t), _ptr(ty), self._stream()),
                    "hrg_shield_reset")
@@ -201,10 +217,23 @@ class BatchedSafetyShield:
         md = v[9:10].view(torch.float64).item()
         return {"n_steps": int(v[0]), "n_unsafe": int(v[1]), "n_branch": [int(v[2]), int(v[3]), int(v[4])],
                 "n_replan": int(v[5]), "n_replan_failed": int(v[6]), "n_near_threshold": int(v[7]),
-                "ltt_len_sum": int(v[8]), "min_dist": md}
+                "ltt_len_sum": int(v[8]), "min_dist": md, "n_ltt_truncated": int(v[10]), "n_pfl_rejected": int(v[11])}
+
+    def check_health(self):
+        """Raises if the batch has left the reference's behaviour: a plan longer than ltt_capacity was rejected (the
+        reference's LTT is unbounded), or an env asked for PFL on a handle without PFL buffers."""
+        st = self.stats()
+        if st["n_ltt_truncated"]:
+            raise cabi.ShieldLibraryError(
+                f"{st['n_ltt_truncated']} replans needed more than ltt_capacity={self.ltt_capacity} samples and were "
+                f"rejected; the reference would have accepted them. Use ltt_capacity >= "
+                f"{cabi.ltt_capacity_bound(self.config)} (or None)")
+        if st["n_pfl_rejected"]:
+            raise cabi.ShieldLibraryError(f"{st['n_pfl_rejected']} envs were reset to PFL without hrg_shield_enable_pfl")
+        return st
 
     def stats_tensor(self, clear=False) -> torch.Tensor:
-        """Raw [10] int64 device tensor (last word = min_dist bits) for the cross-GPU all_reduce."""
+        """Raw HrgStats as an int64 device tensor (word 9 = min_dist bits) for the cross-GPU all_reduce."""
         cabi.check(self.lib.hrg_shield_stats(self._h, _ptr(self._stats), int(clear), self._stream()), "hrg_shield_stats")
         return self._stats
 

@@ -47,7 +47,10 @@ class HrgControllerConfig(C.Structure):
 class HrgStats(C.Structure):
     _fields_ = [("n_steps", C.c_int64), ("n_unsafe", C.c_int64), ("n_branch", C.c_int64 * 3), ("n_replan", C.c_int64),
                 ("n_replan_failed", C.c_int64), ("n_near_threshold", C.c_int64), ("ltt_len_sum", C.c_int64),
-                ("min_dist", _D)]
+                ("min_dist", _D), ("n_ltt_truncated", C.c_int64), ("n_pfl_rejected", C.c_int64)]
+
+
+STATS_WORDS = C.sizeof(HrgStats) // 8  # the struct as int64 words (min_dist = word 9 as a bit pattern)
 
 
 def make_cfg(sc: ShieldConfig, ltt_capacity: int = 1024) -> HrgConfig:
@@ -97,6 +100,8 @@ SYMBOLS = {
     "hrg_shield_create": (C.c_int, [C.POINTER(HrgConfig), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.POINTER(C.c_void_p)]),
     "hrg_shield_destroy": (C.c_int, [C.c_void_p]),
+    "hrg_ltt_capacity_bound": (C.c_int, [C.POINTER(HrgConfig)]),
+    "hrg_shield_enable_pfl": (C.c_int, [C.c_void_p]),
     "hrg_shield_reset": (C.c_int, [C.c_void_p, _u8p, _dp, _dp, _dp, _i32p, _vp]),
     "hrg_shield_human_measurement": (C.c_int, [C.c_void_p, _u8p, _dp, _dp, _vp]),
     "hrg_shield_new_goal": (C.c_int, [C.c_void_p, _u8p, _dp, _dp, _vp]),
@@ -156,6 +161,16 @@ def load_library():
         fn.argtypes = args
     _lib = L
     return L
+
+
+def ltt_capacity_bound(sc: ShieldConfig) -> int:
+    """Samples per LTT slot that can never be exceeded by a plan inside the joint limits (hrg_ltt_capacity_bound): with at
+    least this `ltt_capacity` the library never rejects a plan the reference would accept."""
+    cfg = make_cfg(sc, 2)
+    n = load_library().hrg_ltt_capacity_bound(C.byref(cfg))
+    if n < 0:
+        check(n, "hrg_ltt_capacity_bound")
+    return int(n)
 
 
 def check(rc: int, what: str = ""):

@@ -121,6 +121,7 @@ int hrg_human_destroy(HrgHuman* h) {
 int hrg_human_reset(HrgHuman* h, const uint8_t* env_mask, const double* placement, const int32_t* clip_list,
                     void* stream) {
   if (!h || !placement || !clip_list) return fail(HRG_EINVAL, "hrg_human_reset: NULL argument");
+  CK(cudaSetDevice(h->device));
   hrg::k_human_reset<<<grid_for(h->H.N, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(h->H, env_mask, placement,
                                                                                              clip_list);
   h->launches++;
@@ -131,6 +132,7 @@ int hrg_human_reset(HrgHuman* h, const uint8_t* env_mask, const double* placemen
 int hrg_human_keypoints(HrgHuman* h, const int64_t* low_level_time, double* keypoints, int32_t* clip_out,
                         int32_t* frame_out, void* stream) {
   if (!h || !low_level_time || !keypoints) return fail(HRG_EINVAL, "hrg_human_keypoints: NULL argument");
+  CK(cudaSetDevice(h->device));
   hrg::k_human_keypoints<<<grid_for(h->H.N, hrg::kHumanTileEnvs), hrg::kHumanBlock, 0,
                            static_cast<cudaStream_t>(stream)>>>(h->H, low_level_time, keypoints, clip_out, frame_out);
   h->launches++;
@@ -144,6 +146,7 @@ int hrg_shield_tick_replay_host(HrgShield* s, HrgHuman* h, const int64_t* low_le
   if (!s || !h || !low_level_time_host || !t_host) return fail(HRG_EINVAL, "hrg_shield_tick_replay_host: NULL argument");
   if (h->H.N != s->S.N || h->H.K != s->S.K || h->device != s->device)
     return fail(HRG_EINVAL, "hrg_shield_tick_replay_host: the human batch and the shield batch differ (envs, keypoints or device)");
+  CK(cudaSetDevice(s->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t N = s->S.N, J = s->S.J;
   CK(cudaMemcpyAsync(h->d_clock, low_level_time_host, N * sizeof(int64_t), cudaMemcpyHostToDevice, st));

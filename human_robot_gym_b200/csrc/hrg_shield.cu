@@ -195,8 +195,12 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   S.human_caps = nullptr;
   S.ltt_time = nullptr;
   if (h->pfl) {
-    AL(S.ltt_cart, (size_t)N * 2 * L);
-    AL(S.ltt_time, (size_t)N * 2 * L);
+    h->pfl = false;
+    rc = hrg_shield_enable_pfl(h);
+    if (rc) {
+      hrg_shield_destroy(h);
+      return rc;
+    }
   }
   // staging buffers of hrg_shield_tick_host
   AL(h->d_kp, (size_t)K * 3 * N);
@@ -294,18 +298,50 @@ int hrg_shield_num_envs(const HrgShield* s) { return s ? s->S.N : 0; }
 int hrg_shield_num_human_capsules(const HrgShield* s) { return s ? s->S.H : 0; }
 int64_t hrg_shield_launch_count(const HrgShield* s) { return s ? s->launches : 0; }
 
+int hrg_ltt_capacity_bound(const HrgConfig* c) {
+  if (cfg_check(c)) return HRG_EINVAL;
+  double worst = 0.0;
+  for (int j = 0; j < c->nb_joints; ++j) {
+    const double v = c->v_max[j], a = c->a_max_ltt[j], jk = c->j_max_ltt[j];
+    if (!(v > 0 && a > 0 && jk > 0)) return fail(HRG_EINVAL, "hrg_ltt_capacity_bound: limits must be > 0");
+    const double range = fabs(c->q_max[j] - c->q_min[j]);
+    const double ramp = v / a + a / jk;  // 0 -> v_max under (a, j), or back
+    // brake from full speed the wrong way, overshoot by at most v * ramp, cross the range plus that overshoot, settle
+    const double T = ramp + (range + v * ramp) / v + 2.0 * ramp;
+    if (T > worst) worst = T;
+  }
+  const double n = ceil(worst / c->sample_time) + 8.0;
+  return n > 2.0e9 ? 2000000000 : (int)n;
+}
+
+int hrg_shield_enable_pfl(HrgShield* s) {
+  if (!s) return fail(HRG_EINVAL, "hrg_shield_enable_pfl: NULL handle");
+  if (s->S.ltt_cart && s->S.ltt_time) return HRG_OK;
+  CK(cudaSetDevice(s->device));
+  CK(cudaDeviceSynchronize());  // kernels in flight hold DevState copies with the NULL pointers
+  double *cart = nullptr, *tm = nullptr;
+  const size_t nb = (size_t)s->S.N * 2 * s->S.L * sizeof(double);
+  cudaError_t e = cudaMalloc(&cart, nb);
+  if (e == cudaSuccess) e = cudaMalloc(&tm, nb);
+  if (e == cudaSuccess) e = cudaMemset(cart, 0, nb);
+  if (e == cudaSuccess) e = cudaMemset(tm, 0, nb);
+  if (e != cudaSuccess) {  // both or neither
+    cudaFree(cart);
+    cudaFree(tm);
+    return fail(HRG_ENOMEM, "hrg_shield_enable_pfl: allocation of the PFL buffers failed", e);
+  }
+  s->allocs.push_back(cart);
+  s->allocs.push_back(tm);
+  s->S.ltt_cart = cart;
+  s->S.ltt_time = tm;
+  s->pfl = true;
+  return HRG_OK;
+}
+
 int hrg_shield_reset(HrgShield* s, const uint8_t* env_mask, const double* base_pose, const double* init_q,
                      const double* t, const int32_t* shield_type, void* stream) {
   if (!s || !base_pose || !init_q) return fail(HRG_EINVAL, "hrg_shield_reset: NULL argument");
-  if (shield_type && !s->S.ltt_cart) {
-    // explicit types may contain PFL: make sure the per-sample Cartesian velocity / time buffers exist
-    CK(cudaSetDevice(s->device));
-    int rc = s->alloc(&s->S.ltt_cart, (size_t)s->S.N * 2 * s->S.L);
-    if (rc) return rc;
-    rc = s->alloc(&s->S.ltt_time, (size_t)s->S.N * 2 * s->S.L);
-    if (rc) return rc;
-    s->pfl = true;
-  }
+  CK(cudaSetDevice(s->device));
   (void)t;  // cycle_begin_time_ is only stored by the reference (safety_shield.cc:185)
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   k_reset<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S, env_mask, base_pose, init_q, shield_type);
@@ -317,6 +353,7 @@ int hrg_shield_reset(HrgShield* s, const uint8_t* env_mask, const double* base_p
 int hrg_shield_human_measurement(HrgShield* s, const uint8_t* env_mask, const double* keypoints, const double* t,
                                  void* stream) {
   if (!s || !keypoints || !t) return fail(HRG_EINVAL, "hrg_shield_human_measurement: NULL argument");
+  CK(cudaSetDevice(s->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   k_measure<<<tile_grid(s->S.N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, env_mask, keypoints, t);
   s->launches++;
@@ -327,6 +364,7 @@ int hrg_shield_human_measurement(HrgShield* s, const uint8_t* env_mask, const do
 int hrg_shield_new_goal(HrgShield* s, const uint8_t* env_mask, const double* goal_q, const double* goal_dq,
                         void* stream) {
   if (!s || !goal_q) return fail(HRG_EINVAL, "hrg_shield_new_goal: NULL argument");
+  CK(cudaSetDevice(s->device));
   (void)goal_dq;  // clamped and stored by the reference, never read on the step path (safety_shield.cc:682-684)
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   k_new_goal<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S, env_mask, goal_q);
@@ -357,6 +395,7 @@ static void verify_pass0(HrgShield* s, cudaStream_t st, size_t smem) {
 static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, const double* goal_q, const double* t,
                      double* q, double* dq, double* ddq, double* dddq,
                      uint8_t* is_safe, uint8_t* branch, uint32_t* status, void* stream) {
+  CK(cudaSetDevice(s->device));  // a handle on cuda:1 may be driven while another device is current
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int N = s->S.N;
   const bool prof = s->prof && s->ev_used + 5 <= s->ev.size();
@@ -443,6 +482,7 @@ int hrg_shield_tick_host(HrgShield* s, const double* keypoints_host, const doubl
                          const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
                          double* ddq_host, uint8_t* flags_host, void* stream) {
   if (!s || !keypoints_host || !t_host) return fail(HRG_EINVAL, "hrg_shield_tick_host: NULL argument");
+  CK(cudaSetDevice(s->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t N = s->S.N, J = s->S.J, K3 = (size_t)s->S.K * 3;
   CK(cudaMemcpyAsync(s->d_kp, keypoints_host, N * K3 * sizeof(double), cudaMemcpyHostToDevice, st));
@@ -470,6 +510,7 @@ int hrg_shield_upload_inputs(HrgShield* s, int slot, const double* keypoints_hos
                              const uint8_t* goal_mask_host, const double* goal_q_host, void* copy_stream) {
   if (!s || !keypoints_host || !t_host || slot < 0 || slot > 1)
     return fail(HRG_EINVAL, "hrg_shield_upload_inputs: bad argument");
+  CK(cudaSetDevice(s->device));
   cudaStream_t cs = static_cast<cudaStream_t>(copy_stream);
   const size_t N = s->S.N, J = s->S.J, K3 = (size_t)s->S.K * 3;
   // do not overwrite the slot before the tick that consumed it last has finished with it
@@ -488,6 +529,7 @@ int hrg_shield_upload_inputs(HrgShield* s, int slot, const double* keypoints_hos
 int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_host, double* ddq_host,
                            uint8_t* flags_host, void* stream) {
   if (!s || slot < 0 || slot > 1) return fail(HRG_EINVAL, "hrg_shield_tick_staged: bad argument");
+  CK(cudaSetDevice(s->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t N = s->S.N, J = s->S.J;
   CK(cudaStreamWaitEvent(st, s->ev_up[slot], 0));

@@ -12,6 +12,7 @@ __global__ void k_copy_stats(HrgStats* dst, HrgStats* src, int clear) {
       z.n_steps = 0; z.n_unsafe = 0; z.n_branch[0] = z.n_branch[1] = z.n_branch[2] = 0;
       z.n_replan = 0; z.n_replan_failed = 0; z.n_near_threshold = 0; z.ltt_len_sum = 0;
       z.min_dist = INFINITY;
+      z.n_ltt_truncated = 0; z.n_pfl_rejected = 0;
       *src = z;
     }
   }
@@ -157,6 +158,7 @@ int hrg_shield_store_capsules(HrgShield* s, int on) {
 
 int hrg_shield_get_capsules(HrgShield* s, double* robot, double* human, double* min_dist, void* stream) {
   if (!s) return fail(HRG_EINVAL, "hrg_shield_get_capsules: NULL handle");
+  CK(cudaSetDevice(s->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if ((robot || human) && !s->S.robot_caps)
     return fail(HRG_EINVAL, "capsules are not stored: call hrg_shield_store_capsules(s, 1) before stepping");
@@ -173,6 +175,7 @@ int hrg_shield_get_capsules(HrgShield* s, double* robot, double* human, double* 
 
 int hrg_shield_stats(HrgShield* s, HrgStats* out, int clear, void* stream) {
   if (!s || !out) return fail(HRG_EINVAL, "hrg_shield_stats: NULL argument");
+  CK(cudaSetDevice(s->device));
   k_copy_stats<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(out, s->S.stats, clear);
   s->launches++;
   CK(cudaGetLastError());
@@ -209,6 +212,7 @@ int hrg_shield_set_ltt_batch(HrgShield* s, int n_traj, const int32_t* env_index,
                              const double* alpha_i, int32_t* verdict, void* stream) {
   if (!s || !env_index || !traj || !length || !alpha_i || !verdict)
     return fail(HRG_EINVAL, "hrg_shield_set_ltt_batch: NULL argument");
+  CK(cudaSetDevice(s->device));
   if (n_traj < 0 || max_len < 1) return fail(HRG_EINVAL, "hrg_shield_set_ltt_batch: n_traj < 0 or max_len < 1");
   if (!(sample_time > 0)) return fail(HRG_EINVAL, "hrg_shield_set_ltt_batch: sample_time must be > 0");
   if (n_traj == 0) return HRG_OK;
@@ -349,6 +353,7 @@ int hrg_capsule_markers(int n, const double* caps, double* pos, double* size, do
 int hrg_shield_ltt_max_window(HrgShield* s, const int32_t* index, int window_k, double* max_acc, double* max_jerk,
                               void* stream) {
   if (!s) return fail(HRG_EINVAL, "hrg_shield_ltt_max_window: NULL handle");
+  CK(cudaSetDevice(s->device));
   if (window_k <= 0) window_k = (int)floor(s->cfg.max_s_stop / s->cfg.sample_time);  // sliding_window_k_ (safety_shield.cc:88)
   k_ltt_max_window<<<grid_for(s->S.N, 4), 128, 0, static_cast<cudaStream_t>(stream)>>>(s->S, index, window_k, max_acc, max_jerk);
   s->launches++;
@@ -360,6 +365,7 @@ int hrg_controller_set_goal(HrgShield* s, const HrgControllerConfig* cfg, const 
                             const double* joint_pos, const double* set_qpos, double* goal_out, void* stream) {
   if (int rc = ctrl_check(s, cfg, "hrg_controller_set_goal: NULL argument")) return rc;
   if (!set_qpos && (!action || !joint_pos)) return fail(HRG_EINVAL, "hrg_controller_set_goal: action / joint_pos NULL");
+  CK(cudaSetDevice(s->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   k_ctrl_set_goal<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S, *cfg, env_mask, action, joint_pos, set_qpos, goal_out);
   s->launches++;
@@ -373,6 +379,7 @@ int hrg_controller_torques(HrgShield* s, const HrgControllerConfig* cfg, const d
   if (int rc = ctrl_check(s, cfg, "hrg_controller_torques: NULL argument")) return rc;
   if (!q_des || !dq_des || !ddq_des || !joint_pos || !joint_vel || !mass_matrix || !torque_comp || !torques)
     return fail(HRG_EINVAL, "hrg_controller_torques: NULL argument");
+  CK(cudaSetDevice(s->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   k_ctrl_torques<<<grid_for(s->S.N, 128), 128, 0, st>>>(s->S.N, s->S.J, *cfg, q_des, dq_des, ddq_des, joint_pos, joint_vel,
                                                         mass_matrix, torque_comp, torques);

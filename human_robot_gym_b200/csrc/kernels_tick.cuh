@@ -384,10 +384,11 @@ __global__ void __launch_bounds__(128) k_replan_sample(DevState S, const double*
 __global__ void __launch_bounds__(kTickBlock)
     k_select(DevState S, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe, uint8_t* branch,
              uint32_t* status) {
-  __shared__ unsigned long long s_cnt[8];
+  constexpr int NC = 9;
+  __shared__ unsigned long long s_cnt[NC];
   __shared__ double s_min;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0ull;
+  if (threadIdx.x < NC) s_cnt[threadIdx.x] = 0ull;
   if (threadIdx.x == 0) s_min = INFINITY;
   __syncthreads();
   if (e == 0) {
@@ -395,7 +396,7 @@ __global__ void __launch_bounds__(kTickBlock)
     for (int k = 0; k < N_CTR; ++k) S.replan_ctr[k] = 0;
     S.verify_cnt[0] = S.verify_cnt[1] = 0;
   }
-  unsigned long long my[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum
+  unsigned long long my[NC] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum, truncated
   double my_min = INFINITY;
   if (e < S.N) {
     const HrgConfig& c = *S.cfg;
@@ -414,6 +415,7 @@ __global__ void __launch_bounds__(kTickBlock)
       my[4] = (st & HRG_ST_REPLANNED) ? 1 : 0;
       my[5] = (st & HRG_ST_REPLAN_FAILED) ? 1 : 0;
       my[6] = (st & HRG_ST_NEAR_THRESHOLD) ? 1 : 0;
+      my[8] = (st & HRG_ST_LTT_TRUNCATED) ? 1 : 0;
       if ((st & HRG_ST_REPLANNED) && !(st & HRG_ST_REPLAN_FAILED))
         my[7] = (unsigned long long)S.ltt_len[(size_t)((f & F_LIVE_SLOT) ? 0 : 1) * S.N + e];
       if (f & F_VERIFY) {
@@ -422,7 +424,7 @@ __global__ void __launch_bounds__(kTickBlock)
     }
   }
   if (S.stats) {
-    for (int k = 0; k < 8; ++k) {
+    for (int k = 0; k < NC; ++k) {
       unsigned long long v = my[k];
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_cnt[k], v);
@@ -446,6 +448,7 @@ __global__ void __launch_bounds__(kTickBlock)
       atomicAdd(&g[0], (unsigned long long)n_here);
       for (int k = 0; k < 8; ++k)
         if (s_cnt[k]) atomicAdd(&g[1 + k], s_cnt[k]);
+      if (s_cnt[8]) atomicAdd(reinterpret_cast<unsigned long long*>(&S.stats->n_ltt_truncated), s_cnt[8]);
       if (s_min < INFINITY) {
         unsigned long long* a = reinterpret_cast<unsigned long long*>(&S.stats->min_dist);
         unsigned long long old = *a;
@@ -470,7 +473,12 @@ __global__ void k_reset(DevState S, const uint8_t* __restrict__ mask, const doub
   if (mask && !mask[e]) return;
   const HrgConfig& c = *S.cfg;
   const int J = S.J, N = S.N;
-  const uint32_t type = shield_type ? (uint32_t)shield_type[e] : (uint32_t)HRG_SHIELD_SSM;
+  uint32_t type = shield_type ? (uint32_t)shield_type[e] : (uint32_t)HRG_SHIELD_SSM;
+  if (type > HRG_SHIELD_PFL) type = HRG_SHIELD_SSM;
+  if (type == HRG_SHIELD_PFL && !S.ltt_cart) {  // not a PFL-capable handle (hrg_shield_enable_pfl): keep SSM, count it
+    type = HRG_SHIELD_SSM;
+    if (S.stats) atomicAdd(reinterpret_cast<unsigned long long*>(&S.stats->n_pfl_rejected), 1ull);
+  }
   uint32_t f = S.flags[e] & F_UNDER_V_LIMIT;  // is_under_v_limit_ is not touched by reset()
   f |= (type << F_TYPE_SHIFT) & F_TYPE_MASK;
   if (type == HRG_SHIELD_OFF) f |= F_IS_SAFE;

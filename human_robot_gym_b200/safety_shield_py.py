@@ -193,7 +193,7 @@ class SafetyShield:
                  robot_config_file: Optional[str] = None, mocap_config_file: Optional[str] = None,
                  init_x: float = 0.0, init_y: float = 0.0, init_z: float = 0.0, init_roll: float = 0.0,
                  init_pitch: float = 0.0, init_yaw: float = 0.0, init_qpos=None,
-                 shield_type: ShieldType = ShieldType.SSM, device=None, ltt_capacity: int = 2048):
+                 shield_type: ShieldType = ShieldType.SSM, device=None, ltt_capacity: Optional[int] = None):
         self._b = None
         self._type = ShieldType(int(shield_type))
         self._safe = False

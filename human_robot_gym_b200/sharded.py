@@ -15,6 +15,7 @@ import torch.distributed as dist
 
 STAT_FIELDS = ("n_steps", "n_unsafe", "n_branch0", "n_branch1", "n_branch2", "n_replan", "n_replan_failed",
                "n_near_threshold", "ltt_len_sum")  # then min_dist (f64 bit pattern) — struct HrgStats, include/hrg_shield.h
+TAIL_FIELDS = ("n_ltt_truncated", "n_pfl_rejected")  # after min_dist
 
 
 def shard_range(n_total: int, rank: int, world: int) -> Tuple[int, int]:
@@ -34,17 +35,17 @@ def shard(x, rank: int, world: int, n_total: Optional[int] = None):
 
 
 def reduce_stats(stats: torch.Tensor, group=None) -> dict:
-    """All-reduce one raw HrgStats tensor (int64[10], last word = min_dist bits) over the ranks -> dict.
+    """All-reduce one raw HrgStats tensor (int64 words, word 9 = min_dist bits) over the ranks -> dict.
 
     Works on whatever device the tensor lives on (cuda with the nccl backend, cpu with gloo). Without an initialised
     process group the local values are returned unchanged."""
-    counts = stats[:9].clone()
+    counts = torch.cat([stats[:9], stats[10:10 + len(TAIL_FIELDS)]])
     mind = stats[9:10].clone().view(torch.float64)
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(mind, op=dist.ReduceOp.MIN, group=group)
     c = counts.cpu().tolist()
-    out = dict(zip(STAT_FIELDS, (int(v) for v in c)))
+    out = dict(zip(STAT_FIELDS + TAIL_FIELDS[:max(0, len(c) - 9)], (int(v) for v in c)))
     out["min_dist"] = float(mind.item())
     out["n_branch"] = [out.pop("n_branch0"), out.pop("n_branch1"), out.pop("n_branch2")]
     return out
@@ -75,6 +76,11 @@ class ShardedShield:
             bp = bp[self.lo:self.hi]
         if iq is not None and iq.ndim == 2:
             iq = iq[self.lo:self.hi]
+        if "shield_type" in kw:  # a per-env ShieldType array is sharded like base_pose / init_qpos
+            import numpy as np
+            ty = np.asarray(kw["shield_type"])
+            if ty.ndim == 1:
+                kw = dict(kw, shield_type=ty[self.lo:self.hi])
         self.local = BatchedSafetyShield(self.hi - self.lo, sample_time, trajectory_config_file, robot_config_file,
                                          mocap_config_file, base_pose=None if bp is None else bp.numpy(),
                                          init_qpos=None if iq is None else iq.numpy(), device=device, **kw)

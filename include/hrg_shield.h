@@ -80,6 +80,10 @@ typedef struct HrgStats {
   int64_t n_near_threshold; /* steps with a capsule distance within 1e-6 of 0 */
   int64_t ltt_len_sum;      /* sum of planned LTT lengths (mean L = ltt_len_sum / (n_replan - n_replan_failed)) */
   double min_dist;          /* smallest capsule distance seen */
+  int64_t n_ltt_truncated;  /* replans rejected because the plan needs more than ltt_capacity samples: the ONE place where
+                             * this library can diverge from the reference (its LTT is an unbounded std::vector); must be 0
+                             * for parity - size ltt_capacity with hrg_ltt_capacity_bound() */
+  int64_t n_pfl_rejected;   /* envs reset to ShieldType PFL on a handle without PFL buffers (kept as SSM); must be 0 */
 } HrgStats;
 
 /* Constant tables of the batched FailsafeController: robosuite 1.3.2 Controller.scale_action ranges,
@@ -104,8 +108,21 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
                       const double* init_q_host, const int32_t* shield_type_host, HrgShield** out);
 int hrg_shield_destroy(HrgShield* s);
 
+/* Upper bound on the number of samples LongTermPlanner::getTrajectory (LTP/src/long_term_planner.cc:706-841) can emit for
+ * ANY reachable start state and goal inside the joint limits of cfg: per joint, the time to brake from (v_max, a_max_ltt),
+ * cross the whole range [q_min, q_max] with a v_max / a_max_ltt / j_max_ltt profile and settle, over sample_time (+ slack).
+ * A handle whose ltt_capacity is at least this never truncates, i.e. never diverges from the reference's unbounded LTT. */
+int hrg_ltt_capacity_bound(const HrgConfig* cfg);
+
+/* Make the handle PFL-capable (per-sample Cartesian velocity + time buffers of both LTT slots, 2 x N x L doubles each).
+ * Implied by a PFL entry in hrg_shield_create's shield_type; needed before hrg_shield_reset may switch envs to PFL.
+ * Allocates both buffers or neither. Synchronous (cudaMalloc); not for the tick path. */
+int hrg_shield_enable_pfl(HrgShield* s);
+
 /* SafetyShield.reset(init_x.., init_qpos, current_time, shield_type) — bindings :97-106 / safety_shield.cc:164-201.
- * env_mask [N] u8 or NULL (all). */
+ * env_mask [N] u8 or NULL (all). shield_type [N] i32 or NULL (all SSM); PFL entries need a PFL-capable handle (see
+ * hrg_shield_enable_pfl) - on a handle without, such envs are kept as SSM and counted in HrgStats.n_pfl_rejected.
+ * Never allocates. */
 int hrg_shield_reset(HrgShield* s, const uint8_t* env_mask, const double* base_pose, const double* init_q,
                      const double* t, const int32_t* shield_type, void* stream);
 

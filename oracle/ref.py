@@ -27,6 +27,10 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.ref_create.restype = C.c_void_p
         L.ref_create.argtypes = [C.c_int, C.c_double, C.c_char_p, C.c_char_p, C.c_char_p, _dp, _dp, C.c_int, C.c_int, C.c_int]
+        L.ref_create_types.restype = C.c_void_p
+        L.ref_create_types.argtypes = [C.c_int, C.c_double, C.c_char_p, C.c_char_p, C.c_char_p, _dp, _dp, C.c_int, C.c_int,
+                                       C.c_void_p, C.c_int]
+        L.ref_reset_types.argtypes = [C.c_void_p, _u8p, _dp, _dp, _dp, C.c_int, C.c_void_p]
         L.ref_destroy.argtypes = [C.c_void_p]
         L.ref_set_threads.argtypes = [C.c_void_p, C.c_int]
         L.ref_num_keypoints.argtypes = [C.c_void_p]
@@ -37,6 +41,8 @@ def lib():
         L.ref_step.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, _dp, _u8p, _u8p]
         L.ref_get_capsules.argtypes = [C.c_void_p, _dp, _dp, C.c_int, _dp]
         L.ref_get_state.argtypes = [C.c_void_p, C.c_int, _dp]
+        L.ref_get_paths.argtypes = [C.c_void_p, _dp]
+        L.ref_stage_reach_verify.argtypes = [C.c_void_p, C.c_int] + [_dp] * 10 + [C.c_int, _dp, _u8p]
         L.ref_capsule_dist.argtypes = [C.c_int, _dp, _dp, _dp]
         L.ref_plan_safety_shield.argtypes = [C.c_void_p, C.c_int, _dp, _u8p, _dp, _dp]
         L.ref_ltp_plan.restype = C.c_int
@@ -71,7 +77,7 @@ def _f64(a, shape=None):
 
 
 class RefBatch:
-    """N independent reference `SafetyShield` objects (one per env), SSM=1 / PFL=2 / OFF=0."""
+    """N independent reference `SafetyShield` objects (one per env), SSM=1 / PFL=2 / OFF=0 (a scalar or one per env)."""
 
     def __init__(self, n, sample_time, traj_yaml, robot_yaml, mocap_yaml, base_pose, init_q, shield_type=1, threads=1):
         init_q = _f64(init_q)
@@ -82,8 +88,9 @@ class RefBatch:
             base_pose = np.tile(base_pose, (n, 1))
         self.n, self.J = n, init_q.shape[1]
         self._bp, self._iq = np.ascontiguousarray(base_pose), np.ascontiguousarray(init_q)
-        self.h = lib().ref_create(n, float(sample_time), traj_yaml.encode(), robot_yaml.encode(), mocap_yaml.encode(),
-                                  _d(self._bp), _d(self._iq), self.J, int(shield_type), int(threads))
+        ty = np.ascontiguousarray(np.broadcast_to(np.asarray(shield_type, np.int32), (n,)))
+        self.h = lib().ref_create_types(n, float(sample_time), traj_yaml.encode(), robot_yaml.encode(), mocap_yaml.encode(),
+                                        _d(self._bp), _d(self._iq), self.J, 1, ty.ctypes.data, int(threads))
         self.K = lib().ref_num_keypoints(self.h)
 
     def __del__(self):
@@ -99,7 +106,8 @@ class RefBatch:
 
     def reset(self, base_pose, init_q, t, shield_type=1, mask=None):
         bp, iq, tt, m = _f64(base_pose, (self.n, 6)), _f64(init_q, (self.n, self.J)), _f64(t, (self.n,)), self._mask(mask)
-        lib().ref_reset(self.h, _u8(m), _d(bp), _d(iq), _d(tt), int(shield_type))
+        ty = np.ascontiguousarray(np.broadcast_to(np.asarray(shield_type, np.int32), (self.n,)))
+        lib().ref_reset_types(self.h, _u8(m), _d(bp), _d(iq), _d(tt), 1, ty.ctypes.data)
 
     def human_measurement(self, kp, t, mask=None):
         kp, tt, m = _f64(kp, (self.n, self.K, 3)), _f64(np.broadcast_to(t, (self.n,))), self._mask(mask)
@@ -135,6 +143,23 @@ class RefBatch:
         idx = None if index is None else np.ascontiguousarray(index, dtype=np.int32)
         lib().ref_live_max_window(self.h, None if idx is None else idx.ctypes.data, _d(acc), _d(jerk))
         return acc, jerk
+
+    def paths(self):
+        """[n, 5, 11]: recovery, failsafe, failsafe_2, safe, potential path x (phases[6], pos, vel, acc, jerk, is_current)."""
+        out = np.zeros((self.n, 5, 11))
+        lib().ref_get_paths(self.h, _d(out))
+        return out
+
+    def stage_reach_verify(self, base_pose, q_start, q_goal, s_diff, t_reach, alpha_i, kp_pos, kp_vel, H):
+        """reach + humanReachabilityAnalysis + verify_human_reach on explicit inputs (n cases, on the objects of env 0)
+        -> robot [n,J,7], human [n,H,7], min_dist [n,3], is_safe [n]."""
+        n = np.asarray(s_diff).shape[0]
+        a = [_f64(base_pose, (n, 6)), _f64(q_start, (n, self.J)), _f64(q_goal, (n, self.J)), _f64(s_diff, (n,)),
+             _f64(t_reach, (n,)), _f64(alpha_i, (n, self.J)), _f64(kp_pos, (n, self.K, 3)), _f64(kp_vel, (n, self.K, 3))]
+        robot, human, md = np.zeros((n, self.J, 7)), np.zeros((n, H, 7)), np.full((n, 3), np.inf)
+        safe = np.zeros(n, dtype=np.uint8)
+        lib().ref_stage_reach_verify(self.h, n, *[_d(x) for x in a], _d(robot), _d(human), int(H), _d(md), _u8(safe))
+        return robot, human, md, safe
 
     def state(self, i):
         out = np.zeros(63)

@@ -5,7 +5,9 @@
 // objects and drives them with the loop shape of SS/src/debug.cc:38-55
 // (humanMeasurement -> [newLongTermTrajectory] -> step), dumping everything the parity tests compare.
 // Built with -fno-access-control so private members of the reference classes can be read without touching its sources.
+#include <algorithm>
 #include <array>
+#include <cmath>
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -67,8 +69,10 @@ void put_path(Path& p, double* o) {  // 11 doubles: phases[6], pos, vel, acc, je
 extern "C" {
 
 // ---------------------------------------------------------------------------------------------------- batch of shields
-void* ref_create(int n, double sample_time, const char* traj_yaml, const char* robot_yaml, const char* mocap_yaml,
-                 const double* base_pose /*[n,6]*/, const double* init_q /*[n,J]*/, int J, int shield_type, int threads) {
+// types != NULL: one ShieldType per env (mixed OFF / SSM / PFL batches), else `shield_type` for all.
+void* ref_create_types(int n, double sample_time, const char* traj_yaml, const char* robot_yaml, const char* mocap_yaml,
+                       const double* base_pose /*[n,6]*/, const double* init_q /*[n,J]*/, int J, int shield_type,
+                       const int32_t* types /*[n] or NULL*/, int threads) {
   spdlog::set_level(spdlog::level::off);
   RefBatch* b = new RefBatch();
   b->n = n;
@@ -79,25 +83,34 @@ void* ref_create(int n, double sample_time, const char* traj_yaml, const char* r
     std::vector<double> q(init_q + static_cast<size_t>(i) * J, init_q + static_cast<size_t>(i + 1) * J);
     const double* p = base_pose + static_cast<size_t>(i) * 6;
     b->env[i].reset(new SafetyShield(sample_time, traj_yaml, robot_yaml, mocap_yaml, p[0], p[1], p[2], p[3], p[4], p[5], q,
-                                     static_cast<ShieldType>(shield_type)));
+                                     static_cast<ShieldType>(types ? types[i] : shield_type)));
   }
   b->K = static_cast<int>(b->env[0]->human_reach_->n_joints_meas_);
   return b;
+}
+void* ref_create(int n, double sample_time, const char* traj_yaml, const char* robot_yaml, const char* mocap_yaml,
+                 const double* base_pose, const double* init_q, int J, int shield_type, int threads) {
+  return ref_create_types(n, sample_time, traj_yaml, robot_yaml, mocap_yaml, base_pose, init_q, J, shield_type, nullptr,
+                          threads);
 }
 void ref_destroy(void* h) { delete static_cast<RefBatch*>(h); }
 void ref_set_threads(void* h, int threads) { static_cast<RefBatch*>(h)->threads = threads; }
 int ref_num_keypoints(void* h) { return static_cast<RefBatch*>(h)->K; }
 int ref_num_joints(void* h) { return static_cast<RefBatch*>(h)->env[0]->nb_joints_; }
 
-void ref_reset(void* h, const uint8_t* mask, const double* base_pose, const double* init_q, const double* t,
-               int shield_type) {
+void ref_reset_types(void* h, const uint8_t* mask, const double* base_pose, const double* init_q, const double* t,
+                     int shield_type, const int32_t* types /*[n] or NULL*/) {
   RefBatch* b = static_cast<RefBatch*>(h);
   par_for(b, [=](int i) {
     if (mask && !mask[i]) return;
     const double* p = base_pose + static_cast<size_t>(i) * 6;
     std::vector<double> q(init_q + static_cast<size_t>(i) * b->J, init_q + static_cast<size_t>(i + 1) * b->J);
-    b->env[i]->reset(p[0], p[1], p[2], p[3], p[4], p[5], q, t[i], static_cast<ShieldType>(shield_type));
+    b->env[i]->reset(p[0], p[1], p[2], p[3], p[4], p[5], q, t[i], static_cast<ShieldType>(types ? types[i] : shield_type));
   });
+}
+void ref_reset(void* h, const uint8_t* mask, const double* base_pose, const double* init_q, const double* t,
+               int shield_type) {
+  ref_reset_types(h, mask, base_pose, init_q, t, shield_type, nullptr);
 }
 
 void ref_human_measurement(void* h, const uint8_t* mask, const double* kp /*[n,K,3]*/, const double* t /*[n]*/) {
@@ -184,6 +197,21 @@ void ref_get_state(void* h, int i, double* out /*[63]*/) {
   out[60] = s.recovery_path_correct_;
   out[61] = s.long_term_trajectory_.getLength();
   out[62] = s.new_long_term_trajectory_.getLength();
+}
+
+// recovery / failsafe / failsafe_2 / safe / potential path of every env (11 doubles each, see put_path) - lets a test
+// scenario time its human input on the reference's own braking state (tests/parity_util.py AdaptivePulseScenario).
+void ref_get_paths(void* h, double* out /*[n,5,11]*/) {
+  RefBatch* b = static_cast<RefBatch*>(h);
+  for (int i = 0; i < b->n; ++i) {
+    SafetyShield& s = *b->env[i];
+    double* o = out + static_cast<size_t>(i) * 55;
+    put_path(s.recovery_path_, o);
+    put_path(s.failsafe_path_, o + 11);
+    put_path(s.failsafe_path_2_, o + 22);
+    put_path(s.safe_path_, o + 33);
+    put_path(s.potential_path_, o + 44);
+  }
 }
 
 // ------------------------------------------------------------------------------------------- per-stage entry points
@@ -324,6 +352,49 @@ int ref_human_reach(void* h, int i, double t_command, double t_brake, double* ou
     for (auto& c : set)
       if (k < max_caps) put_capsule(c, out + 7 * k++);
   return k;
+}
+
+// RobotReach::reach (SS/src/robot_reach.cc:61-98) + HumanReach::humanReachabilityAnalysis (human_reach.cc:76-87) +
+// VerifyISO::verify_human_reach (verify_iso.cc:19-33) on explicit inputs, one case after the other on the objects of env 0
+// (its base pose, measurement buffers and capsules are overwritten): the stage hrg_stage_reach_verify mirrors.
+void ref_stage_reach_verify(void* h, int n, const double* base_pose /*[n,6]*/, const double* q_start /*[n,J]*/,
+                            const double* q_goal /*[n,J]*/, const double* s_diff /*[n]*/, const double* t_reach /*[n]*/,
+                            const double* alpha_i /*[n,J]*/, const double* kp_pos /*[n,K,3]*/,
+                            const double* kp_vel /*[n,K,3]*/, double* robot /*[n,J,7]*/, double* human /*[n,H,7]*/, int H,
+                            double* min_dist /*[n,3]*/, uint8_t* is_safe /*[n]*/) {
+  RefBatch* b = static_cast<RefBatch*>(h);
+  SafetyShield& s = *b->env[0];
+  const int J = b->J, K = b->K;
+  for (int i = 0; i < n; ++i) {
+    const double* p = base_pose + static_cast<size_t>(i) * 6;
+    s.robot_reach_->reset(p[0], p[1], p[2], p[3], p[4], p[5]);
+    std::vector<double> q1(q_start + static_cast<size_t>(i) * J, q_start + static_cast<size_t>(i + 1) * J);
+    std::vector<double> q2(q_goal + static_cast<size_t>(i) * J, q_goal + static_cast<size_t>(i + 1) * J);
+    std::vector<double> al(alpha_i + static_cast<size_t>(i) * J, alpha_i + static_cast<size_t>(i + 1) * J);
+    Motion m1(0.0, q1), m2(0.0, q2);
+    std::vector<reach_lib::Capsule> rc = s.robot_reach_->reach(m1, m2, s_diff[i], al);
+    for (int k = 0; k < K; ++k) {
+      const double* a = kp_pos + (static_cast<size_t>(i) * K + k) * 3;
+      const double* v = kp_vel + (static_cast<size_t>(i) * K + k) * 3;
+      s.human_reach_->joint_pos_[k] = reach_lib::Point(a[0], a[1], a[2]);
+      s.human_reach_->joint_vel_[k] = reach_lib::Point(v[0], v[1], v[2]);
+    }
+    s.human_reach_->last_meas_timestep_ = 0.0;
+    s.human_reach_->humanReachabilityAnalysis(0.0, t_reach[i]);
+    std::vector<std::vector<reach_lib::Capsule>> hc = s.human_reach_->getAllCapsules();
+    if (is_safe) is_safe[i] = s.verify_->verify_human_reach(rc, hc) ? 1 : 0;
+    for (int j = 0; j < J && robot; ++j) put_capsule(rc[j], robot + (static_cast<size_t>(i) * J + j) * 7);
+    int k = 0;
+    for (size_t m = 0; m < hc.size(); ++m) {
+      double md = INFINITY;
+      for (auto& c : hc[m]) {
+        if (human && k < H) put_capsule(c, human + (static_cast<size_t>(i) * H + k) * 7);
+        ++k;
+        for (auto& r : rc) md = std::min(md, reach_lib::intersections::capsule_capsule_dist(r, c));
+      }
+      if (min_dist && m < 3) min_dist[static_cast<size_t>(i) * 3 + m] = md;
+    }
+  }
 }
 
 // roots() + getSmallestPositiveNonComplexRoot (LTP/include/long_term_planner/roots.h:22-50)
