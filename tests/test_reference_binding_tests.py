@@ -3,7 +3,7 @@ test_safety_shield.py), against the top-level `safety_shield_py` package of this
 
 They `from safety_shield_py import ...` and find their YAML files through "<their dir>/../../config". Where /root/reference
 is mounted they are collected from there; on the GPU box from the unmodified copies oracle/Makefile stages under
-oracle/_ref/ss (git-ignored, never part of this repository's history). Each file runs in its own pytest process with this
+oracle/_ref/safety_shield (git-ignored, never part of this repository's history). Each file runs in its own pytest process with this
 repository root on PYTHONPATH, exactly like a user of the reference would run them after switching modules."""
 import os
 import subprocess
@@ -14,14 +14,14 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _SS = "human_robot_gym/controllers/failsafe_controller/sara-shield/safety_shield"
 _CANDIDATES = [os.path.join("/root/reference", _SS, "tests", "bindings"),
-               os.path.join(ROOT, "oracle", "_ref", "ss", "tests", "bindings")]
+               os.path.join(ROOT, "oracle", "_ref", "safety_shield", "tests", "bindings")]
 
 
 def _bindings_dir():
     for d in _CANDIDATES:
         if os.path.isfile(os.path.join(d, "test_safety_shield.py")):
             return d
-    pytest.skip("reference binding tests not available (neither /root/reference nor oracle/_ref/ss)")
+    pytest.skip("reference binding tests not available (neither /root/reference nor oracle/_ref/safety_shield)")
 
 
 def _run(name):
