@@ -47,6 +47,12 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--seed", type=int, default=1003)
     ap.add_argument("--shield", default="ssm", choices=["ssm", "pfl"], help="ShieldType of every env (config 4 runs both)")
+    ap.add_argument("--strong-total", type=int, default=65536,
+                    help="N>1 only: also run BASELINE config 3 - this many shields IN TOTAL, sharded env-wise over the GPUs "
+                         "(0 = skip); reported as `strong_65536` beside the weak-scaling headline")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="strong: --envs is the TOTAL number of shields, sharded over the GPUs (the headline then is the "
+                         "strong-scaling figure)")
     return ap.parse_args()
 
 
@@ -335,6 +341,138 @@ def bench_human_fk(n, dev, launches=50):
     return out
 
 
+def time_shield(args, sc, files, names, dev, rank, world, n, W, S, seed, with_e2e=True):
+    """W + S device-resident ticks of a fresh batch of n shields on this rank (CUDA events, barrier on both sides, max over
+    ranks), then the double-buffered host-buffer form. Used for the strong-scaling leg (BASELINE config 3)."""
+    import torch
+    import torch.distributed as dist
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    J = sc.robot.nb_joints
+    scen, kp_h, goals_h, masks_h = make_inputs(args, sc, n, seed, names)
+    shield = BatchedSafetyShield(n, SAMPLE_TIME, *files, init_qpos=scen.init_q, device=dev, ltt_capacity=args.ltt_capacity,
+                                 config=sc, shield_type=2 if args.shield == "pfl" else 1)
+    kp_d, goals_d, masks_d = (torch.from_numpy(x).to(dev) for x in (kp_h, goals_h, masks_h))
+    total = 2 * (W + S) + 16
+    t_d = (torch.arange(total, dtype=torch.float64, device=dev) * SAMPLE_TIME)[:, None].expand(total, n).contiguous()
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    def tick(k):
+        shield.tick_device(kp_d[ring_index(k, args.ring)], t_d[k], masks_d[k % GOAL_PERIOD],
+                           goals_d[(k // GOAL_PERIOD) % goals_d.shape[0]])
+
+    k = 0
+    for _ in range(W):
+        tick(k)
+        k += 1
+    sync_all()
+    shield.stats(clear=True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(S):
+        tick(k)
+        k += 1
+    e1.record()
+    sync_all()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    n_all = torch.tensor([n], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(n_all, op=dist.ReduceOp.SUM)
+    ms, n_all = float(ms.item()), int(n_all.item())
+    st = shield.check_health()
+    out = {"envs_total": n_all, "envs_per_gpu": n, "value": n_all * S / (ms / 1e3), "ms_per_step": ms / S,
+           "n_replan_local": st["n_replan"]}
+    if with_e2e:
+        ms_e, k, _ = time_e2e_piped(shield, kp_h, goals_h, masks_h, n, J, dev, max(3, min(W, 10)), S, world, k, sync_all)
+        out["e2e"] = {"value": n_all * S / (ms_e / 1e3), "ms_per_step": ms_e / S}
+    shield.close()
+    return out
+
+
+def time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, W, S, world, k0, sync_all, plain=False):
+    """S ticks through the host-buffer C ABI (pinned host inputs in, pinned host setpoints out, one stream sync per tick):
+    double-buffered upload of tick k+1 during tick k (plain=True: hrg_shield_tick_host, copy -> kernels -> copy).
+    Returns (ms over ranks' max, next tick index, launches)."""
+    import torch
+    import torch.distributed as dist
+    pin = dict(pin_memory=True)
+    kp_p, goals_p, masks_p = (torch.from_numpy(x).pin_memory() for x in (kp_h, goals_h, masks_h))
+    t_p = [torch.zeros(N, dtype=torch.float64, **pin) for _ in range(2)]
+    q_p, dq_p, ddq_p = (torch.zeros(N, J, dtype=torch.float64, **pin) for _ in range(3))
+    fl_p = torch.zeros(N, dtype=torch.uint8, **pin)
+    R = kp_h.shape[0]
+    copy_stream = torch.cuda.Stream(device=dev)
+    main = torch.cuda.current_stream(dev)
+
+    def upload(kk):
+        slot = kk & 1
+        t_p[slot].fill_(kk * SAMPLE_TIME)
+        shield.upload_inputs(slot, kp_p[ring_index(kk, R)], t_p[slot], masks_p[kk % GOAL_PERIOD],
+                             goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], copy_stream)
+
+    def tick_piped(kk):
+        upload(kk + 1)                       # next tick's inputs travel while this tick computes
+        shield.tick_staged(kk & 1, q_p, dq_p, ddq_p, fl_p)
+        main.synchronize()                   # the caller consumes the setpoints before the next tick
+
+    def tick_plain(kk):
+        t_p[0].fill_(kk * SAMPLE_TIME)
+        shield.tick_host(kp_p[ring_index(kk, R)], t_p[0], masks_p[kk % GOAL_PERIOD],
+                         goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], q_p, dq_p, ddq_p, fl_p)
+        main.synchronize()
+
+    fn = tick_plain if plain else tick_piped
+    kk = k0
+    if not plain:
+        upload(kk)
+    for _ in range(W):
+        fn(kk)
+        kk += 1
+    sync_all()
+    copy_stream.synchronize()
+    l0 = shield.launch_count()
+    t0 = time.perf_counter()
+    for _ in range(S):
+        fn(kk)
+        kk += 1
+    sync_all()
+    ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    copy_stream.synchronize()
+    time_e2e_piped.checksum = float(q_p.sum().item()) + float(fl_p.sum().item())  # the result was really read back
+    return float(ms.item()), kk + 1, shield.launch_count() - l0
+
+
+def h2d_copy_rate(dev, world, nbytes, reps=20):
+    """GB/s of one pinned host -> device copy of `nbytes` on this rank while every other rank does the same (no kernels):
+    what the box's PCIe / host memory gives the e2e leg. Min over ranks (the slowest rank sets the tick)."""
+    import torch
+    import torch.distributed as dist
+    src = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    dst = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    for _ in range(3):
+        dst.copy_(src, non_blocking=True)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        dst.copy_(src, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    rate = torch.tensor([nbytes * reps / (e0.elapsed_time(e1) / 1e3) / 1e9], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(rate, op=dist.ReduceOp.MIN)
+    return float(rate.item())
+
+
 def main():
     args = parse_args()
     from human_robot_gym_b200.config import ShieldConfig
@@ -359,7 +497,13 @@ def main():
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries exactly one JSON line
         dist.init_process_group("nccl", device_id=dev)
-    N, J, K = args.envs, sc.robot.nb_joints, sc.human.n_keypoints
+    from human_robot_gym_b200.sharded import shard_range
+    J, K = sc.robot.nb_joints, sc.human.n_keypoints
+    if args.scaling == "strong":   # --envs shields in total, rank r owns the contiguous block shard_range(envs, r, world)
+        lo, hi = shard_range(args.envs, rank, world)
+        N, n_total = hi - lo, args.envs
+    else:                          # --envs shields on every GPU
+        N, n_total = args.envs, args.envs * world
     W, S = args.warmup, args.steps
     scen, kp_h, goals_h, masks_h = make_inputs(args, sc, N, args.seed + rank, names)
     shield = BatchedSafetyShield(N, SAMPLE_TIME, *files, init_qpos=scen.init_q, device=dev,
@@ -413,8 +557,17 @@ def main():
     for _ in range(S):
         tick(k)
         k += 1
-    kms, ksteps = shield.profile_read()
+    kdetail, ksteps = shield.profile_read_kernels()
     shield.profile(0)
+    grp = {"k_pre_plan": ("k_measure", "k_pre", "k_plan"),
+           "k_replan": ("k_replan_plan", "k_replan_deep", "k_replan_sample", "k_pfl_ltt", "k_replan_tail"),
+           "k_reach_verify": ("k_reach_verify_p0", "k_verify_stage_vel", "k_verify_stage_acc", "k_reach_verify_p1"),
+           "k_select": ("k_select",)}
+    kms = {g: sum(kdetail[x] for x in members) for g, members in grp.items()}
+    fp64_peak = None
+    if rank == 0:
+        from human_robot_gym_b200 import cabi as _cabi
+        fp64_peak = _cabi.microbench_fp64(local_rank)
 
     # ---- end to end through the C ABI with HOST buffers -----------------------------------------------------------
     # The call a vectorised env makes every tick: pinned host keypoints/goals in, pinned host setpoints out, and a stream
@@ -423,61 +576,21 @@ def main():
     # the next keypoints exist early. `unpipelined` is the plain hrg_shield_tick_host (copy -> kernels -> copy).
     e2e = None
     if not args.no_e2e:
-        pin = dict(pin_memory=True)
-        kp_p = torch.from_numpy(kp_h).pin_memory()
-        goals_p = torch.from_numpy(goals_h).pin_memory()
-        masks_p = torch.from_numpy(masks_h).pin_memory()
-        t_p = [torch.zeros(N, dtype=torch.float64, **pin) for _ in range(2)]
-        q_p, dq_p, ddq_p = (torch.zeros(N, J, dtype=torch.float64, **pin) for _ in range(3))
-        fl_p = torch.zeros(N, dtype=torch.uint8, **pin)
-        copy_stream = torch.cuda.Stream(device=dev)
-        main = torch.cuda.current_stream(dev)
-
-        def upload(kk):
-            slot = kk & 1
-            t_p[slot].fill_(kk * SAMPLE_TIME)
-            shield.upload_inputs(slot, kp_p[ring_index(kk, args.ring)], t_p[slot], masks_p[kk % GOAL_PERIOD],
-                                 goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], copy_stream)
-
-        def tick_piped(kk):
-            upload(kk + 1)                       # next tick's inputs travel while this tick computes
-            shield.tick_staged(kk & 1, q_p, dq_p, ddq_p, fl_p)
-            main.synchronize()                   # the caller consumes the setpoints before the next tick
-
-        def tick_plain(kk):
-            t_p[0].fill_(kk * SAMPLE_TIME)
-            shield.tick_host(kp_p[ring_index(kk, args.ring)], t_p[0], masks_p[kk % GOAL_PERIOD],
-                             goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], q_p, dq_p, ddq_p, fl_p)
-            main.synchronize()
-
-        def timed(fn, kk):
-            for _ in range(max(3, min(W, 10))):
-                fn(kk)
-                kk += 1
-            sync_all()
-            copy_stream.synchronize()
-            l0 = shield.launch_count()
-            t0 = time.perf_counter()
-            for _ in range(S):
-                fn(kk)
-                kk += 1
-            sync_all()
-            ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
-            if world > 1:
-                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-            return float(ms.item()), kk, shield.launch_count() - l0
-
-        ms_plain, k, _ = timed(tick_plain, k)
-        upload(k)
-        ms_piped, k, l_e = timed(tick_piped, k)
-        copy_stream.synchronize()
-        checksum = float(q_p.sum().item()) + float(fl_p.sum().item())  # the result was really read back
-        e2e = {"value": N * world * S / (ms_piped / 1e3), "unit": METRIC,
-               "h2d_bytes_per_step": N * (K * 3 * 8 + 8 + 1 + J * 8), "d2h_bytes_per_step": N * (3 * J * 8 + 1),
+        Wx = max(3, min(W, 10))
+        ms_plain, k, _ = time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, Wx, S, world, k, sync_all, plain=True)
+        ms_piped, k, l_e = time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, Wx, S, world, k, sync_all)
+        h2d = N * (K * 3 * 8 + 8 + 1 + J * 8)
+        copy_gbs = h2d_copy_rate(dev, world, h2d)
+        e2e = {"value": n_total * S / (ms_piped / 1e3), "unit": METRIC,
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": N * (3 * J * 8 + 1),
                "ms_per_step": ms_piped / S, "gpu_launches": l_e,
                "mode": "double-buffered upload of tick k+1 during tick k; stream sync per tick; host wall clock",
-               "unpipelined": {"value": N * world * S / (ms_plain / 1e3), "ms_per_step": ms_plain / S},
-               "checksum": checksum}
+               "unpipelined": {"value": n_total * S / (ms_plain / 1e3), "ms_per_step": ms_plain / S},
+               "h2d_copy_alone": {"GBps_per_rank_min": copy_gbs, "ranks_copying": world,
+                                  "ms_for_one_tick_of_inputs": h2d / copy_gbs / 1e6,
+                                  "note": "one pinned host->device copy of a tick's inputs per rank, all ranks at once, no "
+                                          "kernels: the floor the box's PCIe / host memory puts under ms_per_step"},
+               "checksum": time_e2e_piped.checksum}
 
     # ---- end to end with the RECORDED human (the reference's own workload: the human is a clip replay, BASELINE config 1) -----
     # The keypoints never exist on the host: per tick the host sends the clock and the goals (pinned -> device), the device
@@ -496,6 +609,13 @@ def main():
             human_fk = bench_human_fk(N, dev)
         except Exception as ex:  # reported, never hidden: the main line does not depend on it
             human_fk = {"error": repr(ex)}
+
+    # ---- BASELINE config 3 ("65,536 envs sharded env-wise over 8 B200"): the same metric with the batch split over the ranks
+    strong = None
+    if world > 1 and args.scaling == "weak" and args.strong_total > 0:
+        lo, hi = shard_range(args.strong_total, rank, world)
+        strong = time_shield(args, sc, files, names, dev, rank, world, hi - lo, W, S, args.seed + 101 * (rank + 1),
+                             with_e2e=not args.no_e2e)
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -527,12 +647,12 @@ def main():
                            if kms[kk] > 0 else 0.0} for kk in kms}
         b_tick = 48 * K + 770 + 136 * J
         b_step = b_tick + (32 * J * L_mean + 16 * J) / GOAL_PERIOD
-        value = N * world * S / (ms_total / 1e3)
+        value = n_total * S / (ms_total / 1e3)
         line = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": S, "warmup": W,
-            "ms_per_step": ms_total / S, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_total / S, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args, sc), "envs_total": N * world, "sample_time": SAMPLE_TIME,
+            "config": {"workload": workload_name(args, sc), "envs_total": n_total, "envs_per_gpu": N, "sample_time": SAMPLE_TIME,
                        "l2_note": f"per-step working set {N * b_tick / 1e6:.0f} MB of state + {N * K * 24 / 1e6:.0f} MB "
                                   "of new keypoints exceeds the 126 MB L2; no explicit flush",
                        "ltt_capacity": args.ltt_capacity, "mean_ltt_len": L_mean},
@@ -544,6 +664,8 @@ def main():
                                  "24 / 23 / 14 / 15 % busy in opt / scale / deep / sample (ncu, "
                                  "profiles/r01l_replan_ncu_summary.md)"},
             "kernel_ms_per_step": {kk: v / max(ksteps, 1) for kk, v in kms.items()},
+            "kernel_ms_per_launch": {kk: v / max(ksteps, 1) for kk, v in kdetail.items() if v > 0},
+            "fp64_peak_measured": fp64_peak,
             "roofline_per_kernel": per_kernel,
             "roofline_tick": {"algorithmic_bytes_per_step": b_step, "achieved": b_step * N / (ms_total / S / 1e3) / 1e9,
                               "unit": "GB/s", "frac": b_step * N / (ms_total / S / 1e3) / 1e9 / peak},
@@ -552,6 +674,11 @@ def main():
                              "n_near_threshold": counts[7], "min_dist": gs["min_dist"]},
             "clocks": clk, "gpu_launches": int(launches),
         }
+        if strong:
+            strong["note"] = ("BASELINE config 3: this many shields IN TOTAL, sharded env-wise; the per-GPU batch shrinks with N, so "
+                              "the tick approaches the latency floor of its dependent kernel chain - strong-scaling efficiency "
+                              "is value / (n_gpus x the 1-GPU value at 65 536 envs)")
+            line[f"strong_{args.strong_total}"] = strong
         if e2e:
             line["e2e"] = e2e
         if e2e_rec:

@@ -247,6 +247,14 @@ class BatchedSafetyShield:
         cabi.check(self.lib.hrg_shield_profile_read(self._h, C.addressof(ms), C.addressof(n)), "hrg_shield_profile_read")
         return dict(zip(("k_pre_plan", "k_replan", "k_reach_verify", "k_select"), list(ms))), n.value
 
+    def profile_read_kernels(self):
+        """({kernel: total ms} for every launch slot of the tick (cabi.PROF_SLOTS), steps) since profile(max_steps)."""
+        ms = (C.c_double * len(cabi.PROF_SLOTS))()
+        n = C.c_int(0)
+        cabi.check(self.lib.hrg_shield_profile_read_kernels(self._h, C.addressof(ms), C.addressof(n)),
+                   "hrg_shield_profile_read_kernels")
+        return dict(zip(cabi.PROF_SLOTS, list(ms))), n.value
+
     def launch_count(self) -> int:
         return int(self.lib.hrg_shield_launch_count(self._h))
 

@@ -18,6 +18,10 @@ OK, EINVAL, ENODEVICE, ECUDA, ENOMEM = 0, -1, -2, -3, -4
 SHIELD_OFF, SHIELD_SSM, SHIELD_PFL = 0, 1, 2
 ST_REPLANNED, ST_REPLAN_FAILED, ST_NOT_PLANNABLE, ST_JOINT_LIMIT, ST_LTT_TRUNCATED, ST_NEAR_THRESHOLD = 1, 2, 4, 8, 16, 32
 
+PROF_SLOTS = ("k_measure", "k_pre", "k_plan", "k_replan_plan", "_spare", "k_replan_deep", "k_replan_sample",
+              "k_pfl_ltt", "k_replan_tail", "k_reach_verify_p0", "k_verify_stage_vel", "k_verify_stage_acc",
+              "k_reach_verify_p1", "k_select")  # HRG_PROF_* of include/hrg_shield.h
+
 _D = C.c_double
 _I = C.c_int32
 
@@ -121,6 +125,7 @@ SYMBOLS = {
     "hrg_shield_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _vp]),
     "hrg_shield_profile": (C.c_int, [C.c_void_p, C.c_int]),
     "hrg_shield_profile_read": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "hrg_shield_profile_read_kernels": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "hrg_shield_num_envs": (C.c_int, [C.c_void_p]),
     "hrg_shield_num_human_capsules": (C.c_int, [C.c_void_p]),
     "hrg_shield_launch_count": (C.c_int64, [C.c_void_p]),
@@ -134,6 +139,7 @@ SYMBOLS = {
     "hrg_human_keypoints": (C.c_int, [C.c_void_p, C.c_void_p, _dp, _i32p, _i32p, _vp]),
     "hrg_shield_tick_replay_host": (C.c_int, [C.c_void_p, C.c_void_p] + [C.c_void_p] * 8 + [_vp]),
     "hrg_human_launch_count": (C.c_int64, [C.c_void_p]),
+    "hrg_microbench_fp64": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "hrg_stage_capsule_dist": (C.c_int, [C.c_int, _dp, _dp, _dp, _vp]),
     "hrg_stage_plan_safety_shield": (C.c_int, [C.c_double, C.c_int, _dp, _u8p, _dp, _dp, _vp]),
     "hrg_stage_ltp_plan": (C.c_int, [C.POINTER(HrgConfig), C.c_int, _dp, _dp, _dp, _dp, _dp, _i32p, C.c_int, _vp]),
@@ -171,6 +177,17 @@ def ltt_capacity_bound(sc: ShieldConfig) -> int:
     if n < 0:
         check(n, "hrg_ltt_capacity_bound")
     return int(n)
+
+
+def microbench_fp64(device: int = 0, iters: int = 4096) -> dict:
+    """Measured register-resident FP64 peaks of `device`: {"dfma"|"dmul_dadd"|"dadd": {"gflops", "ginst", "ms"}}."""
+    out = {}
+    for mode, name in enumerate(("dfma", "dmul_dadd", "dadd")):
+        g, i, ms = C.c_double(0), C.c_double(0), C.c_double(0)
+        check(load_library().hrg_microbench_fp64(int(device), mode, int(iters), C.addressof(g), C.addressof(i),
+                                                 C.addressof(ms)), "hrg_microbench_fp64")
+        out[name] = {"gflops": g.value, "ginst": i.value, "ms": ms.value}
+    return out
 
 
 def check(rc: int, what: str = ""):

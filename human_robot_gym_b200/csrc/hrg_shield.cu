@@ -12,6 +12,7 @@
 #include "kernels_reach.cuh"
 #include "kernels_tick.cuh"
 #include "kernels_controller.cuh"
+#include "microbench.cuh"
 
 using namespace hrg;
 
@@ -82,11 +83,12 @@ struct HrgShield {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_meas = nullptr;
   bool overlap = true;
+  bool debug_sync = false;
   bool cascade = true;  // verification cascade for pass 0 (HRG_NO_CASCADE=1 or stored capsules: full kernel)
-  int replan_blocks_per_sm = 12;  // resident 64-thread replan blocks per SM while overlapped with k_reach_verify pass 0 (measured best)
-  // optional per-kernel timing of hrg_shield_step (bench.py's roofline leg): 5 boundary events per step
+  // optional per-kernel timing of the tick (bench.py's roofline leg): one event after every launch of a step
   bool prof = false;
   std::vector<cudaEvent_t> ev;
+  std::vector<int> ev_id;  // HRG_PROF_* slot of the kernel that ENDS at this event; -1 = start of a step
   size_t ev_used = 0;
 
   template <class T>
@@ -234,9 +236,9 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
     int lo = 0, hi = 0;  // the replan chain is the critical path of the tick: highest priority for its blocks
     cudaDeviceGetStreamPriorityRange(&lo, &hi);
     ce = cudaStreamCreateWithPriority(&h->side, cudaStreamNonBlocking, hi);
-    if (const char* v = getenv("HRG_REPLAN_BLOCKS_PER_SM")) h->replan_blocks_per_sm = atoi(v) > 0 ? atoi(v) : 12;
     if (const char* v = getenv("HRG_NO_OVERLAP")) h->overlap = !(atoi(v) > 0);
     if (const char* v = getenv("HRG_NO_CASCADE")) h->cascade = !(atoi(v) > 0);
+    if (const char* v = getenv("HRG_DEBUG_SYNC")) h->debug_sync = atoi(v) > 0;
   }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
@@ -375,19 +377,26 @@ int hrg_shield_new_goal(HrgShield* s, const uint8_t* env_mask, const double* goa
 
 // reach + verify of the envs that do not replan this tick: the Pos-model tile kernel plus the two cascade stages over its
 // survivors, or the full kernel when capsules / all distances are stored for the getters.
-static void verify_pass0(HrgShield* s, cudaStream_t st, size_t smem) {
+extern "C++" {
+template <class Mark>
+static void verify_pass0(HrgShield* s, cudaStream_t st, size_t smem, Mark&& mark) {
   const int N = s->S.N, J = s->S.J;
   if (s->cascade && !s->S.human_caps) {
     size_t stage_smem = (size_t)kHumDoubles * s->cfg.n_bodies * kTileEnvs * sizeof(double);
     if (stage_smem < (size_t)J * kTileEnvs * sizeof(double)) stage_smem = (size_t)J * kTileEnvs * sizeof(double);
     k_reach_verify<1, true><<<tile_grid(N), 32 * J, smem, st>>>(s->S, 0);
+    mark(HRG_PROF_VERIFY_P0);
     k_verify_stage<1><<<tile_grid(N), 32 * J, stage_smem, st>>>(s->S);
+    mark(HRG_PROF_STAGE_VEL);
     k_verify_stage<2><<<tile_grid(N), 32 * J, stage_smem, st>>>(s->S);
+    mark(HRG_PROF_STAGE_ACC);
     s->launches += 2;
   } else {
     k_reach_verify<1><<<tile_grid(N), 32 * J, smem, st>>>(s->S, 0);
+    mark(HRG_PROF_VERIFY_P0);
   }
 }
+}  // extern "C++"
 
 // One tick's launches. `kp` != NULL folds humanMeasurement(kp, t) into the tick: the keypoints are only read by reach +
 // verify (and last_meas by the path planning), so k_measure runs on the main stream next to the start of the replan chain
@@ -398,68 +407,90 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
   CK(cudaSetDevice(s->device));  // a handle on cuda:1 may be driven while another device is current
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int N = s->S.N;
-  const bool prof = s->prof && s->ev_used + 5 <= s->ev.size();
-  cudaEvent_t* ev = prof ? &s->ev[s->ev_used] : nullptr;
-  if (prof) {
-    s->ev_used += 5;
-    cudaEventRecord(ev[0], st);
-  }
+  const bool prof = s->prof && s->ev_used + HRG_PROF_SLOTS + 1 <= s->ev.size();
+  // profiling: everything on `st`, one event after each launch (the chain is then serialised, so the events are clean)
+  auto mark = [&](int id) {
+    if (s->debug_sync) {  // HRG_DEBUG_SYNC=1: wait for every kernel and name it on stderr (finds a kernel that hangs or faults)
+      const cudaError_t e1 = cudaStreamSynchronize(s->side), e2 = cudaStreamSynchronize(st);
+      fprintf(stderr, "[hrg] after launch slot %d: %s / %s\n", id, cudaGetErrorString(e1), cudaGetErrorString(e2));
+      fflush(stderr);
+    }
+    if (!prof) return;
+    s->ev_id[s->ev_used] = id;
+    cudaEventRecord(s->ev[s->ev_used++], st);
+  };
+  mark(-1);
   const bool fork = s->overlap && !prof;
   if (kp && !fork) {
     k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
     s->launches++;
+    mark(HRG_PROF_MEASURE);
   }
   k_pre<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, goal_mask, goal_q);
-  if (!fork) k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
-  if (prof) cudaEventRecord(ev[1], st);
+  mark(HRG_PROF_PRE);
+  if (!fork) {
+    k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
+    mark(HRG_PROF_PLAN);
+  }
   cudaStream_t rs = fork ? s->side : st;
   if (fork) {
     // replan || reach + verify of the envs that do not replan, then the replanned envs
     CK(cudaEventRecord(s->ev_fork, st));
     CK(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
   }
+  // from here to the join an early return would leave the side stream un-joined for the next tick: collect the first
+  // error instead and join in any case
+  cudaError_t err = cudaSuccess;
+  auto keep = [&](cudaError_t e) {
+    if (err == cudaSuccess && e != cudaSuccess) err = e;
+  };
   {
-    // the replan list length is only known on the device: grids cover the worst case (every env replans) and surplus
-    // groups / warps leave at once; the planning kernels fetch their tasks from counters, their grid only bounds residency
-    int sgrid = grid_for(N * s->S.J, kReplanBlock / 32);
-    const int per_sm = fork ? s->replan_blocks_per_sm : HRG_REPLAN_MINBLOCKS;
-    if (sgrid > s->sm_count * per_sm) sgrid = s->sm_count * per_sm;
-    k_replan_opt<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
-    k_replan_scale<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
-    k_replan_deep<<<sgrid, kReplanBlock, 0, rs>>>(s->S);
-    if (fork && kp) {
-      // lane 0's tail of k_replan_sample reads last_meas: k_measure (main stream) must be through by then
-      k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
-      s->launches++;
-      CK(cudaEventRecord(s->ev_meas, st));
-      CK(cudaStreamWaitEvent(s->side, s->ev_meas, 0));
-    }
+    // the replan list length is only known on the device: the kernels fetch their work from device counters, their grids
+    // only bound residency (one warp per block, so that the few hundred busy warps spread over all schedulers)
+    const int J = s->S.J, E = 32 / J;
+    const int cap = s->sm_count * 16;
+    int g_env = grid_for(N, E);
+    if (g_env > cap) g_env = cap;
+    int g_deep = grid_for(N * J * 6, 32);
+    if (g_deep > cap) g_deep = cap;
+    k_replan_plan<<<g_env, kReplanBlock, 0, rs>>>(s->S);
+    mark(HRG_PROF_PLAN_LTT);
+    k_replan_deep<<<g_deep, kReplanBlock, 0, rs>>>(s->S);
+    mark(HRG_PROF_DEEP);
+    k_replan_sample<<<g_env, kReplanBlock, 0, rs>>>(s->S);
+    mark(HRG_PROF_SAMPLE);
     if (s->pfl) {
-      k_replan_sample<true><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t, 1);
       int pgrid = s->sm_count * 8;
       if (pgrid > N) pgrid = N;
       k_pfl_ltt<<<pgrid, kPflBlock, 0, rs>>>(s->S);
-      k_replan_sample<true><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t, 2);
-      s->launches += 2;
-    } else {
-      k_replan_sample<false><<<grid_for(N, 128 / 32), 128, 0, rs>>>(s->S, t, 0);
+      mark(HRG_PROF_PFL);
+      s->launches++;
     }
+    if (fork && kp) {
+      // k_replan_tail (plan_env) reads last_meas: k_measure (main stream) must be through by then
+      k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
+      s->launches++;
+      keep(cudaEventRecord(s->ev_meas, st));
+      keep(cudaStreamWaitEvent(s->side, s->ev_meas, 0));
+    }
+    k_replan_tail<<<grid_for(N, 128), 128, 0, rs>>>(s->S, t);
+    mark(HRG_PROF_TAIL);
   }
   if (fork) {
-    CK(cudaEventRecord(s->ev_join, s->side));
+    keep(cudaEventRecord(s->ev_join, s->side));
     k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
-    verify_pass0(s, st, s->reach_smem_p0);
-    CK(cudaStreamWaitEvent(st, s->ev_join, 0));
+    verify_pass0(s, st, s->reach_smem_p0, mark);
+    keep(cudaStreamWaitEvent(st, s->ev_join, 0));
   } else {
-    if (prof) cudaEventRecord(ev[2], st);
-    verify_pass0(s, st, s->reach_smem);
+    verify_pass0(s, st, s->reach_smem, mark);
   }
   k_reach_verify<2><<<tile_grid(N), 32 * s->S.J * 2, s->reach_smem, st>>>(s->S, 1);
-  if (prof) cudaEventRecord(ev[3], st);
+  mark(HRG_PROF_VERIFY_P1);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
-  if (prof) cudaEventRecord(ev[4], st);
+  mark(HRG_PROF_SELECT);
   s->launches += 9;
-  CK(cudaGetLastError());
+  keep(cudaGetLastError());
+  if (err != cudaSuccess) return fail(HRG_ECUDA, "hrg_shield_step: launch failed", err);
   return HRG_OK;
 }
 

@@ -226,30 +226,90 @@ int hrg_shield_set_ltt_batch(HrgShield* s, int n_traj, const int32_t* env_index,
 int hrg_shield_profile(HrgShield* s, int max_steps) {
   if (!s || max_steps < 0) return fail(HRG_EINVAL, "hrg_shield_profile: bad argument");
   CK(cudaSetDevice(s->device));
-  while (s->ev.size() < (size_t)max_steps * 5) {
+  while (s->ev.size() < (size_t)max_steps * (HRG_PROF_SLOTS + 1)) {
     cudaEvent_t e;
     CK(cudaEventCreate(&e));
     s->ev.push_back(e);
   }
+  s->ev_id.resize(s->ev.size(), -1);
   s->prof = max_steps > 0;
+  s->ev_used = 0;
+  return HRG_OK;
+}
+
+int hrg_shield_profile_read_kernels(HrgShield* s, double* ms_host, int* steps_host) {
+  if (!s || !ms_host || !steps_host) return fail(HRG_EINVAL, "hrg_shield_profile_read_kernels: NULL argument");
+  CK(cudaSetDevice(s->device));
+  for (int k = 0; k < HRG_PROF_SLOTS; ++k) ms_host[k] = 0.0;
+  int steps = 0;
+  if (s->ev_used) CK(cudaEventSynchronize(s->ev[s->ev_used - 1]));
+  for (size_t i = 0; i < s->ev_used; ++i) {
+    const int id = s->ev_id[i];
+    if (id < 0) {
+      ++steps;
+      continue;
+    }
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, s->ev[i - 1], s->ev[i]));
+    if (id < HRG_PROF_SLOTS) ms_host[id] += ms;
+  }
+  *steps_host = steps;
   s->ev_used = 0;
   return HRG_OK;
 }
 
 int hrg_shield_profile_read(HrgShield* s, double* ms_host, int* steps_host) {
   if (!s || !ms_host || !steps_host) return fail(HRG_EINVAL, "hrg_shield_profile_read: NULL argument");
-  CK(cudaSetDevice(s->device));
-  for (int k = 0; k < 4; ++k) ms_host[k] = 0.0;
-  const size_t steps = s->ev_used / 5;
-  if (steps) CK(cudaEventSynchronize(s->ev[s->ev_used - 1]));
-  for (size_t i = 0; i < steps; ++i)
-    for (int k = 0; k < 4; ++k) {
-      float ms = 0.f;
-      CK(cudaEventElapsedTime(&ms, s->ev[i * 5 + k], s->ev[i * 5 + k + 1]));
-      ms_host[k] += ms;
-    }
-  *steps_host = (int)steps;
-  s->ev_used = 0;
+  double k[HRG_PROF_SLOTS];
+  const int rc = hrg_shield_profile_read_kernels(s, k, steps_host);
+  if (rc) return rc;
+  ms_host[0] = k[HRG_PROF_MEASURE] + k[HRG_PROF_PRE] + k[HRG_PROF_PLAN];
+  ms_host[1] = k[HRG_PROF_PLAN_LTT] + k[HRG_PROF_DEEP] + k[HRG_PROF_SAMPLE] + k[HRG_PROF_PFL] + k[HRG_PROF_TAIL];
+  ms_host[2] = k[HRG_PROF_VERIFY_P0] + k[HRG_PROF_STAGE_VEL] + k[HRG_PROF_STAGE_ACC] + k[HRG_PROF_VERIFY_P1];
+  ms_host[3] = k[HRG_PROF_SELECT];
+  return HRG_OK;
+}
+
+// ---- FP64 peak microbenchmark (roofline denominator of the FP64-bound kernels) -----------------------------------------
+int hrg_microbench_fp64(int device, int mode, int iters, double* gflops_host, double* ginst_host, double* ms_host) {
+  if (mode < 0 || mode > 2 || iters < 1 || !gflops_host) return fail(HRG_EINVAL, "hrg_microbench_fp64: bad argument");
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev < 1) return fail(HRG_ENODEVICE, "no CUDA device (this library has no CPU fallback)", ce);
+  if (device < 0 || device >= ndev) return fail(HRG_EINVAL, "device index out of range");
+  CK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  const int block = 256, grid = prop.multiProcessorCount * 8;  // 2048 threads per SM: every scheduler has 16 warps to pick from
+  double* out = nullptr;
+  CK(cudaMalloc(&out, (size_t)grid * block * sizeof(double)));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {  // first launch = warm-up, then best of three
+    cudaEventRecord(e0, 0);
+    if (mode == 0) hrg::k_fp64_peak<0><<<grid, block>>>(out, iters, 1.0000001, 1e-9);
+    if (mode == 1) hrg::k_fp64_peak<1><<<grid, block>>>(out, iters, 1.0000001, 1e-9);
+    if (mode == 2) hrg::k_fp64_peak<2><<<grid, block>>>(out, iters, 1.0000001, 1e-9);
+    cudaEventRecord(e1, 0);
+    ce = cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (rep > 0 && ms < best) best = ms;
+    if (ce != cudaSuccess) break;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  if (ce != cudaSuccess) return fail(HRG_ECUDA, "hrg_microbench_fp64", ce);
+  // per thread and iteration: 4 x 8 chain steps, each one DFMA (2 flop) / one DMUL + one DADD (2 flop) / one DADD (1 flop)
+  const double steps = (double)grid * block * (double)iters * 32.0;
+  const double inst = steps * (mode == 1 ? 2.0 : 1.0);
+  const double flop = steps * (mode == 2 ? 1.0 : 2.0);
+  *gflops_host = flop / (best * 1e-3) / 1e9;
+  if (ginst_host) *ginst_host = inst / (best * 1e-3) / 1e9;  // thread-level FP64 instructions per second / 1e9
+  if (ms_host) *ms_host = best;
   return HRG_OK;
 }
 

@@ -1,6 +1,6 @@
 // LongTermPlanner on the device: per-joint time-optimal 7-phase jerk profiles, synchronisation to the slowest joint,
 // sampled trajectory. LTP = SS/external/LongTermPlanner (reference tree); everything here follows
-// LTP/src/long_term_planner.cc and LTP/include/long_term_planner/roots.h. One thread plans one (env, joint).
+// LTP/src/long_term_planner.cc and LTP/include/long_term_planner/roots.h. One lane plans one (env, joint).
 #pragma once
 #include "path_math.cuh"
 
@@ -8,14 +8,10 @@ namespace hrg {
 
 struct LtpLimits {  // limits of ONE joint (LongTermPlanner members, long_term_planner.h)
   double v_max, a_max, j_max, t_sample;
-  // 36 doubles of scratch for the <= 6x6 companion matrix of the root finder. NULL = a local array (host tests, stage
-  // kernel); the replan kernels point it at shared memory (dynamically indexed local arrays would live in L1/L2).
+  // 36 doubles of scratch for the <= 6x6 companion matrix of the matrix-in-memory root finder (host build; on the device
+  // only for degrees other than the planner's 4..6, which go to the register-resident solver of ltp_roots_reg.cuh).
+  // NULL = a local array on the host; the device needs shared memory here.
   double* mat = nullptr;
-  // Device only: coop_mask != 0 says "the 8 lanes of coop_mask run this very call together, with identical arguments";
-  // the root finder then shares ONE eigen-solve between them (real_schur_hessenberg_coop) and `mat` is their common
-  // scratch. 0 = every lane solves its own problem in its own scratch.
-  unsigned coop_mask = 0;
-  int coop_lane = 0;
 };
 
 HRG_HD int isign(double v) { return (0.0 < v) - (v < 0.0); }  // long_term_planner.h sign()
@@ -217,14 +213,17 @@ HRG_HD void real_schur_hessenberg(SmallMat& T) {
   }
 }
 
+}  // namespace hrg
+#include "ltp_roots_reg.cuh"
+namespace hrg {
+
 // roots() + getSmallestPositiveNonComplexRoot (roots.h:22-50): coef[0] is the leading coefficient, ncoef = degree+1.
 // Returns +inf if there is no real root > 1e-7.
-#if defined(__CUDACC__)
-__device__ double smallest_positive_real_root_coop(const LtpLimits& L, const double* coef, int ncoef);
-#endif
 HRG_HD_CALL double smallest_positive_real_root(const LtpLimits& L, const double* coef, int ncoef) {
-#if defined(__CUDA_ARCH__)
-  if (L.coop_mask) return smallest_positive_real_root_coop(L, coef, ncoef);
+#if defined(__CUDA_ARCH__) || defined(HRG_HOST_USE_RR)
+  // one problem per lane: the register-resident solver (bit-identical, ltp_roots_reg.cuh) for the planner's degrees
+  // (HRG_HOST_USE_RR: the host emulation can be built on it too, tests/host_emul/build.sh)
+  if (rr_has_degree(ncoef)) return rr_root(coef, ncoef);
 #endif
   SmallMat C;
 #if defined(__CUDA_ARCH__)
@@ -278,242 +277,6 @@ HRG_HD_CALL double smallest_positive_real_root(const LtpLimits& L, const double*
   }
   return best;
 }
-
-#if defined(__CUDACC__)
-// ---- cooperative form: 8 lanes share one eigen-solve ----------------------------------------------------------------
-// Every matrix element sees the same operations in the same order as in real_schur_hessenberg (the single-column /
-// single-row calls below ARE hh_left / hh_right), so the results are bit-identical; but the independent column updates
-// of a left reflection and the independent row updates of a right reflection run one per lane instead of one after the
-// other, which shortens the dependent chain of a Francis step ~2.5x for n = 5..6. Scalars (shifts, deflation tests,
-// reflectors) are recomputed by every lane from the shared matrix, so control flow is uniform within the group.
-// gs() orders "everyone has read" before "someone writes" and publishes the writes.
-__device__ void real_schur_hessenberg_coop(SmallMat& T, int gl, unsigned gm) {
-#define gs() __syncwarp(gm)
-  const int n = T.n;
-  const double eps = 2.220446049250313e-16, dmin = 2.2250738585072014e-308;
-  int iu = n - 1, iter = 0, total_iter = 0;
-  const int max_iters = 40 * n;
-  double exshift = 0.0, norm = 0.0;
-  for (int j = 0; j < n; ++j)
-    for (int i = 0; i < (n < j + 2 ? n : j + 2); ++i) norm += fabs(T(i, j));
-  double caz = norm * eps * eps;
-  if (caz < dmin) caz = dmin;
-  if (norm == 0.0) return;
-  while (iu >= 0) {
-    int il = iu;
-    while (il > 0) {
-      double s = fabs(T(il - 1, il - 1)) + fabs(T(il, il));
-      s = s * eps > caz ? s * eps : caz;
-      if (fabs(T(il, il - 1)) <= s) break;
-      il--;
-    }
-    if (il == iu) {
-      gs();
-      if (gl == 0) {
-        T(iu, iu) += exshift;
-        if (iu > 0) T(iu, iu - 1) = 0.0;
-      }
-      gs();
-      iu--;
-      iter = 0;
-    } else if (il == iu - 1) {
-      double p = 0.5 * (T(iu - 1, iu - 1) - T(iu, iu));
-      double q = p * p + T(iu, iu - 1) * T(iu - 1, iu);
-      const double gq = T(iu, iu - 1);
-      gs();
-      if (gl == 0) {
-        T(iu, iu) += exshift;
-        T(iu - 1, iu - 1) += exshift;
-      }
-      gs();
-      if (q >= 0.0) {
-        double z = sqrt(fabs(q));
-        double gp = (p >= 0.0) ? p + z : p - z, c, s;
-        if (gq == 0.0) {
-          c = gp < 0.0 ? -1.0 : 1.0;
-          s = 0.0;
-        } else if (gp == 0.0) {
-          c = 0.0;
-          s = gq < 0.0 ? 1.0 : -1.0;
-        } else if (fabs(gp) > fabs(gq)) {
-          double t = gq / gp, u = sqrt(1.0 + t * t);
-          if (gp < 0.0) u = -u;
-          c = 1.0 / u;
-          s = -t * c;
-        } else {
-          double t = gp / gq, u = sqrt(1.0 + t * t);
-          if (gq < 0.0) u = -u;
-          s = -1.0 / u;
-          c = -t * s;
-        }
-        {
-          const int j = iu - 1 + gl;  // one column per lane
-          if (j < n) {
-            double x = T(iu - 1, j), y = T(iu, j);
-            T(iu - 1, j) = c * x - s * y;
-            T(iu, j) = s * x + c * y;
-          }
-        }
-        gs();
-        if (gl <= iu) {  // one row per lane
-          double x = T(gl, iu - 1), y = T(gl, iu);
-          T(gl, iu - 1) = c * x - s * y;
-          T(gl, iu) = s * x + c * y;
-        }
-        gs();
-        if (gl == 0) T(iu, iu - 1) = 0.0;
-      }
-      if (gl == 0 && iu > 1) T(iu - 1, iu - 2) = 0.0;
-      gs();
-      iu -= 2;
-      iter = 0;
-    } else {
-      double sh0 = T(iu, iu), sh1 = T(iu - 1, iu - 1), sh2 = T(iu, iu - 1) * T(iu - 1, iu);
-      if (iter == 10) {
-        exshift += sh0;
-        gs();
-        if (gl <= iu) T(gl, gl) -= sh0;
-        gs();
-        double s = fabs(T(iu, iu - 1)) + fabs(T(iu - 1, iu - 2));
-        sh0 = 0.75 * s;
-        sh1 = 0.75 * s;
-        sh2 = -0.4375 * s * s;
-      }
-      if (iter == 30) {
-        double s = (sh1 - sh0) / 2.0;
-        s = s * s + sh2;
-        if (s > 0.0) {
-          s = sqrt(s);
-          if (sh1 < sh0) s = -s;
-          s = s + (sh1 - sh0) / 2.0;
-          s = sh0 - sh2 / s;
-          exshift += s;
-          gs();
-          if (gl <= iu) T(gl, gl) -= s;
-          gs();
-          sh0 = sh1 = sh2 = 0.964;
-        }
-      }
-      iter++;
-      total_iter++;
-      if (total_iter > max_iters) break;
-      int im;
-      double v[3] = {0.0, 0.0, 0.0};
-      for (im = iu - 2; im >= il; --im) {
-        const double Tmm = T(im, im);
-        const double r = sh0 - Tmm, s = sh1 - Tmm;
-        v[0] = (r * s - sh2) / T(im + 1, im) + T(im, im + 1);
-        v[1] = T(im + 1, im + 1) - Tmm - r - s;
-        v[2] = T(im + 2, im + 1);
-        if (im == il) break;
-        const double lhs = T(im, im - 1) * (fabs(v[1]) + fabs(v[2]));
-        const double rhs = v[0] * (fabs(T(im - 1, im - 1)) + fabs(Tmm) + fabs(T(im + 1, im + 1)));
-        if (fabs(lhs) < eps * rhs) break;
-      }
-      for (int k = im; k <= iu - 2; ++k) {
-        const bool first = (k == im);
-        double w[3];
-        if (first) {
-          w[0] = v[0]; w[1] = v[1]; w[2] = v[2];
-        } else {
-          w[0] = T(k, k - 1); w[1] = T(k + 1, k - 1); w[2] = T(k + 2, k - 1);
-        }
-        double tau, beta, ess[2];
-        mk_householder(w, 3, ess, tau, beta);
-        if (beta != 0.0) {
-          gs();
-          if (gl == 0) {
-            if (first && k > il)
-              T(k, k - 1) = -T(k, k - 1);
-            else if (!first)
-              T(k, k - 1) = beta;
-          }
-          if (gl < n - k) hh_left(T, k, k + gl, 3, 1, ess, tau);  // columns k .. n-1, one per lane
-          gs();
-          if (gl < (iu < k + 3 ? iu : k + 3) + 1) hh_right(T, gl, k, 1, 3, ess, tau);  // rows 0 .. min(iu, k+3)
-          gs();
-        }
-      }
-      {
-        double w[2] = {T(iu - 1, iu - 2), T(iu, iu - 2)};
-        double tau, beta, ess[1];
-        mk_householder(w, 2, ess, tau, beta);
-        if (beta != 0.0) {
-          gs();
-          if (gl == 0) T(iu - 1, iu - 2) = beta;
-          if (gl < n - iu + 1) hh_left(T, iu - 1, iu - 1 + gl, 2, 1, ess, tau);
-          gs();
-          if (gl < iu + 1) hh_right(T, gl, iu - 1, 1, 2, ess, tau);
-          gs();
-        }
-      }
-      gs();
-      if (gl == 0)
-        for (int i = im + 2; i <= iu; ++i) {
-          T(i, i - 2) = 0.0;
-          if (i > im + 2) T(i, i - 3) = 0.0;
-        }
-      gs();
-    }
-  }
-#undef gs
-}
-
-__device__ __noinline__ double smallest_positive_real_root_coop(const LtpLimits& L, const double* coef, int ncoef) {
-  const unsigned gm = L.coop_mask;
-  const int gl = L.coop_lane;
-  SmallMat C;
-  C.a = L.mat;
-  __builtin_assume(__isShared(C.a));
-  const int n = ncoef - 1;
-  C.n = n;
-  __syncwarp(gm);  // the previous solve's readers are done with the scratch
-  for (int i = gl; i < 36; i += 8) C.a[i] = 0.0;
-  __syncwarp(gm);
-  if (gl == 0) {
-    for (int i = 0; i + 1 < n; ++i) C(i + 1, i) = 1.0;
-    for (int i = 0; i < n; ++i) C(i, n - 1) = (-1 * coef[ncoef - 1 - i]) / coef[0];
-  }
-  __syncwarp(gm);
-  double scale = 0.0;
-  for (int j = 0; j < n; ++j)
-    for (int i = 0; i < n; ++i) scale = fabs(C(i, j)) > scale ? fabs(C(i, j)) : scale;
-  double best = INFINITY;
-  if (scale < 2.2250738585072014e-308) return best;
-  __syncwarp(gm);
-  if (gl < n)
-    for (int i = 0; i < n; ++i)
-      if (C(i, gl) != 0.0) C(i, gl) /= scale;
-  __syncwarp(gm);
-  real_schur_hessenberg_coop(C, gl, gm);
-  __syncwarp(gm);
-  if (gl < n)
-    for (int i = 0; i < n; ++i) C(i, gl) *= scale;
-  __syncwarp(gm);
-  int i = 0;
-  while (i < n) {
-    if (i == n - 1 || C(i + 1, i) == 0.0) {
-      double re = C(i, i);
-      if (re > 1e-7) best = fmin(best, re);
-      ++i;
-    } else {
-      double p = 0.5 * (C(i, i) - C(i + 1, i + 1));
-      double t0 = C(i + 1, i), t1 = C(i, i + 1);
-      double maxval = fmax(fabs(p), fmax(fabs(t0), fabs(t1)));
-      t0 /= maxval;
-      t1 /= maxval;
-      double p0 = p / maxval;
-      double z = maxval * sqrt(fabs(p0 * p0 + t0 * t1));
-      if (z == 0.0) {
-        double re = C(i + 1, i + 1) + p;
-        if (re > 1e-7) best = fmin(best, re);
-      }
-      i += 2;
-    }
-  }
-  return best;
-}
-#endif
 
 }  // namespace hrg
 #include "ltp_profiles.cuh"

@@ -47,10 +47,56 @@ HRG_HD void ltp_cumsum7(const double* t, double* T) {
   }
 }
 
+// The two quartics optSwitchTimes solves in its "neither max velocity nor max acceleration reached" branch (:245-337) have
+// coefficients in (q_goal, q_0, v_0, a_0, dir, j_max, a_max) only - NOT in v_drive - and dir is itself a function of
+// (q_goal, q_0, v_0, a_0). planTrajectory calls optSwitchTimes for one joint up to nine times with the same four values and
+// different v_drive (once with v_max, then once per timeScaling candidate), so the roots are computed at most once per
+// (env, joint) and handed on: same inputs, same deterministic routine, hence the same bits as solving again. The cache is
+// keyed by the exact bit patterns of the four inputs; a call with any other input (e.g. the -0.0 a mirrored zero velocity
+// turns into) solves afresh and leaves the cache alone.
+struct OptRootCache {
+  double q_goal, q_0, v_0, a_0;  // key
+  double root[2];                // :261, :321
+  int have;                      // bit 0 / 1: root[0] / root[1] valid; bit 2: key set
+};
+HRG_HD void opt_cache_clear(OptRootCache& c) {
+  c.q_goal = c.q_0 = c.v_0 = c.a_0 = 0.0;
+  c.root[0] = c.root[1] = 0.0;
+  c.have = 0;
+}
+HRG_HD bool same_bits(double a, double b) {
+#if defined(__CUDA_ARCH__)
+  return __double_as_longlong(a) == __double_as_longlong(b);
+#else
+  long long x, y;
+  memcpy(&x, &a, 8);
+  memcpy(&y, &b, 8);
+  return x == y;
+#endif
+}
+HRG_HD double opt_cached_root(const LtpLimits& L, OptRootCache* c, bool key_ok, int which, const double* A) {
+  if (c && key_ok && (c->have & (1 << which))) return c->root[which];
+  const double r = smallest_positive_real_root(L, A, 5);
+  if (c && key_ok) {
+    c->root[which] = r;
+    c->have |= 1 << which;
+  }
+  return r;
+}
+
 // optSwitchTimes (LTP/src/long_term_planner.cc:82-353). Returns the reference's bool; T = cumulative switch times.
 HRG_HD_CALL bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double v_drive,
-                                 double* T, double& dir, int& mod_jerk_profile) {
+                                 double* T, double& dir, int& mod_jerk_profile, OptRootCache* cache = nullptr) {
   const double jm = L.j_max, am = L.a_max;
+  bool key_ok = false;
+  if (cache) {
+    if (!(cache->have & 4)) {
+      cache->q_goal = q_goal; cache->q_0 = q_0; cache->v_0 = v_0; cache->a_0 = a_0;
+      cache->have |= 4;
+    }
+    key_ok = same_bits(cache->q_goal, q_goal) && same_bits(cache->q_0, q_0) && same_bits(cache->v_0, v_0) &&
+             same_bits(cache->a_0, a_0);
+  }
   double t[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   mod_jerk_profile = 0;
   const double eps = 4e-3;
@@ -147,7 +193,7 @@ HRG_HD_CALL bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double 
         A[2] = -24 * sq(a_0) + 48 * jm * v_0;
         A[3] = 48 * dir * sq(jm) * q_0 - 48 * dir * sq(jm) * q_goal + 16 * cube(a_0) - 48 * a_0 * jm * v_0;
         A[4] = -3 * pow4(a_0) + 12.0 * sq(a_0) * jm * v_0 - 12.0 * sq(jm) * sq(v_0);
-        root = smallest_positive_real_root(L, A, 5);
+        root = opt_cached_root(L, cache, key_ok, 0, A);
       }
       t[0] = (2.0 * sq(root) - 4 * a_0 * root + sq(a_0) - 2.0 * v_0 * jm) / (4 * jm * root);
       t[6] = sqrt(4 * sq(jm) * sq(t[0]) + 8 * a_0 * jm * t[0] + 2.0 * sq(a_0) + 4 * jm * v_0) / (2.0 * jm);
@@ -182,7 +228,7 @@ HRG_HD_CALL bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double 
         A[4] = 24 * dir * sq(jm) * q_0 * am - 24 * dir * sq(jm) * q_goal * am + 3 * pow4(a_0) + 8 * cube(a_0) * am +
                6 * sq(a_0) * sq(am) - 12.0 * sq(a_0) * jm * v_0 - 24 * a_0 * jm * v_0 * am - 12.0 * sq(am) * jm * v_0 +
                12.0 * sq(jm) * sq(v_0);
-        root = smallest_positive_real_root(L, A, 5);
+        root = opt_cached_root(L, cache, key_ok, 1, A);
         t[0] = (root - a_0 - am) / jm;
         t[4] = (a_0 + am) / jm + t[0];
         t[5] = (sq(jm) * sq(t[0]) + 2.0 * sq(jm) * t[0] * t[4] - sq(jm) * sq(t[4]) + 2.0 * a_0 * jm * t[0] +

@@ -6,11 +6,11 @@ namespace hrg {
 
 // One candidate: accept if optSwitchTimes succeeds and -0.01 < t_required - T[6] < 0.1 (:398-405 and repeats).
 HRG_HD_CALL bool ltp_try_vdrive(const LtpLimits& L, double q_goal, double q_0, double v_orig, double a_orig, double v_drive,
-                           double t_required, double* T, int& mod_jerk_profile) {
+                           double t_required, double* T, int& mod_jerk_profile, OptRootCache* cache = nullptr) {
   const double tol = 0.1;
   if (!isnan(v_drive) && v_drive > 0) {
     double trash;
-    bool ok = ltp_opt_switch_times(L, q_goal, q_0, v_orig, a_orig, v_drive, T, trash, mod_jerk_profile);
+    bool ok = ltp_opt_switch_times(L, q_goal, q_0, v_orig, a_orig, v_drive, T, trash, mod_jerk_profile, cache);
     if (ok && t_required - T[6] < tol && t_required - T[6] > -tol / 10) return true;
   }
   return false;
@@ -141,7 +141,7 @@ HRG_HD double ltp_scaling_vdrive(const LtpLimits& L, int cand, double root, doub
 // Sequential form: the candidates one after the other, first accepted wins (host tests, stage kernel).
 HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double dir,
                                   double tr /*t_required*/, double* T /*scaled_t*/, double& v_drive,
-                                  int& mod_jerk_profile) {
+                                  int& mod_jerk_profile, OptRootCache* cache = nullptr) {
   if (dir < 0) {
     v_0 = -v_0;
     a_0 = -a_0;
@@ -152,7 +152,7 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
     int ncoef;
     v_drive = ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, dir, tr, A, ncoef);
     if (ncoef) v_drive = ltp_scaling_vdrive(L, cand, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
-    if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile)) return true;
+    if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile, cache)) return true;
   }
   // no valid solution (:640-644)
   mod_jerk_profile = 0;

@@ -212,6 +212,7 @@ HRG_HD int ltp_plan_env_seq(const HrgConfig& c, const double* q_goal, const doub
   const int J = c.nb_joints;
   JointPlan opt[HRG_MAX_JOINTS], sc[HRG_MAX_JOINTS];
   LtpLimits L[HRG_MAX_JOINTS];
+  OptRootCache rc[HRG_MAX_JOINTS];  // the quartic roots of optSwitchTimes, shared by all its calls for a joint
   for (int j = 0; j < J; ++j) {
     L[j].v_max = c.v_max[j]; L[j].a_max = c.a_max_ltt[j]; L[j].j_max = c.j_max_ltt[j]; L[j].t_sample = c.sample_time;
     L[j].mat = mat;
@@ -219,7 +220,8 @@ HRG_HD int ltp_plan_env_seq(const HrgConfig& c, const double* q_goal, const doub
   }
   for (int j = 0; j < J; ++j) {
     ltp_zero7(opt[j].T);
-    if (!ltp_opt_switch_times(L[j], q_goal[j], q_0[j], v_0[j], a_0[j], L[j].v_max, opt[j].T, opt[j].dir, opt[j].mod))
+    opt_cache_clear(rc[j]);
+    if (!ltp_opt_switch_times(L[j], q_goal[j], q_0[j], v_0[j], a_0[j], L[j].v_max, opt[j].T, opt[j].dir, opt[j].mod, &rc[j]))
       return 0;
   }
   double t_required = -1;
@@ -237,7 +239,7 @@ HRG_HD int ltp_plan_env_seq(const HrgConfig& c, const double* q_goal, const doub
     ltp_zero7(sc[j].T);
     if (j != slowest)
       ltp_time_scaling(L[j], q_goal[j], q_0[j], v_0[j], a_0[j], opt[j].dir, t_required, sc[j].T, sc[j].v_drive,
-                       sc[j].mod);
+                       sc[j].mod, &rc[j]);
     double mx = sc[j].T[0];
     for (int k = 1; k < 7; ++k) mx = (mx < sc[j].T[k]) ? sc[j].T[k] : mx;
     if (mx <= 0.0)

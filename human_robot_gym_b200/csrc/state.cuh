@@ -37,7 +37,9 @@ enum { P_REC = 0, P_FS = 1, P_FS2 = 2, P_SAFE = 3, N_PATHS = 4, PATH_FIELDS = 10
 struct PlanRec {   // one joint: cumulative jerk switch times, direction, cruise velocity, profile flag, samples needed
   double T[7];
   double dir, v_drive;
+  double root[2];   // optSwitchTimes' two quartic roots of this joint, once solved (OptRootCache, ltp_profiles.cuh)
   int32_t mod, len;
+  int32_t have, pad;  // bit 0 / 1: root[0] / root[1] valid
 };
 struct PlanHead {  // one env: time of the slowest joint, its index, and whether every joint passed checkInputs/optSwitchTimes
   double t_required;
@@ -75,9 +77,9 @@ struct DevState {
   double* min_dist;   // [3][N]
   int32_t* replan_list;   // [N]
   int32_t* replan_count;  // [1]
-  int32_t* replan_ctr;    // [4] work counters of the replan kernels + length of the deep list (kernels_tick.cuh CTR_*)
-  PlanRec* plan_opt;      // [N][HRG_MAX_JOINTS] time-optimal plan per joint (k_replan_opt); len = this joint ok
-  PlanRec* plan_sc;       // [N][HRG_MAX_JOINTS] plan scaled to the slowest joint (k_replan_scale / k_replan_sample); len < 0 = -(deep slot + 1)
+  int32_t* replan_ctr;    // [4] work counters of the replan kernels + length of the deep list (kernels_replan.cuh CTR_*)
+  PlanRec* plan_opt;      // [N][HRG_MAX_JOINTS] time-optimal plan per joint (k_replan_plan); len = this joint ok
+  PlanRec* plan_sc;       // [N][HRG_MAX_JOINTS] plan scaled to the slowest joint (k_replan_plan / k_replan_sample); len < 0 = -(deep slot + 1)
   PlanHead* plan_head;    // [N]
   int32_t* deep_list;     // [N * J] (env, joint) tasks whose closed-form timeScaling candidates were rejected
   PlanRec* deep_res;      // [N * J][6] result of each polynomial candidate; len = accepted

@@ -210,10 +210,28 @@ int hrg_shield_ltt_max_window(HrgShield* s, const int32_t* index, int window_k, 
 /* Accumulated statistics since the last clear; `out` is a DEVICE pointer to one HrgStats. */
 int hrg_shield_stats(HrgShield* s, HrgStats* out, int clear, void* stream);
 
-/* Per-kernel device timing of hrg_shield_step for the next `max_steps` steps (0 = off): CUDA events are recorded on the
- * step's stream around k_pre + k_plan, the four k_replan_* kernels, both k_reach_verify passes, k_select (the replan is not overlapped while profiling). hrg_shield_profile_read synchronises on the last
- * event and returns the summed milliseconds per kernel (ms_host[4]) and the number of steps they cover. */
+/* Per-kernel device timing of the tick for the next `max_steps` steps (0 = off): a CUDA event is recorded on the step's
+ * stream after EVERY kernel launch of a step (the replan chain is not overlapped while profiling, so each interval is one
+ * kernel). hrg_shield_profile_read_kernels synchronises on the last event and returns the summed milliseconds per launch
+ * slot (ms_host[HRG_PROF_SLOTS], indices below) and the number of steps they cover; hrg_shield_profile_read returns the same
+ * folded into four groups (ms_host[4]: measure+pre+plan, the replan chain, reach+verify, select). */
+#define HRG_PROF_MEASURE 0    /* k_measure */
+#define HRG_PROF_PRE 1        /* k_pre */
+#define HRG_PROF_PLAN 2       /* k_plan */
+#define HRG_PROF_PLAN_LTT 3   /* k_replan_plan */
+#define HRG_PROF_SPARE 4      /* (unused) */
+#define HRG_PROF_DEEP 5       /* k_replan_deep */
+#define HRG_PROF_SAMPLE 6     /* k_replan_sample */
+#define HRG_PROF_PFL 7        /* k_pfl_ltt (PFL handles) */
+#define HRG_PROF_TAIL 8       /* k_replan_tail */
+#define HRG_PROF_VERIFY_P0 9  /* k_reach_verify pass 0 (Pos model of the cascade, or the full kernel) */
+#define HRG_PROF_STAGE_VEL 10 /* k_verify_stage<1> */
+#define HRG_PROF_STAGE_ACC 11 /* k_verify_stage<2> */
+#define HRG_PROF_VERIFY_P1 12 /* k_reach_verify pass 1 (replanned envs) */
+#define HRG_PROF_SELECT 13    /* k_select */
+#define HRG_PROF_SLOTS 14
 int hrg_shield_profile(HrgShield* s, int max_steps);
+int hrg_shield_profile_read_kernels(HrgShield* s, double* ms_host, int* steps_host);
 int hrg_shield_profile_read(HrgShield* s, double* ms_host, int* steps_host);
 
 int hrg_shield_num_envs(const HrgShield* s);
@@ -275,6 +293,13 @@ int hrg_shield_tick_replay_host(HrgShield* s, HrgHuman* h, const int64_t* low_le
                                 const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
                                 double* ddq_host, uint8_t* flags_host, void* stream);
 int64_t hrg_human_launch_count(const HrgHuman* h);
+
+/* Register-resident FP64 throughput of CUDA device `device` (the FP-pipe roofline denominator, not in
+ * MEASURED_PEAKS.json): mode 0 = DFMA chains, 1 = DMUL + DADD pairs (what this library's -fmad=false arithmetic issues),
+ * 2 = DADD only; 8 independent chains per thread, 2048 threads per SM, `iters` x 32 chain steps per thread. Synchronous.
+ * gflops_host: achieved GFLOP/s (FMA = 2 flop); ginst_host (may be NULL): 1e9 thread-level FP64 instructions per second -
+ * the unit of ncu's smsp__sass_thread_inst_executed_op_d{add,mul,fma}_pred_on; ms_host (may be NULL): best launch time. */
+int hrg_microbench_fp64(int device, int mode, int iters, double* gflops_host, double* ginst_host, double* ms_host);
 
 /* ---- per-stage entry points (parity tests + ncu); all DEVICE pointers --------------------------------------- */
 /* capsule_capsule_dist (RL/include/intersections.hpp:105-124) for n independent pairs: c1,c2 [n,7] -> dist [n]. */

@@ -298,6 +298,15 @@ int emul_ltp_plan(const HrgConfig* cfg, const double* goal, const double* q0, co
   return ltp_plan_env_seq(*cfg, goal, q0, v0, a0, traj, cap);
 }
 double emul_poly_root(const double* coef, int ncoef) { LtpLimits L{}; return smallest_positive_real_root(L, coef, ncoef); }
+// the register-resident solver the device uses for one-problem-per-lane kernels (csrc/ltp_roots_reg.cuh), degrees 4..6
+double emul_poly_root_reg(const double* coef, int ncoef) { return rr_has_degree(ncoef) ? rr_root(coef, ncoef) : NAN; }
+void emul_poly_root_batch(int n, int ncoef, const double* coef /*[n, ncoef]*/, double* out_mat, double* out_reg) {
+  LtpLimits L{};
+  for (int i = 0; i < n; ++i) {
+    out_mat[i] = smallest_positive_real_root(L, coef + (size_t)i * ncoef, ncoef);
+    out_reg[i] = rr_has_degree(ncoef) ? rr_root(coef + (size_t)i * ncoef, ncoef) : NAN;
+  }
+}
 
 // ---- single-function entry points for the golden-vector tests -------------------------------------------------------
 static LtpLimits lim1(double ts, const double* lim) {

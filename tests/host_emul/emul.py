@@ -17,7 +17,9 @@ def lib():
     global _lib
     if _lib is None:
         src = os.path.join(_HERE, "emul.cc")
-        if not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(src):
+        csrc = os.path.join(_HERE, "..", "..", "human_robot_gym_b200", "csrc")
+        newest = max([os.path.getmtime(src)] + [os.path.getmtime(os.path.join(csrc, f)) for f in os.listdir(csrc)])
+        if not os.path.exists(_LIB) or os.path.getmtime(_LIB) < newest:
             subprocess.check_call([os.path.join(_HERE, "build.sh")])
         L = C.CDLL(_LIB)
         L.emul_create.restype = C.c_void_p
@@ -44,6 +46,9 @@ def lib():
         L.emul_human_keypoints.argtypes = [C.c_int, _p, _p, C.c_int, _p, _p, _p, _p]
         L.emul_poly_root.restype = C.c_double
         L.emul_poly_root.argtypes = [_p, C.c_int]
+        L.emul_poly_root_reg.restype = C.c_double
+        L.emul_poly_root_reg.argtypes = [_p, C.c_int]
+        L.emul_poly_root_batch.argtypes = [C.c_int, C.c_int, _p, _p, _p]
         _lib = L
     return _lib
 
@@ -134,6 +139,15 @@ def ltp_plan(cfg, goal, q0, v0, a0, cap=4096):
 def poly_root(coef):
     c = _a(coef)
     return lib().emul_poly_root(_ptr(c), c.shape[0])
+
+
+def poly_root_batch(coefs):
+    """(matrix-in-memory solver, register-resident solver) smallest positive real roots of coefs [n, ncoef]."""
+    c = _a(coefs)
+    n, ncoef = c.shape
+    a, b = np.zeros(n), np.zeros(n)
+    lib().emul_poly_root_batch(n, ncoef, _ptr(c), _ptr(a), _ptr(b))
+    return a, b
 
 
 def ltp_opt_braking(ts, lim, v0, a0):
