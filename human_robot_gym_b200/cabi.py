@@ -140,6 +140,7 @@ SYMBOLS = {
     "hrg_shield_tick_replay_host": (C.c_int, [C.c_void_p, C.c_void_p] + [C.c_void_p] * 8 + [_vp]),
     "hrg_human_launch_count": (C.c_int64, [C.c_void_p]),
     "hrg_microbench_fp64": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "hrg_microbench_fp64_latency": (C.c_int, [C.c_int, C.c_void_p]),
     "hrg_stage_capsule_dist": (C.c_int, [C.c_int, _dp, _dp, _dp, _vp]),
     "hrg_stage_plan_safety_shield": (C.c_int, [C.c_double, C.c_int, _dp, _u8p, _dp, _dp, _vp]),
     "hrg_stage_ltp_plan": (C.c_int, [C.POINTER(HrgConfig), C.c_int, _dp, _dp, _dp, _dp, _dp, _i32p, C.c_int, _vp]),
@@ -188,6 +189,13 @@ def microbench_fp64(device: int = 0, iters: int = 4096) -> dict:
                                                  C.addressof(ms)), "hrg_microbench_fp64")
         out[name] = {"gflops": g.value, "ginst": i.value, "ms": ms.value}
     return out
+
+
+def microbench_fp64_latency(device: int = 0) -> dict:
+    """Dependent-chain latency (SM cycles per operation, one warp alone) of the FP64 operations the planner is made of."""
+    out = (C.c_double * 6)()
+    check(load_library().hrg_microbench_fp64_latency(int(device), C.addressof(out)), "hrg_microbench_fp64_latency")
+    return dict(zip(("dadd", "dmul", "dfma", "ddiv_plus_dadd", "dsqrt_plus_dadd", "dadd_cmp_select"), [round(x, 2) for x in out]))
 
 
 def check(rc: int, what: str = ""):

@@ -84,6 +84,8 @@ struct HrgShield {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_meas = nullptr;
   bool overlap = true;
   bool debug_sync = false;
+  int deep_per_warp = 4;  // tasks per warp of k_replan_deep (HRG_DEEP_PER_WARP)
+  int plan_envs_per_warp = 2;  // envs per warp of k_replan_plan, <= 16 / J (HRG_PLAN_ENVS_PER_WARP)
   bool cascade = true;  // verification cascade for pass 0 (HRG_NO_CASCADE=1 or stored capsules: full kernel)
   // optional per-kernel timing of the tick (bench.py's roofline leg): one event after every launch of a step
   bool prof = false;
@@ -239,6 +241,11 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
     if (const char* v = getenv("HRG_NO_OVERLAP")) h->overlap = !(atoi(v) > 0);
     if (const char* v = getenv("HRG_NO_CASCADE")) h->cascade = !(atoi(v) > 0);
     if (const char* v = getenv("HRG_DEBUG_SYNC")) h->debug_sync = atoi(v) > 0;
+    h->plan_envs_per_warp = 16 / J > 2 ? 2 : 16 / J;
+    if (const char* v = getenv("HRG_PLAN_ENVS_PER_WARP"))
+      if (atoi(v) >= 1 && atoi(v) <= 16 / J) h->plan_envs_per_warp = atoi(v);
+    if (const char* v = getenv("HRG_DEEP_PER_WARP"))
+      if (atoi(v) >= 1 && atoi(v) <= 32) h->deep_per_warp = atoi(v);
   }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
@@ -447,17 +454,17 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
   {
     // the replan list length is only known on the device: the kernels fetch their work from device counters, their grids
     // only bound residency (one warp per block, so that the few hundred busy warps spread over all schedulers)
-    const int J = s->S.J, E = 32 / J;
+    const int J = s->S.J;
     const int cap = s->sm_count * 16;
-    int g_env = grid_for(N, E);
-    if (g_env > cap) g_env = cap;
-    int g_deep = grid_for(N * J * 6, 32);
+    int g_plan = grid_for(N, s->plan_envs_per_warp), g_samp = N, g_deep = grid_for(N * J * 6, s->deep_per_warp);
+    if (g_plan > cap) g_plan = cap;
+    if (g_samp > cap) g_samp = cap;
     if (g_deep > cap) g_deep = cap;
-    k_replan_plan<<<g_env, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_plan<<<g_plan, kReplanBlock, 0, rs>>>(s->S, s->plan_envs_per_warp);
     mark(HRG_PROF_PLAN_LTT);
-    k_replan_deep<<<g_deep, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_deep<<<g_deep, kReplanBlock, 0, rs>>>(s->S, s->deep_per_warp);
     mark(HRG_PROF_DEEP);
-    k_replan_sample<<<g_env, kReplanBlock, 0, rs>>>(s->S);
+    k_replan_sample<<<g_samp, kSampleBlock, 0, rs>>>(s->S);
     mark(HRG_PROF_SAMPLE);
     if (s->pfl) {
       int pgrid = s->sm_count * 8;
@@ -480,13 +487,16 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
     keep(cudaEventRecord(s->ev_join, s->side));
     k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
     verify_pass0(s, st, s->reach_smem_p0, mark);
+    // determineNextMotion of the envs that did not replan: off the critical path, next to the replan chain
+    k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status, 0);
+    s->launches++;
     keep(cudaStreamWaitEvent(st, s->ev_join, 0));
   } else {
     verify_pass0(s, st, s->reach_smem, mark);
   }
   k_reach_verify<2><<<tile_grid(N), 32 * s->S.J * 2, s->reach_smem, st>>>(s->S, 1);
   mark(HRG_PROF_VERIFY_P1);
-  k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status);
+  k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status, fork ? 1 : -1);
   mark(HRG_PROF_SELECT);
   s->launches += 9;
   keep(cudaGetLastError());

@@ -313,6 +313,37 @@ int hrg_microbench_fp64(int device, int mode, int iters, double* gflops_host, do
   return HRG_OK;
 }
 
+int hrg_microbench_fp64_latency(int device, double* cycles_host /*[6]*/) {
+  if (!cycles_host) return fail(HRG_EINVAL, "hrg_microbench_fp64_latency: NULL argument");
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev < 1) return fail(HRG_ENODEVICE, "no CUDA device (this library has no CPU fallback)", ce);
+  if (device < 0 || device >= ndev) return fail(HRG_EINVAL, "device index out of range");
+  CK(cudaSetDevice(device));
+  double* out = nullptr;
+  long long* cyc = nullptr;
+  CK(cudaMalloc(&out, 32 * sizeof(double)));
+  CK(cudaMalloc(&cyc, sizeof(long long)));
+  const int iters = 256;
+  for (int mode = 0; mode < 6 && ce == cudaSuccess; ++mode) {
+    for (int rep = 0; rep < 2; ++rep) {  // the second launch has the code in the instruction cache
+      if (mode == 0) hrg::k_fp64_latency<0><<<1, 32>>>(out, cyc, iters, 1.0000001, 1e-9);
+      if (mode == 1) hrg::k_fp64_latency<1><<<1, 32>>>(out, cyc, iters, 1.0000001, 1e-9);
+      if (mode == 2) hrg::k_fp64_latency<2><<<1, 32>>>(out, cyc, iters, 1.0000001, 1e-9);
+      if (mode == 3) hrg::k_fp64_latency<3><<<1, 32>>>(out, cyc, iters, 1.0000001, 1e-9);
+      if (mode == 4) hrg::k_fp64_latency<4><<<1, 32>>>(out, cyc, iters, 1.0000001, 1e-9);
+      if (mode == 5) hrg::k_fp64_latency<5><<<1, 32>>>(out, cyc, iters, 1.0000001, 1e-9);
+    }
+    long long h = 0;
+    ce = cudaMemcpy(&h, cyc, sizeof(h), cudaMemcpyDeviceToHost);
+    cycles_host[mode] = (double)h / (iters * 16.0);
+  }
+  cudaFree(out);
+  cudaFree(cyc);
+  if (ce != cudaSuccess) return fail(HRG_ECUDA, "hrg_microbench_fp64_latency", ce);
+  return HRG_OK;
+}
+
 // ---- per-stage entry points ------------------------------------------------------------------------------------
 int hrg_stage_capsule_dist(int n, const double* c1, const double* c2, double* dist, void* stream) {
   if (n < 0 || !c1 || !c2 || !dist) return fail(HRG_EINVAL, "hrg_stage_capsule_dist: bad argument");

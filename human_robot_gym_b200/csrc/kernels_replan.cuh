@@ -69,15 +69,24 @@ __device__ __forceinline__ int fetch_warp_tasks(int32_t* ctr, int per_warp, int 
   return base < ntask ? base : -1;
 }
 
-__global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S) {
+// Lane = (env, joint, half): two lanes per joint, floor(16 / J) envs per warp. A tick has far fewer problems than the GPU has
+// lanes, so lanes are spent on shortening each warp's dependent chain - the kernel takes as long as its slowest warp:
+//   1. half h solves quartic h of optSwitchTimes ahead of time (opt_prefill_root): every lane of the warp is in the
+//      eigen-solver at the same program point, and the two solves of a joint run side by side;
+//   2. half 0 runs checkInputs + optSwitchTimes with v_max (closed forms only now); the env's slowest joint comes from
+//      shuffles over its lanes;
+//   3. half h evaluates closed-form timeScaling candidate h (:378-436) - the reference tries (1) first and (2) only if
+//      (1) is rejected, so half 0's result wins when both are accepted.
+__global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S, int envs_per_warp) {
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int J = S.J, N = S.N;
-  const int E = 32 / J;                          // envs per warp
-  const int sub = lane / J;                      // env of this lane within the warp (>= E: spare lane)
-  const int j = lane - sub * J;
-  const int seg0 = (sub < E ? sub : 0) * J;      // first lane of this lane's env
+  const int E = envs_per_warp;                   // envs per warp, <= 16 / J
+  const int half = lane & 1, pairi = lane >> 1;
+  const int sub = pairi / J;                     // env of this lane within the warp (>= E: spare lane)
+  const int j = pairi - sub * J;
+  const int seg0 = (sub < E ? sub : 0) * 2 * J;  // first lane of this lane's env
   const int count = *S.replan_count;
   for (;;) {
     const int base = fetch_warp_tasks(S.replan_ctr + CTR_PLAN, E, count, lane);
@@ -93,23 +102,31 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S) {
     opt_cache_clear(rc);
     double q_0 = 0.0, v_0 = 0.0, a_0 = 0.0, q_goal = 0.0;
     bool ok_j = false;
-    int e = 0;
     if (act) {
-      e = S.replan_list[idx];
+      const int e = S.replan_list[idx];
       q_0 = cur_at(S, j, e); v_0 = cur_at(S, J + j, e); a_0 = cur_at(S, 2 * J + j, e);
       q_goal = S.goal_q[(size_t)j * N + e];
       ok_j = ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0);
-      if (ok_j) ok_j = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, opt.T, opt.dir, opt.mod, &rc);
+      if (ok_j) opt_prefill_root(L, q_goal, q_0, v_0, a_0, half, rc);  // 1.
     }
-    // slowest joint of the env (:39-45) in the reference's loop order; it stops at the first joint whose checkInputs /
-    // optSwitchTimes fails: ok = all joints ok
+    {  // the partner's root
+      const double other = __shfl_xor_sync(full, rc.root[half], 1);
+      rc.root[half ^ 1] = other;
+      if (ok_j) rc.have |= 3;
+    }
+    if (act && ok_j && half == 0)  // 2.
+      ok_j = ltp_opt_switch_times(L, q_goal, q_0, v_0, a_0, L.v_max, opt.T, opt.dir, opt.mod, &rc);
+    // half 1 gets its joint's result; then the slowest joint of the env (:39-45) in the reference's loop order; the
+    // reference stops at the first joint whose checkInputs / optSwitchTimes fails: ok = all joints ok
+    opt.dir = __shfl_sync(full, opt.dir, lane & ~1);
+    opt.mod = __shfl_sync(full, opt.mod, lane & ~1);
     PlanHead h;
     h.t_required = -1;
     h.slowest = -1;
     bool ok = true;
     for (int k = 0; k < J; ++k) {
-      const double tk = __shfl_sync(full, opt.T[6], seg0 + k);
-      const int okk = __shfl_sync(full, ok_j ? 1 : 0, seg0 + k);
+      const double tk = __shfl_sync(full, opt.T[6], seg0 + 2 * k);
+      const int okk = __shfl_sync(full, ok_j ? 1 : 0, seg0 + 2 * k);
       ok = ok && okk != 0;
       if (tk > h.t_required) {
         h.t_required = tk;
@@ -118,40 +135,59 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S) {
     }
     if (h.slowest == -1) ok = false;
     h.ok = ok ? 1 : 0;
-    if (!act) continue;  // (spare lanes wait in the next fetch's shuffle)
+    // 3. candidate `half`
+    double T[7];
+    ltp_zero7(T);
+    double v_drive = L.v_max;
+    int mod = opt.mod;
+    bool acc = false;
+    const bool scale = act && ok && j != h.slowest;
+    if (scale) {
+      double v_m = v_0, a_m = a_0;
+      if (opt.dir < 0) {
+        v_m = -v_m;
+        a_m = -a_m;
+      }
+      const double v_orig = opt.dir * v_m, a_orig = opt.dir * a_m;
+      double A[7];
+      int ncoef;
+      v_drive = ltp_scaling_setup(L, half, q_goal, q_0, v_m, a_m, opt.dir, h.t_required, A, ncoef);
+      acc = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, h.t_required, T, mod, &rc);
+    }
+    // half 0 keeps its own candidate if accepted, else takes half 1's
+    const int acc1 = __shfl_xor_sync(full, acc ? 1 : 0, 1);
+    const bool take1 = half == 0 && !acc && acc1 != 0;
+    {
+      const double vd1 = __shfl_xor_sync(full, v_drive, 1);
+      const int mod1 = __shfl_xor_sync(full, mod, 1);
+      if (take1) {
+        v_drive = vd1;
+        mod = mod1;
+      }
+#pragma unroll
+      for (int k = 0; k < 7; ++k) {
+        const double t1 = __shfl_xor_sync(full, T[k], 1);
+        if (take1) T[k] = t1;
+      }
+    }
+    if (!act || half != 0) continue;  // (the other lanes wait in the next fetch's shuffle)
     opt.len = h.ok;
     PlanRec sc = opt;
     if (ok) {
-      double T[7];
-      ltp_zero7(T);
-      double v_drive = L.v_max;
-      int mod = opt.mod;
-      bool deep = false;
-      if (j != h.slowest) {
-        double v_m = v_0, a_m = a_0;
-        if (opt.dir < 0) {
-          v_m = -v_m;
-          a_m = -a_m;
-        }
-        const double v_orig = opt.dir * v_m, a_orig = opt.dir * a_m;
-        bool acc = false;
-        for (int cand = 0; cand < 2 && !acc; ++cand) {
-          double A[7];
-          int ncoef;
-          v_drive = ltp_scaling_setup(L, cand, q_goal, q_0, v_m, a_m, opt.dir, h.t_required, A, ncoef);
-          acc = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, h.t_required, T, mod, &rc);
-        }
-        deep = !acc;
-      }
-      if (deep) {
+      if (scale && !acc && !take1) {
         const int slot = atomicAdd(S.replan_ctr + CTR_DEEP_COUNT, 1);
         S.deep_list[slot] = idx * J + j;
         sc.len = -(slot + 1);
       } else {
+        if (!scale) {  // the slowest joint keeps its time-optimal plan (:41-45): zero times -> the `mx <= 0` fallback
+          ltp_zero7(T);
+          v_drive = L.v_max;
+          mod = opt.mod;
+        }
         finish_scaled(L, opt, T, v_drive, mod, sc);
       }
     }
-    opt.root[0] = rc.root[0]; opt.root[1] = rc.root[1]; opt.have = rc.have & 3;  // whatever has been solved so far
+    opt.root[0] = rc.root[0]; opt.root[1] = rc.root[1]; opt.have = rc.have & 3;
     S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j] = opt;
     S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j] = sc;
     if (j == 0) S.plan_head[idx] = h;
@@ -160,17 +196,20 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S) {
 
 // One (deep-list slot, polynomial candidate) task per lane. Tasks are ordered by candidate - the degree-6 one first, it
 // has the longest solve - so that the 32 lanes of a warp run the same solver.
-__global__ void __launch_bounds__(kReplanBlock) k_replan_deep(DevState S) {
+// `per_warp` <= 32 tasks per warp: the lanes of a warp run the solver's three-way case split and its unrolled row / column
+// positions one after the other wherever they disagree, so fewer problems per warp = a shorter chain per warp, and the GPU
+// has warps to spare.
+__global__ void __launch_bounds__(kReplanBlock) k_replan_deep(DevState S, int per_warp) {
   const HrgConfig& c = *S.cfg;
   const int lane = threadIdx.x & 31;
   const int J = S.J, N = S.N;
   const int n_deep = S.replan_ctr[CTR_DEEP_COUNT];
   const int ntask = n_deep * 6;
   for (;;) {
-    const int base = fetch_warp_tasks(S.replan_ctr + CTR_DEEP, 32, ntask, lane);
+    const int base = fetch_warp_tasks(S.replan_ctr + CTR_DEEP, per_warp, ntask, lane);
     if (base < 0) break;
     const int dt = base + lane;
-    if (dt >= ntask) continue;
+    if (lane >= per_warp || dt >= ntask) continue;
     const int cls = dt / n_deep, slot = dt - cls * n_deep;
     const int cand = cls == 0 ? 7 : (cls == 1 ? 4 : (cls < 4 ? cls : cls + 1));  // 7, 4, 2, 3, 5, 6
     const int task = S.deep_list[slot];
@@ -265,34 +304,42 @@ __device__ __forceinline__ double jerk_reg_at(const JerkSamplerReg& S, int i) {
   return j;
 }
 
-// WITH_PFL only decides who owns alpha_i afterwards (k_pfl_ltt for PFL envs); the sampling itself is the same.
-__global__ void __launch_bounds__(kReplanBlock) k_replan_sample(DevState S) {
+// One env per block of two warps. getTrajectory has two parts of very different shape: the jerk of sample i of joint r
+// (a 7-way range test plus up to twelve sub-sample corrections, ~90 instructions, independent for every (r, i)), and the
+// reference's sequential recurrence a += ts j, v += ts a, q += ts v (a dozen instructions that cannot be reordered without
+// changing roundings). The kernel takes as long as the LONGEST trajectory of the tick, so only the recurrence may sit on the
+// dependent chain: warp 1 produces the jerk of chunk c + 1 (lane = sample, one joint after the other) into one half of a
+// double buffer while lanes 0..J-1 of warp 0 integrate chunk c out of the other half and stream the samples out.
+constexpr int kSampleBlock = 64;
+__global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S) {
+  __shared__ JerkSamplerReg q_s[HRG_MAX_JOINTS];
+  __shared__ double jbuf_s[2][HRG_MAX_JOINTS][33];
+  __shared__ int len_s[HRG_MAX_JOINTS];
+  __shared__ int idx_s;
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
-  const int lane = threadIdx.x & 31;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int J = S.J;
-  const int E = 32 / J;
-  const int sub = lane / J;
-  const int j = lane - sub * J;
-  const int seg0 = (sub < E ? sub : 0) * J;
   const int count = *S.replan_count;
   for (;;) {
-    const int base = fetch_warp_tasks(S.replan_ctr + CTR_SAMPLE, E, count, lane);
-    if (base < 0) break;
-    const int idx = base + sub;
-    const bool act = sub < E && idx < count;
-    const LtpLimits L = joint_limits(c, act ? j : 0);
-    int e = 0, pend = 0, len_j = 0;
-    bool ok = false;
+    if (tid == 0) idx_s = atomicAdd(S.replan_ctr + CTR_SAMPLE, 1);
+    __syncthreads();
+    const int idx = idx_s;
+    if (idx >= count) break;
+    const int e = S.replan_list[idx];
+    const int pend = (S.flags[e] & F_LIVE_SLOT) ? 0 : 1;
+    const PlanHead head = S.plan_head[idx];
+    bool ok = head.ok != 0;
+    const bool jl = warp == 0 && lane < J;  // the lane that owns joint `lane`
+    const int j = lane < J ? lane : 0;
+    const LtpLimits L = joint_limits(c, j);
     JointPlan sc;
     ltp_zero7(sc.T);
     sc.dir = 0.0; sc.v_drive = 0.0; sc.mod = 0;
     double q_0 = 0.0, v_0 = 0.0, a_0 = 0.0;
-    if (act) {
-      e = S.replan_list[idx];
-      pend = (S.flags[e] & F_LIVE_SLOT) ? 0 : 1;
-      ok = S.plan_head[idx].ok != 0;
+    if (jl) {
       q_0 = cur_at(S, j, e); v_0 = cur_at(S, J + j, e); a_0 = cur_at(S, 2 * J + j, e);
+      int len_j = 0;
       if (ok) {
         PlanRec rec = S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j];
         if (rec.len < 0) {
@@ -316,14 +363,13 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_sample(DevState S) {
         for (int k = 0; k < 7; ++k) sc.T[k] = rec.T[k];
         sc.dir = rec.dir; sc.v_drive = rec.v_drive; sc.mod = rec.mod;
         len_j = rec.len;
+        sampler_reg_init(L, sc, q_s[j]);
       }
+      len_s[j] = len_j;
     }
-    // trajectory length of the env = max over its joints (:716-719)
-    int len = 0;
-    for (int k = 0; k < J; ++k) {
-      const int other = __shfl_sync(full, len_j, seg0 + k);
-      len = other > len ? other : len;
-    }
+    __syncthreads();
+    int len = 0;  // trajectory length of the env = max over its joints (:716-719)
+    for (int k = 0; k < J; ++k) len = len_s[k] > len ? len_s[k] : len;
     uint32_t trunc = 0;
     if (ok) {
       if (len > S.L) {
@@ -333,18 +379,18 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_sample(DevState S) {
         ok = false;
       }
     }
-    const int my_len = (act && ok) ? len : 0;
-    int wlen = my_len;  // samples this warp integrates
-    for (int o = 16; o > 0; o >>= 1) {
-      const int other = __shfl_xor_sync(full, wlen, o);
-      wlen = other > wlen ? other : wlen;
-    }
     bool in = true;
-    if (wlen > 0) {
-      JerkSamplerReg Q;
-      sampler_reg_init(L, sc, Q);
+    if (ok) {
+      const int nchunk = (len + 31) >> 5;
+      auto produce = [&](int ch) {  // warp 1: jerk of samples ch * 32 + lane of every joint
+        const int i = (ch << 5) + lane;
+        for (int r = 0; r < J; ++r) jbuf_s[ch & 1][r][lane] = jerk_reg_at(q_s[r], i);
+      };
+      if (warp == 1) produce(0);
+      __syncthreads();
       const double ts = L.t_sample;
       const double v_cruise = sc.v_drive * sc.dir;
+      const JerkSamplerReg& Q = q_s[j];
       const int s6 = Q.s[6];
       const int cr_lo = Q.s[2] + 1;
       const bool phase4 = Q.s[3] - Q.s[2] > 2;
@@ -352,14 +398,27 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_sample(DevState S) {
       double* out = ltt_sample_w(S, e, pend, 0) + j;  // sample i: out[i * 4J + {0, J, 2J, 3J}] = q, v, a, j
       const size_t stride = (size_t)4 * J;
       double a = a_0, v = v_0, q = q_0;
-      for (int i = 0; i < wlen; ++i) {
-        const double jj = jerk_reg_at(Q, i);
-        if (i < my_len) {
-          if (i == 0) {  // the first sample integrates unconditionally (:810-813)
+      for (int ch = 0; ch < nchunk; ++ch) {
+        if (warp == 1) {
+          if (ch + 1 < nchunk) produce(ch + 1);
+        } else if (jl) {
+          const double* jb = jbuf_s[ch & 1][j];
+          const int i0 = ch << 5;
+          const int n = (len - i0) < 32 ? (len - i0) : 32;
+          int u = 0;
+          if (ch == 0) {  // the first sample integrates unconditionally (:810-813)
+            const double jj = jb[0];
             a = a_0 + ts * jj;
             v = v_0 + ts * a;
             q = q_0 + ts * v;
-          } else {
+            out[0] = q; out[J] = v; out[2 * J] = a; out[3 * J] = jj;
+            out += stride;
+            u = 1;
+          }
+#pragma unroll 4
+          for (; u < n; ++u) {
+            const int i = i0 + u;
+            const double jj = jb[u];
             const bool live = i <= s6;
             const bool cruise = (unsigned)(i - cr_lo) < cr_span;
             const double an = a + ts * jj;
@@ -368,30 +427,26 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_sample(DevState S) {
             vn = live ? vn : 0.0;
             v = cruise ? v_cruise : vn;
             q = q + ts * v;
+            out[0] = q; out[J] = v; out[2 * J] = a; out[3 * J] = jj;
+            out += stride;
           }
-          out[0] = q;
-          out[J] = v;
-          out[2 * J] = a;
-          out[3 * J] = jj;
-          out += stride;
         }
+        __syncthreads();
       }
-      if (my_len > 0) in = !(q < c.q_min[j] || q > c.q_max[j]);  // (:59-61)
+      if (jl) in = !(q < c.q_min[j] || q > c.q_max[j]);  // (:59-61)
     }
-    // every joint of the env must end inside its limits
-    bool all_in = true;
-    for (int k = 0; k < J; ++k) {
-      const int in_k = __shfl_sync(full, in ? 1 : 0, seg0 + k);  // (never behind a short-circuit: every lane must shuffle)
-      all_in = all_in && in_k != 0;
+    if (warp == 0) {
+      const bool all_in = __all_sync(full, in);  // every joint of the env must end inside its limits
+      if (lane == 0) {
+        // verdict for k_pfl_ltt / k_replan_tail: bit 0 = trajectory written and valid, bit 1 = longer than the slot;
+        // slowest = its length
+        PlanHead o = head;
+        o.ok = ((ok && all_in) ? 1 : 0) | (int)trunc;
+        o.slowest = len;
+        S.plan_head[idx] = o;
+      }
     }
-    if (act && j == 0) {
-      // verdict for k_pfl_ltt / k_replan_tail: bit 0 = trajectory written and valid, bit 1 = longer than the slot;
-      // slowest = its length
-      PlanHead o = S.plan_head[idx];
-      o.ok = ((ok && all_in) ? 1 : 0) | (int)trunc;
-      o.slowest = len;
-      S.plan_head[idx] = o;
-    }
+    __syncthreads();  // idx_s, q_s, len_s are re-used by the next env
   }
 }
 

@@ -47,22 +47,26 @@ __global__ void __launch_bounds__(kTickBlock) k_plan(DevState S, const double* _
 // determineNextMotion + setpoint write-out + statistics. Also re-arms the replan list for the next tick.
 __global__ void __launch_bounds__(kTickBlock)
     k_select(DevState S, double* q, double* dq, double* ddq, double* dddq, uint8_t* is_safe, uint8_t* branch,
-             uint32_t* status) {
-  constexpr int NC = 9;
+             uint32_t* status, int which) {
+  // which: -1 = every env; 0 = the envs that did not replan this tick (runs while the replan chain is still busy: they are
+  // 96 % of the batch and nothing of theirs depends on it); 1 = the replanned envs, and the tick's last launch (re-arms the
+  // work counters).
+  constexpr int NC = 10;
   __shared__ unsigned long long s_cnt[NC];
   __shared__ double s_min;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (threadIdx.x < NC) s_cnt[threadIdx.x] = 0ull;
   if (threadIdx.x == 0) s_min = INFINITY;
   __syncthreads();
-  if (e == 0) {
+  if (e == 0 && which != 0) {
     *S.replan_count = 0;
     for (int k = 0; k < N_CTR; ++k) S.replan_ctr[k] = 0;
     S.verify_cnt[0] = S.verify_cnt[1] = 0;
   }
-  unsigned long long my[NC] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum, truncated
+  unsigned long long my[NC] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum, truncated, steps
   double my_min = INFINITY;
-  if (e < S.N) {
+  if (e < S.N && (which < 0 || (int)S.replan_mark[e] == which)) {
+    my[9] = 1;
     const HrgConfig& c = *S.cfg;
     uint32_t f = S.flags[e];
     select_env(S, c, e, f, q, dq, ddq, dddq);
@@ -106,10 +110,8 @@ __global__ void __launch_bounds__(kTickBlock)
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-      int n_here = S.N - blockIdx.x * blockDim.x;
-      if (n_here > (int)blockDim.x) n_here = blockDim.x;
       unsigned long long* g = reinterpret_cast<unsigned long long*>(S.stats);
-      atomicAdd(&g[0], (unsigned long long)n_here);
+      if (s_cnt[9]) atomicAdd(&g[0], s_cnt[9]);
       for (int k = 0; k < 8; ++k)
         if (s_cnt[k]) atomicAdd(&g[1 + k], s_cnt[k]);
       if (s_cnt[8]) atomicAdd(reinterpret_cast<unsigned long long*>(&S.stats->n_ltt_truncated), s_cnt[8]);

@@ -84,6 +84,53 @@ HRG_HD double opt_cached_root(const LtpLimits& L, OptRootCache* c, bool key_ok, 
   return r;
 }
 
+// Coefficients of the two quartics (:246-261 and :301-321); v_0 / a_0 already mirrored for dir < 0.
+HRG_HD void opt_quartic_coef(const LtpLimits& L, int which, double q_goal, double q_0, double v_0, double a_0, double dir,
+                             double* A /*[5]*/) {
+  const double jm = L.j_max, am = L.a_max;
+  if (which == 0) {
+    A[0] = 12;
+    A[1] = 0;
+    A[2] = -24 * sq(a_0) + 48 * jm * v_0;
+    A[3] = 48 * dir * sq(jm) * q_0 - 48 * dir * sq(jm) * q_goal + 16 * cube(a_0) - 48 * a_0 * jm * v_0;
+    A[4] = -3 * pow4(a_0) + 12.0 * sq(a_0) * jm * v_0 - 12.0 * sq(jm) * sq(v_0);
+  } else {
+    A[0] = 12;
+    A[1] = -24 * am;
+    A[2] = -12.0 * sq(a_0) + 12.0 * sq(am) + 24 * jm * v_0;
+    A[3] = 0;
+    A[4] = 24 * dir * sq(jm) * q_0 * am - 24 * dir * sq(jm) * q_goal * am + 3 * pow4(a_0) + 8 * cube(a_0) * am +
+           6 * sq(a_0) * sq(am) - 12.0 * sq(a_0) * jm * v_0 - 24 * a_0 * jm * v_0 * am - 12.0 * sq(am) * jm * v_0 +
+           12.0 * sq(jm) * sq(v_0);
+  }
+}
+
+// Solves quartic `which` of optSwitchTimes for the inputs (q_goal, q_0, v_0, a_0) AHEAD of the call, whether or not the
+// call will reach the branch that needs it: the head of optSwitchTimes (:95-112) up to dir and the mirrored v_0 / a_0,
+// then the same coefficients and the same solver as the branch itself, so the cached root has the bits the branch would
+// compute. Lets every lane of a warp run its eigen-solve at ONE program point (converged) instead of wherever its
+// branches lead it.
+HRG_HD void opt_prefill_root(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, int which,
+                             OptRootCache& c) {
+  if (!(c.have & 4)) {
+    c.q_goal = q_goal; c.q_0 = q_0; c.v_0 = v_0; c.a_0 = a_0;
+    c.have |= 4;
+  }
+  double t[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  double q_stop = 0, dir;
+  ltp_opt_braking(L, v_0, a_0, q_stop, t, dir);
+  const double q_diff = q_goal - (q_0 + q_stop);
+  dir = isign(q_diff);
+  if (dir < 0) {
+    v_0 = -v_0;
+    a_0 = -a_0;
+  }
+  double A[5];
+  opt_quartic_coef(L, which, q_goal, q_0, v_0, a_0, dir, A);
+  c.root[which] = smallest_positive_real_root(L, A, 5);
+  c.have |= 1 << which;
+}
+
 // optSwitchTimes (LTP/src/long_term_planner.cc:82-353). Returns the reference's bool; T = cumulative switch times.
 HRG_HD_CALL bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double v_drive,
                                  double* T, double& dir, int& mod_jerk_profile, OptRootCache* cache = nullptr) {
@@ -188,11 +235,7 @@ HRG_HD_CALL bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double 
     if (t[5] < -eps || t[1] < -eps) {
       {
         double A[5];
-        A[0] = 12;
-        A[1] = 0;
-        A[2] = -24 * sq(a_0) + 48 * jm * v_0;
-        A[3] = 48 * dir * sq(jm) * q_0 - 48 * dir * sq(jm) * q_goal + 16 * cube(a_0) - 48 * a_0 * jm * v_0;
-        A[4] = -3 * pow4(a_0) + 12.0 * sq(a_0) * jm * v_0 - 12.0 * sq(jm) * sq(v_0);
+        opt_quartic_coef(L, 0, q_goal, q_0, v_0, a_0, dir, A);
         root = opt_cached_root(L, cache, key_ok, 0, A);
       }
       t[0] = (2.0 * sq(root) - 4 * a_0 * root + sq(a_0) - 2.0 * v_0 * jm) / (4 * jm * root);
@@ -221,13 +264,7 @@ HRG_HD_CALL bool ltp_opt_switch_times(const LtpLimits& L, double q_goal, double 
       if (t[6] * jm > am) {  // phase 6 exists (:299-333)
         t[6] = am / jm;
         double A[5];
-        A[0] = 12;
-        A[1] = -24 * am;
-        A[2] = -12.0 * sq(a_0) + 12.0 * sq(am) + 24 * jm * v_0;
-        A[3] = 0;
-        A[4] = 24 * dir * sq(jm) * q_0 * am - 24 * dir * sq(jm) * q_goal * am + 3 * pow4(a_0) + 8 * cube(a_0) * am +
-               6 * sq(a_0) * sq(am) - 12.0 * sq(a_0) * jm * v_0 - 24 * a_0 * jm * v_0 * am - 12.0 * sq(am) * jm * v_0 +
-               12.0 * sq(jm) * sq(v_0);
+        opt_quartic_coef(L, 1, q_goal, q_0, v_0, a_0, dir, A);
         root = opt_cached_root(L, cache, key_ok, 1, A);
         t[0] = (root - a_0 - am) / jm;
         t[4] = (a_0 + am) / jm + t[0];

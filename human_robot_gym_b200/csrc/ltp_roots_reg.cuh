@@ -13,6 +13,9 @@
 namespace hrg {
 
 #define HRG_RR_UNROLL _Pragma("unroll")
+#if defined(HRG_RR_TRACE) && !defined(__CUDA_ARCH__)
+static long long hrg_rr_trace_hist[8][64];  // [N][Francis step number] -> how many solves reached it
+#endif
 
 // Householder vector of (x0, x1, x2) / (x0, x1): mk_householder (ltp_math.cuh) for m = 3 / m = 2.
 HRG_HD void rr_householder3(double x0, double x1, double x2, double& e0, double& e1, double& tau, double& beta) {
@@ -174,6 +177,9 @@ HRG_HD void rr_real_schur(double (&T)[N][N]) {
       }
       iter++;
       total_iter++;
+#if defined(HRG_RR_TRACE) && !defined(__CUDA_ARCH__)
+      ++hrg_rr_trace_hist[N][total_iter < 63 ? total_iter : 63];  // host-only instrumentation (tests/host_emul)
+#endif
       if (total_iter > max_iters) break;
       // im: two consecutive small sub-diagonal elements
       int im = il;

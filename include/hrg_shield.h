@@ -300,6 +300,10 @@ int64_t hrg_human_launch_count(const HrgHuman* h);
  * gflops_host: achieved GFLOP/s (FMA = 2 flop); ginst_host (may be NULL): 1e9 thread-level FP64 instructions per second -
  * the unit of ncu's smsp__sass_thread_inst_executed_op_d{add,mul,fma}_pred_on; ms_host (may be NULL): best launch time. */
 int hrg_microbench_fp64(int device, int mode, int iters, double* gflops_host, double* ginst_host, double* ms_host);
+/* Dependent-issue latency in SM cycles of one FP64 operation in a chain, one warp alone on its SM: cycles_host[6] = DADD, DMUL,
+ * DFMA, IEEE division (+ one DADD), sqrt (+ one DADD), DADD + compare + select. The replan chain of a tick is a few hundred
+ * warps running dependent FP64 code, so these - not the throughput peaks - bound it. */
+int hrg_microbench_fp64_latency(int device, double* cycles_host);
 
 /* ---- per-stage entry points (parity tests + ncu); all DEVICE pointers --------------------------------------- */
 /* capsule_capsule_dist (RL/include/intersections.hpp:105-124) for n independent pairs: c1,c2 [n,7] -> dist [n]. */

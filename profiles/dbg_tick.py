@@ -1,23 +1,16 @@
-import sys, faulthandler, time, os
+"""Debug aid: a short closed loop on the GPU with a watchdog (dumps the Python stack and exits if a kernel hangs).
+  [HRG_DEBUG_SYNC=1] python profiles/dbg_tick.py <robot> <n_envs> [ticks]"""
+import faulthandler
+import os
+import sys
+
 sys.path.insert(0, os.getcwd())
 faulthandler.dump_traceback_later(70, exit=True)
-import numpy as np, torch
-from tests import parity_util as pu
-from human_robot_gym_b200.batched import BatchedSafetyShield
-from human_robot_gym_b200.config import ShieldConfig
-from human_robot_gym_b200.synthetic import SyntheticScenario
-robot=sys.argv[1]; n=int(sys.argv[2])
-files=pu.default_files(robot)
-sc=ShieldConfig.from_files(0.004,*files)
-scen=SyntheticScenario(n, pu.mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, 1002)
-g=BatchedSafetyShield(n,0.004,*files,init_qpos=scen.init_q,device="cuda:0",ltt_capacity=1024)
-phase=np.arange(n)%25
-for k in range(80):
-    t=k*0.004
-    g.humanMeasurement(torch.from_numpy(scen.keypoints(t)),t)
-    gm=phase==(k%25)
-    g.newLongTermTrajectory(torch.from_numpy(scen.next_goal(gm)),env_mask=torch.from_numpy(gm))
-    g.step(t)
-    torch.cuda.synchronize()
-    print("tick",k,"ok", g.stats()["n_replan"], flush=True)
+from tests import parity_util as pu  # noqa: E402
+
+robot, n = sys.argv[1], int(sys.argv[2])
+ticks = int(sys.argv[3]) if len(sys.argv) > 3 else 80
+res = pu.closed_loop_compare(pu.default_files(robot), n_envs=n, ticks=ticks, seed=1002, store_capsules=False)
+print(res)
+pu.assert_parity(res)
 print("done")

@@ -297,6 +297,14 @@ int emul_ltp_plan(const HrgConfig* cfg, const double* goal, const double* q0, co
                   double* traj, int cap) {
   return ltp_plan_env_seq(*cfg, goal, q0, v0, a0, traj, cap);
 }
+#if defined(HRG_RR_TRACE)
+void emul_rr_trace(long long* out /*[8][64]*/, int clear) {
+  for (int i = 0; i < 8 * 64; ++i) {
+    out[i] = (&hrg_rr_trace_hist[0][0])[i];
+    if (clear) (&hrg_rr_trace_hist[0][0])[i] = 0;
+  }
+}
+#endif
 double emul_poly_root(const double* coef, int ncoef) { LtpLimits L{}; return smallest_positive_real_root(L, coef, ncoef); }
 // the register-resident solver the device uses for one-problem-per-lane kernels (csrc/ltp_roots_reg.cuh), degrees 4..6
 double emul_poly_root_reg(const double* coef, int ncoef) { return rr_has_degree(ncoef) ? rr_root(coef, ncoef) : NAN; }
