@@ -145,6 +145,7 @@ SYMBOLS = {
     "hrg_stage_plan_safety_shield": (C.c_int, [C.c_double, C.c_int, _dp, _u8p, _dp, _dp, _vp]),
     "hrg_stage_ltp_plan": (C.c_int, [C.POINTER(HrgConfig), C.c_int, _dp, _dp, _dp, _dp, _dp, _i32p, C.c_int, _vp]),
     "hrg_stage_reach_verify": (C.c_int, [C.POINTER(HrgConfig), C.c_int] + [_dp] * 8 + [_dp, _dp, _dp, _u8p, _vp]),
+    "hrg_stage_reach_verify_noalloc": (C.c_int, [C.POINTER(HrgConfig), C.c_int] + [_dp] * 8 + [_dp, _dp, _dp, _u8p, _vp]),
 }
 
 

@@ -595,3 +595,4 @@ int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_ho
 }  // extern "C"
 #include "hrg_shield_extra.cuh"
 #include "hrg_human.cuh"
+#include "hrg_noalloc.cuh"

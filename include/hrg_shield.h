@@ -324,6 +324,23 @@ int hrg_stage_reach_verify(const HrgConfig* cfg, int n, const double* base_pose,
                            const double* kp_pos, const double* kp_vel, double* robot, double* human, double* min_dist,
                            uint8_t* is_safe, void* stream);
 
+/* hrg_stage_reach_verify without any allocation. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). Same arguments and results as hrg_stage_reach_verify (bit-identical); the packed scratch state lives in a
+ * static __device__ array of HRG_NOALLOC_SCRATCH_BYTES inside the library, which every GPU that loads the library holds
+ * until exit. Limit: sizeof(HrgConfig) + n * (8 * (17 + 3J + 6K) + 4) bytes must fit, i.e. n <= 6 041 for Schunk (J 6) /
+ * 5 938 for Panda (J 7) with the 23-keypoint mujoco_mocap human, 2 463 at HRG_MAX_JOINTS / HRG_MAX_KEYPOINTS; a larger n is
+ * rejected with HRG_EINVAL and a message naming the limit (hrg_last_error). Calls no cudaMalloc, cudaFree or allocating
+ * library routine; launches four kernels on `stream` on the CURRENT device and, unlike hrg_stage_reach_verify, does not
+ * synchronise. All calls on a device share the one array: calls that overlap on the GPU (different streams, or the
+ * same stream from two threads without ordering) race - serialise them; the result fields are cleared at the start of
+ * every call, the input fields are fully rewritten. */
+#define HRG_NOALLOC_SCRATCH_BYTES (8u << 20)
+int hrg_stage_reach_verify_noalloc(const HrgConfig* cfg, int n, const double* base_pose, const double* q_start,
+                                   const double* q_goal, const double* s_diff, const double* t_reach,
+                                   const double* alpha_i, const double* kp_pos, const double* kp_vel, double* robot,
+                                   double* human, double* min_dist, uint8_t* is_safe, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
