@@ -30,7 +30,7 @@ GOAL_PERIOD = 25  # shield ticks per policy step (human_env.yaml:21,35)
 METRIC = "shield-steps/sec"
 
 
-def parse_args():
+def parse_args(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
@@ -53,7 +53,7 @@ def parse_args():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="strong: --envs is the TOTAL number of shields, sharded over the GPUs (the headline then is the "
                          "strong-scaling figure)")
-    return ap.parse_args()
+    return ap.parse_args(argv)
 
 
 def workload_name(args, sc):
