@@ -29,7 +29,7 @@ _I = C.c_int32
 class HrgConfig(C.Structure):
     """Mirror of `struct HrgConfig` (include/hrg_shield.h)."""
     _fields_ = [
-        ("nb_joints", _I), ("n_keypoints", _I), ("n_bodies", _I), ("n_ext", _I), ("ltt_capacity", _I), ("reserved0", _I),
+        ("nb_joints", _I), ("n_keypoints", _I), ("n_bodies", _I), ("n_ext", _I), ("ltt_capacity", _I), ("root_mode", _I),
         ("sample_time", _D), ("max_s_stop", _D), ("v_safe", _D), ("alpha_i_max", _D), ("secure_radius", _D),
         ("meas_err_pos", _D), ("meas_err_vel", _D), ("delay", _D),
         ("q_min", _D * MAX_JOINTS), ("q_max", _D * MAX_JOINTS), ("v_max", _D * MAX_JOINTS), ("a_max", _D * MAX_JOINTS),
@@ -71,6 +71,7 @@ def make_cfg(sc: ShieldConfig, ltt_capacity: int = 1024) -> HrgConfig:
             raise ValueError(f"trajectory config: {name} shorter than nb_joints")
     c = HrgConfig()
     c.nb_joints, c.n_keypoints, c.n_bodies, c.n_ext, c.ltt_capacity = J, h.n_keypoints, h.n_bodies, h.n_ext, int(ltt_capacity)
+    c.root_mode = int(os.environ.get("HRG_ROOT_MODE", DEFAULT_ROOT_MODE))
     c.sample_time, c.max_s_stop, c.v_safe, c.alpha_i_max = sc.sample_time, t.max_s_stop, t.v_safe, t.alpha_i_max
     c.secure_radius = r.secure_radius
     c.meas_err_pos, c.meas_err_vel, c.delay = h.measurement_error_pos, h.measurement_error_vel, h.delay
@@ -147,6 +148,11 @@ SYMBOLS = {
     "hrg_stage_reach_verify": (C.c_int, [C.POINTER(HrgConfig), C.c_int] + [_dp] * 8 + [_dp, _dp, _dp, _u8p, _vp]),
     "hrg_stage_reach_verify_noalloc": (C.c_int, [C.POINTER(HrgConfig), C.c_int] + [_dp] * 8 + [_dp, _dp, _dp, _u8p, _vp]),
 }
+
+
+# planner root finder (HrgConfig.root_mode): 1 = derivative-chain finder with the exact QR iteration as the arbiter of close
+# calls, 0 = the exact QR iteration for every polynomial. HRG_ROOT_MODE overrides.
+DEFAULT_ROOT_MODE = 1
 
 
 class ShieldLibraryError(RuntimeError):

@@ -84,7 +84,7 @@ struct HrgShield {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_meas = nullptr;
   bool overlap = true;
   bool debug_sync = false;
-  int deep_per_warp = 4;  // tasks per warp of k_replan_deep (HRG_DEEP_PER_WARP)
+  int deep_per_warp = 2;  // deep-list joints per warp of k_replan_deep, <= 4 (HRG_DEEP_PER_WARP)
   int plan_envs_per_warp = 2;  // envs per warp of k_replan_plan, <= 16 / J (HRG_PLAN_ENVS_PER_WARP)
   bool cascade = true;  // verification cascade for pass 0 (HRG_NO_CASCADE=1 or stored capsules: full kernel)
   // optional per-kernel timing of the tick (bench.py's roofline leg): one event after every launch of a step
@@ -245,7 +245,7 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
     if (const char* v = getenv("HRG_PLAN_ENVS_PER_WARP"))
       if (atoi(v) >= 1 && atoi(v) <= 16 / J) h->plan_envs_per_warp = atoi(v);
     if (const char* v = getenv("HRG_DEEP_PER_WARP"))
-      if (atoi(v) >= 1 && atoi(v) <= 32) h->deep_per_warp = atoi(v);
+      if (atoi(v) >= 1 && atoi(v) <= 4) h->deep_per_warp = atoi(v);
   }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
@@ -456,7 +456,7 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
     // only bound residency (one warp per block, so that the few hundred busy warps spread over all schedulers)
     const int J = s->S.J;
     const int cap = s->sm_count * 16;
-    int g_plan = grid_for(N, s->plan_envs_per_warp), g_samp = N, g_deep = grid_for(N * J * 6, s->deep_per_warp);
+    int g_plan = grid_for(N, s->plan_envs_per_warp), g_samp = N, g_deep = grid_for(N * J, s->deep_per_warp);
     if (g_plan > cap) g_plan = cap;
     if (g_samp > cap) g_samp = cap;
     if (g_deep > cap) g_deep = cap;
@@ -464,24 +464,28 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
     mark(HRG_PROF_PLAN_LTT);
     k_replan_deep<<<g_deep, kReplanBlock, 0, rs>>>(s->S, s->deep_per_warp);
     mark(HRG_PROF_DEEP);
-    k_replan_sample<<<g_samp, kSampleBlock, 0, rs>>>(s->S);
-    mark(HRG_PROF_SAMPLE);
-    if (s->pfl) {
-      int pgrid = s->sm_count * 8;
-      if (pgrid > N) pgrid = N;
-      k_pfl_ltt<<<pgrid, kPflBlock, 0, rs>>>(s->S);
-      mark(HRG_PROF_PFL);
-      s->launches++;
-    }
     if (fork && kp) {
-      // k_replan_tail (plan_env) reads last_meas: k_measure (main stream) must be through by then
+      // the tail of the chain (plan_env) reads last_meas: k_measure (main stream) must be through by then
       k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
       s->launches++;
       keep(cudaEventRecord(s->ev_meas, st));
       keep(cudaStreamWaitEvent(s->side, s->ev_meas, 0));
     }
-    k_replan_tail<<<grid_for(N, 128), 128, 0, rs>>>(s->S, t);
-    mark(HRG_PROF_TAIL);
+    if (s->pfl) {
+      k_replan_sample<false><<<g_samp, kSampleBlock, 0, rs>>>(s->S, t);
+      mark(HRG_PROF_SAMPLE);
+      int pgrid = s->sm_count * 8;
+      if (pgrid > N) pgrid = N;
+      k_pfl_ltt<<<pgrid, kPflBlock, 0, rs>>>(s->S);
+      mark(HRG_PROF_PFL);
+      k_replan_tail<<<grid_for(N, 128), 128, 0, rs>>>(s->S, t);
+      mark(HRG_PROF_TAIL);
+      s->launches += 2;
+    } else {
+      // SSM / OFF handles: the env tail runs at the end of the sampler (one launch and one kernel boundary less)
+      k_replan_sample<true><<<g_samp, kSampleBlock, 0, rs>>>(s->S, t);
+      mark(HRG_PROF_SAMPLE);
+    }
   }
   if (fork) {
     keep(cudaEventRecord(s->ev_join, s->side));
@@ -498,7 +502,7 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
   mark(HRG_PROF_VERIFY_P1);
   k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status, fork ? 1 : -1);
   mark(HRG_PROF_SELECT);
-  s->launches += 9;
+  s->launches += 8;
   keep(cudaGetLastError());
   if (err != cudaSuccess) return fail(HRG_ECUDA, "hrg_shield_step: launch failed", err);
   return HRG_OK;
@@ -596,3 +600,14 @@ int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_ho
 #include "hrg_shield_extra.cuh"
 #include "hrg_human.cuh"
 #include "hrg_noalloc.cuh"
+#if defined(HRG_TASK_TRACE)
+// profiling builds only (profiles/build_trace.sh): copies the task trace [4][kTraceTasks][4] u64 to the host and clears it
+extern "C" int hrg_trace_read(unsigned long long* dst_host) {
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(dst_host, hrg::g_task_trace, sizeof(hrg::g_task_trace)));
+  void* p = nullptr;
+  CK(cudaGetSymbolAddress(&p, hrg::g_task_trace));
+  CK(cudaMemset(p, 0, sizeof(hrg::g_task_trace)));
+  return HRG_OK;
+}
+#endif

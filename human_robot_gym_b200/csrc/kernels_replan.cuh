@@ -26,6 +26,7 @@
 #include "ltp_math.cuh"
 #include "step_logic.cuh"
 #include "pfl_math.cuh"
+#include "task_trace.cuh"
 
 namespace hrg {
 
@@ -36,6 +37,7 @@ __device__ __forceinline__ LtpLimits joint_limits(const HrgConfig& c, int j) {
   LtpLimits L;
   L.v_max = c.v_max[j]; L.a_max = c.a_max_ltt[j]; L.j_max = c.j_max_ltt[j]; L.t_sample = c.sample_time;
   L.mat = nullptr;
+  L.root_mode = c.root_mode;
   return L;
 }
 
@@ -91,6 +93,7 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S, int en
   for (;;) {
     const int base = fetch_warp_tasks(S.replan_ctr + CTR_PLAN, E, count, lane);
     if (base < 0) break;
+    HRG_TRACE_T0();
     const int idx = base + sub;
     const bool act = sub < E && idx < count;
     const LtpLimits L = joint_limits(c, act ? j : 0);
@@ -170,6 +173,7 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S, int en
         if (take1) T[k] = t1;
       }
     }
+    HRG_TRACE_TASK(0, base / E, 0);
     if (!act || half != 0) continue;  // (the other lanes wait in the next fetch's shuffle)
     opt.len = h.ok;
     PlanRec sc = opt;
@@ -194,51 +198,89 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S, int en
   }
 }
 
-// One (deep-list slot, polynomial candidate) task per lane. Tasks are ordered by candidate - the degree-6 one first, it
-// has the longest solve - so that the 32 lanes of a warp run the same solver.
-// `per_warp` <= 32 tasks per warp: the lanes of a warp run the solver's three-way case split and its unrolled row / column
-// positions one after the other wherever they disagree, so fewer problems per warp = a shorter chain per warp, and the GPU
-// has warps to spare.
-__global__ void __launch_bounds__(kReplanBlock) k_replan_deep(DevState S, int per_warp) {
+// One deep-list joint per 8-lane group, lane c of the group = polynomial candidate c + 2 in the reference's order (:449-629,
+// degrees 4, 4, 5, 4, 4, 6); `joints_per_warp` <= 4 groups are used. The reference walks the six candidates one after the
+// other and takes the first one it accepts; here all six are evaluated side by side:
+//   A. every lane finds its root with the derivative-chain finder (ltp_roots_fast.cuh) and, where that verdict is
+//      unambiguous, runs the optSwitchTimes trial;
+//   B. a candidate whose root is a close call (margin below kRootMargin: the QR iteration's rounding decides, typically a
+//      start from rest, whose polynomials have a multiple root at 0) is settled by the exact QR restatement - but only if it
+//      comes BEFORE the first candidate already accepted in A, since the reference never gets to the later ones.
+// With root_mode 0 every candidate is a close call by definition and B is the whole kernel.
+__global__ void __launch_bounds__(kReplanBlock) k_replan_deep(DevState S, int joints_per_warp) {
   const HrgConfig& c = *S.cfg;
+  const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int J = S.J, N = S.N;
   const int n_deep = S.replan_ctr[CTR_DEEP_COUNT];
-  const int ntask = n_deep * 6;
+  const int grp = lane >> 3, ci = lane & 7;
   for (;;) {
-    const int base = fetch_warp_tasks(S.replan_ctr + CTR_DEEP, per_warp, ntask, lane);
+    const int base = fetch_warp_tasks(S.replan_ctr + CTR_DEEP, joints_per_warp, n_deep, lane);
     if (base < 0) break;
-    const int dt = base + lane;
-    if (lane >= per_warp || dt >= ntask) continue;
-    const int cls = dt / n_deep, slot = dt - cls * n_deep;
-    const int cand = cls == 0 ? 7 : (cls == 1 ? 4 : (cls < 4 ? cls : cls + 1));  // 7, 4, 2, 3, 5, 6
-    const int task = S.deep_list[slot];
-    const int idx = task / J, j = task - idx * J;
-    const int e = S.replan_list[idx];
-    const PlanHead h = S.plan_head[idx];
-    const PlanRec opt = S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j];
-    const LtpLimits L = joint_limits(c, j);
-    const double q_0 = cur_at(S, j, e), v_raw = cur_at(S, J + j, e), a_raw = cur_at(S, 2 * J + j, e);
-    const double q_goal = S.goal_q[(size_t)j * N + e];
-    OptRootCache rc;
-    cache_from_rec(opt, q_goal, q_0, v_raw, a_raw, rc);
-    double v_0 = v_raw, a_0 = a_raw;
-    if (opt.dir < 0) {
-      v_0 = -v_0;
-      a_0 = -a_0;
-    }
-    const double v_orig = opt.dir * v_0, a_orig = opt.dir * a_0;
+    HRG_TRACE_T0();
+    const int slot = base + grp;
+    const bool act = grp < joints_per_warp && slot < n_deep && ci < 6;
+    const int cand = ci + 2;
     PlanRec r;
     ltp_zero7(r.T);
-    r.dir = opt.dir;
-    r.mod = opt.mod;
+    r.dir = 0.0; r.v_drive = 0.0; r.mod = 0; r.len = 0;
     r.root[0] = r.root[1] = 0.0; r.have = 0; r.pad = 0;
+    LtpLimits L = joint_limits(c, 0);
+    OptRootCache rc;
+    opt_cache_clear(rc);
     double A[7];
-    int ncoef;
-    ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, opt.dir, h.t_required, A, ncoef);
-    r.v_drive = ltp_scaling_vdrive(L, cand, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
-    r.len = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, r.v_drive, h.t_required, r.T, r.mod, &rc) ? 1 : 0;
-    S.deep_res[(size_t)slot * 6 + (cand - 2)] = r;
+    int ncoef = 5;
+    double q_0 = 0.0, q_goal = 0.0, v_0 = 0.0, a_0 = 0.0, v_orig = 0.0, a_orig = 0.0, t_required = 0.0;
+    bool need_qr = false;
+    if (act) {
+      const int task = S.deep_list[slot];
+      const int idx = task / J, j = task - idx * J;
+      const int e = S.replan_list[idx];
+      const PlanHead h = S.plan_head[idx];
+      const PlanRec opt = S.plan_opt[(size_t)idx * HRG_MAX_JOINTS + j];
+      L = joint_limits(c, j);
+      q_0 = cur_at(S, j, e);
+      const double v_raw = cur_at(S, J + j, e), a_raw = cur_at(S, 2 * J + j, e);
+      q_goal = S.goal_q[(size_t)j * N + e];
+      cache_from_rec(opt, q_goal, q_0, v_raw, a_raw, rc);
+      v_0 = v_raw;
+      a_0 = a_raw;
+      if (opt.dir < 0) {
+        v_0 = -v_0;
+        a_0 = -a_0;
+      }
+      v_orig = opt.dir * v_0;
+      a_orig = opt.dir * a_0;
+      t_required = h.t_required;
+      r.dir = opt.dir;
+      r.mod = opt.mod;
+      ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, opt.dir, t_required, A, ncoef);
+      // A.
+      need_qr = true;
+      if (L.root_mode == 1) {
+        double margin;
+        const double root = fr_root_mixed(A, ncoef, margin);
+        if (margin >= kRootMargin) {
+          need_qr = false;
+          r.v_drive = ltp_scaling_vdrive(L, cand, root, v_0, a_0);
+          r.len = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, r.v_drive, t_required, r.T, r.mod, &rc) ? 1 : 0;
+        } else if (ltp_cand_rejected_from_rest(L, cand, A, ncoef, q_goal, q_0, v_0, a_0, v_orig, a_orig, t_required, &rc)) {
+          need_qr = false;  // a start from rest: rejected whichever way the QR iteration's rounding falls (ltp_scaling.cuh)
+          ltp_zero7(r.T);
+          r.mod = opt.mod;
+        }
+      }
+    }
+    // B.
+    const unsigned acc = (__ballot_sync(full, act && !need_qr && r.len != 0) >> (grp * 8)) & 0x3fu;
+    const int first_acc = acc ? (__ffs(acc) - 1) : 6;
+    if (act && need_qr && ci < first_acc) {
+      r.v_drive = ltp_scaling_vdrive(L, cand, rr_root(A, ncoef), v_0, a_0);
+      r.len = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, r.v_drive, t_required, r.T, r.mod, &rc) ? 1 : 0;
+    }
+    if (act) S.deep_res[(size_t)slot * 6 + ci] = r;
+    __syncwarp(full);
+    HRG_TRACE_TASK(1, base / joints_per_warp, n_deep);
   }
 }
 
@@ -304,42 +346,119 @@ __device__ __forceinline__ double jerk_reg_at(const JerkSamplerReg& S, int i) {
   return j;
 }
 
-// One env per block of two warps. getTrajectory has two parts of very different shape: the jerk of sample i of joint r
-// (a 7-way range test plus up to twelve sub-sample corrections, ~90 instructions, independent for every (r, i)), and the
-// reference's sequential recurrence a += ts j, v += ts a, q += ts v (a dozen instructions that cannot be reordered without
-// changing roundings). The kernel takes as long as the LONGEST trajectory of the tick, so only the recurrence may sit on the
-// dependent chain: warp 1 produces the jerk of chunk c + 1 (lane = sample, one joint after the other) into one half of a
-// double buffer while lanes 0..J-1 of warp 0 integrate chunk c out of the other half and stream the samples out.
-constexpr int kSampleBlock = 64;
-__global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S) {
+// Install the new trajectory of one replanning env (safety_shield.cc:593-604, long_term_traj.h:108-116) and run the rest of
+// the env's step up to the reach / verify hand-over. The envs that do not replan got this from k_plan while the chain was
+// running. `h` = the sampler's verdict (ok bit 0: trajectory valid, bit 1: longer than the slot; slowest = its length).
+__device__ __forceinline__ void replan_tail_env(const DevState& S, const HrgConfig& c, int e, const PlanHead& h, double t) {
+  const int J = S.J, N = S.N;
+  uint32_t f = S.flags[e];
+  const int pend = (f & F_LIVE_SLOT) ? 0 : 1;
+  const bool ok = (h.ok & 1) != 0;
+  uint32_t status = HRG_ST_REPLANNED;
+  if (h.ok & 2) status |= HRG_ST_LTT_TRUNCATED;
+  const bool pfl = ((f & F_TYPE_MASK) >> F_TYPE_SHIFT) == HRG_SHIELD_PFL;
+  if (ok) {
+    double cq[HRG_MAX_JOINTS];  // all loads first: a store in between would serialise them
+#pragma unroll
+    for (int j = 0; j < HRG_MAX_JOINTS; ++j)
+      if (j < J) cq[j] = cur_at(S, j, e);
+    const int sd = S.path_sd[e];
+    const double ps = S.path_s[e];
+#pragma unroll
+    for (int j = 0; j < HRG_MAX_JOINTS; ++j)
+      if (j < J) {
+        S.replan_q[(size_t)j * N + e] = cq[j];  // last_replan_start_motion_ = current_motion (:593)
+        // SSM / OFF: alpha_i_ = alpha_i_max (long_term_traj.h:108-116); PFL: written by k_pfl_ltt
+        if (!pfl) S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
+      }
+    S.ltt_len[(size_t)pend * N + e] = h.slowest;
+    S.ltt_cur[(size_t)pend * N + e] = 0;
+    S.ltt_start[(size_t)pend * N + e] = sd;
+    S.ltt_t0[(size_t)pend * N + e] = ps;
+    S.ltt_ts[(size_t)pend * N + e] = c.sample_time;
+    f |= F_NEW_LTT;
+    f &= ~F_NEW_LTT_PROCESSED;
+  } else {
+    f &= ~F_NEW_LTT;
+    status |= HRG_ST_REPLAN_FAILED;
+  }
+  f &= ~F_PENDING_REPLAN;
+  f |= status << F_STATUS_SHIFT;
+  plan_env(S, c, e, t, f);
+  S.flags[e] = f;
+}
+
+// The tail as a kernel of its own (thread per replanning env): PFL handles, whose k_pfl_ltt runs between the sampler and
+// the tail. SSM handles run it at the end of k_replan_sample<true>.
+__global__ void __launch_bounds__(128) k_replan_tail(DevState S, const double* __restrict__ t) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= *S.replan_count) return;
+  const int e = S.replan_list[idx];
+  replan_tail_env(S, *S.cfg, e, S.plan_head[idx], t[e]);
+}
+
+// What replan_tail_env / plan_env will read of env e, asked for ahead of time by all lanes of the env's warp (field-major
+// state: every field is its own cache line, and the tail is one lane chasing ~100 of them one after the other).
+__device__ __forceinline__ void prefetch_tail_inputs(const DevState& S, int e, int lane) {
+  const int J = S.J;
+  const size_t N = (size_t)S.N;
+  auto pf = [](const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); };
+  for (int k = lane; k < N_PATHS * PATH_FIELDS; k += 32) pf(S.paths + (size_t)k * N + e);
+  for (int k = lane; k < 4 * J + 1; k += 32) pf(S.cur + (size_t)k * N + e);
+  for (int k = lane; k < J; k += 32) pf(S.prev_dq + (size_t)k * N + e);
+  for (int k = lane; k < 2 * J; k += 32) pf(S.ltt_alpha + (size_t)k * N + e);
+  if (lane < 2) {
+    pf(S.ltt_len + (size_t)lane * N + e);
+    pf(S.ltt_cur + (size_t)lane * N + e);
+    pf(S.ltt_start + (size_t)lane * N + e);
+    pf(S.ltt_t0 + (size_t)lane * N + e);
+    pf(S.ltt_ts + (size_t)lane * N + e);
+  }
+  if (lane == 2) pf(S.path_s + e);
+  if (lane == 3) pf(S.path_sd + e);
+  if (lane == 4) pf(S.last_meas + e);
+}
+
+// One env per warp (one warp per block, so the blocks of a tick are all resident at once and spread over every
+// scheduler). getTrajectory has two parts of very different shape: the jerk of sample i of joint r - piecewise constant over
+// the seven phases plus up to twelve one-sample corrections - and the reference's sequential recurrence a += ts j,
+// v += ts a, q += ts v, which cannot be reordered without changing roundings. Per super-chunk of kSampleChunk samples the
+// warp first FILLS the jerk of every joint into shared memory phase by phase (all 32 lanes, a handful of instructions per
+// phase that touches the chunk - evaluating jerk_reg_at per sample, ~100 instructions each, made the earlier producer /
+// consumer forms throughput bound: 13 M warp instructions per tick), applies the corrections in the reference's order, and
+// then lanes 0..J-1 integrate the chunk and stream the samples out.
+constexpr int kSampleBlock = 32;
+constexpr int kSampleChunk = 128;
+template <bool TAIL>
+__global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S, const double* __restrict__ t) {
   __shared__ JerkSamplerReg q_s[HRG_MAX_JOINTS];
-  __shared__ double jbuf_s[2][HRG_MAX_JOINTS][33];
-  __shared__ int len_s[HRG_MAX_JOINTS];
-  __shared__ int idx_s;
+  __shared__ double jbuf_s[HRG_MAX_JOINTS][kSampleChunk + 1];  // + 1: the J consumer lanes read one column of it
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int lane = threadIdx.x & 31;
   const int J = S.J;
   const int count = *S.replan_count;
   for (;;) {
-    if (tid == 0) idx_s = atomicAdd(S.replan_ctr + CTR_SAMPLE, 1);
-    __syncthreads();
-    const int idx = idx_s;
+    int idx = 0;
+    if (lane == 0) idx = atomicAdd(S.replan_ctr + CTR_SAMPLE, 1);
+    idx = __shfl_sync(full, idx, 0);
     if (idx >= count) break;
+    HRG_TRACE_T0();
     const int e = S.replan_list[idx];
+    if (TAIL) prefetch_tail_inputs(S, e, lane);
     const int pend = (S.flags[e] & F_LIVE_SLOT) ? 0 : 1;
     const PlanHead head = S.plan_head[idx];
     bool ok = head.ok != 0;
-    const bool jl = warp == 0 && lane < J;  // the lane that owns joint `lane`
+    const bool jl = lane < J;  // the lane that owns joint `lane`
     const int j = lane < J ? lane : 0;
     const LtpLimits L = joint_limits(c, j);
     JointPlan sc;
     ltp_zero7(sc.T);
     sc.dir = 0.0; sc.v_drive = 0.0; sc.mod = 0;
     double q_0 = 0.0, v_0 = 0.0, a_0 = 0.0;
+    int len_j = 0;
     if (jl) {
       q_0 = cur_at(S, j, e); v_0 = cur_at(S, J + j, e); a_0 = cur_at(S, 2 * J + j, e);
-      int len_j = 0;
       if (ok) {
         PlanRec rec = S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j];
         if (rec.len < 0) {
@@ -365,11 +484,13 @@ __global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S) {
         len_j = rec.len;
         sampler_reg_init(L, sc, q_s[j]);
       }
-      len_s[j] = len_j;
     }
-    __syncthreads();
-    int len = 0;  // trajectory length of the env = max over its joints (:716-719)
-    for (int k = 0; k < J; ++k) len = len_s[k] > len ? len_s[k] : len;
+    __syncwarp(full);
+    int len = len_j;  // trajectory length of the env = max over its joints (:716-719)
+    for (int o = 16; o >= 1; o >>= 1) {
+      const int other = __shfl_xor_sync(full, len, o);
+      len = other > len ? other : len;
+    }
     uint32_t trunc = 0;
     if (ok) {
       if (len > S.L) {
@@ -381,13 +502,6 @@ __global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S) {
     }
     bool in = true;
     if (ok) {
-      const int nchunk = (len + 31) >> 5;
-      auto produce = [&](int ch) {  // warp 1: jerk of samples ch * 32 + lane of every joint
-        const int i = (ch << 5) + lane;
-        for (int r = 0; r < J; ++r) jbuf_s[ch & 1][r][lane] = jerk_reg_at(q_s[r], i);
-      };
-      if (warp == 1) produce(0);
-      __syncthreads();
       const double ts = L.t_sample;
       const double v_cruise = sc.v_drive * sc.dir;
       const JerkSamplerReg& Q = q_s[j];
@@ -395,98 +509,127 @@ __global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S) {
       const int cr_lo = Q.s[2] + 1;
       const bool phase4 = Q.s[3] - Q.s[2] > 2;
       const unsigned cr_span = (phase4 && Q.s[3] - 1 > cr_lo) ? (unsigned)(Q.s[3] - 1 - cr_lo) : 0u;
-      double* out = ltt_sample_w(S, e, pend, 0) + j;  // sample i: out[i * 4J + {0, J, 2J, 3J}] = q, v, a, j
+      double* out_q = ltt_sample_w(S, e, pend, 0) + j;  // sample i: [i * 4J + {0, J, 2J, 3J}] = q, v, a, j
+      double *out_v = out_q + J, *out_a = out_q + 2 * J;
       const size_t stride = (size_t)4 * J;
       double a = a_0, v = v_0, q = q_0;
-      for (int ch = 0; ch < nchunk; ++ch) {
-        if (warp == 1) {
-          if (ch + 1 < nchunk) produce(ch + 1);
-        } else if (jl) {
-          const double* jb = jbuf_s[ch & 1][j];
-          const int i0 = ch << 5;
-          const int n = (len - i0) < 32 ? (len - i0) : 32;
-          int u = 0;
-          if (ch == 0) {  // the first sample integrates unconditionally (:810-813)
-            const double jj = jb[0];
-            a = a_0 + ts * jj;
-            v = v_0 + ts * a;
-            q = q_0 + ts * v;
-            out[0] = q; out[J] = v; out[2 * J] = a; out[3 * J] = jj;
-            out += stride;
-            u = 1;
+#if defined(HRG_TASK_TRACE)
+      unsigned long long tr_fill = 0, tr_cons = 0, tr_a = trace_now();
+      const unsigned long long tr_init = tr_a - trace_t0;
+#endif
+      for (int c0 = 0; c0 < len; c0 += kSampleChunk) {
+        const int c1 = (c0 + kSampleChunk < len) ? c0 + kSampleChunk : len;
+        // fill: index i always belongs to lane (i - c0) & 31, so the phases can overwrite each other in the reference's
+        // order (jerk_reg_at: the LAST matching range wins) without a barrier
+        for (int r = 0; r < J; ++r) {
+          const JerkSamplerReg& R = q_s[r];
+          double* jb = jbuf_s[r];
+          for (int u = lane; u < c1 - c0; u += 32) jb[u] = 0.0;
+          int lo = -2147483647 - 1;
+#pragma unroll
+          for (int k = 0; k < 7; ++k) {
+            const int hi = R.s[k];
+            const int a0i = lo > c0 ? lo : c0, a1i = hi < c1 ? hi : c1;
+            if (a0i < a1i) {  // warp-uniform
+              const double jp = R.jp[k];
+              for (int i = a0i + ((lane - (a0i - c0)) & 31); i < a1i; i += 32) jb[i - c0] = jp;
+            }
+            lo = hi;
           }
-#pragma unroll 4
-          for (; u < n; ++u) {
-            const int i = i0 + u;
-            const double jj = jb[u];
-            const bool live = i <= s6;
-            const bool cruise = (unsigned)(i - cr_lo) < cr_span;
-            const double an = a + ts * jj;
-            a = live ? an : 0.0;
+        }
+        __syncwarp(full);
+#if defined(HRG_TASK_TRACE)
+        {
+          const unsigned long long nw = trace_now();
+          tr_fill += nw - tr_a;
+          tr_a = nw;
+        }
+#endif
+        if (jl) {  // the one-sample corrections of the lane's own joint, in slot order (two of them can hit one sample)
+          double* jb = jbuf_s[j];
+#pragma unroll
+          for (int k = 0; k < 12; ++k) {
+            const int ci = Q.cidx[k];
+            if (ci >= c0 && ci < c1) jb[ci - c0] = jb[ci - c0] + Q.cval[k];
+          }
+          // The recurrence, skewed by one sample per stage so that the three chains of an iteration are independent
+          // (a single warp issues in order: un-skewed, every sample was one ~60-cycle dependent chain a -> v -> q):
+          // iteration i computes a_i, v_(i-1) and q_(i-2), each from the values the PREVIOUS iteration left - the
+          // operations on every value, and their order, are the reference's (:810-831; its unconditional first sample is
+          // the general formula with live = true, cruise = false, which is what i = 0 gives: s6 >= 0, cr_lo >= 1).
+          auto stage_q = [&]() {  // q_(i-2) = q_(i-3) + ts v_(i-2)
+            q = q + ts * v;
+            out_q[0] = q;
+            out_q += stride;
+          };
+          auto stage_v = [&](int iv) {  // v_(i-1) from v_(i-2) and a_(i-1)
+            const bool live = iv <= s6;
+            const bool cruise = (unsigned)(iv - cr_lo) < cr_span;
             double vn = v + ts * a;
             vn = live ? vn : 0.0;
             v = cruise ? v_cruise : vn;
-            q = q + ts * v;
-            out[0] = q; out[J] = v; out[2 * J] = a; out[3 * J] = jj;
-            out += stride;
+            out_v[0] = v;
+            out_v += stride;
+          };
+          auto stage_a = [&](int i) {  // a_i from a_(i-1) and the jerk of sample i
+            const double jj = jb[i - c0];
+            const bool live = i <= s6;
+            const double an = a + ts * jj;
+            a = live ? an : 0.0;
+            out_a[0] = a;
+            out_a[J] = jj;
+            out_a += stride;
+          };
+          int i = c0;
+          for (; i < 2 && i < c1; ++i) {  // pipeline fill (first chunk only)
+            if (i >= 1) stage_v(i - 1);
+            stage_a(i);
+          }
+#pragma unroll 4
+          for (; i < c1; ++i) {  // steady state: three independent chains per iteration, no guards
+            stage_q();
+            stage_v(i - 1);
+            stage_a(i);
+          }
+          if (c1 == len) {  // pipeline drain
+            if (len >= 2) stage_q();
+            stage_v(len - 1);
+            stage_q();
           }
         }
-        __syncthreads();
+        __syncwarp(full);
+#if defined(HRG_TASK_TRACE)
+        {
+          const unsigned long long nw = trace_now();
+          tr_cons += nw - tr_a;
+          tr_a = nw;
+        }
+#endif
       }
+#if defined(HRG_TASK_TRACE)
+      if (lane == 0 && idx < kTraceTasks) {
+        g_task_trace[3][idx][0] = tr_init;
+        g_task_trace[3][idx][1] = tr_fill;
+        g_task_trace[3][idx][2] = tr_cons;
+        g_task_trace[3][idx][3] = (unsigned long long)len;
+      }
+#endif
       if (jl) in = !(q < c.q_min[j] || q > c.q_max[j]);  // (:59-61)
     }
-    if (warp == 0) {
-      const bool all_in = __all_sync(full, in);  // every joint of the env must end inside its limits
-      if (lane == 0) {
-        // verdict for k_pfl_ltt / k_replan_tail: bit 0 = trajectory written and valid, bit 1 = longer than the slot;
-        // slowest = its length
-        PlanHead o = head;
-        o.ok = ((ok && all_in) ? 1 : 0) | (int)trunc;
-        o.slowest = len;
-        S.plan_head[idx] = o;
-      }
+    const bool all_in = __all_sync(full, in);  // every joint of the env must end inside its limits
+    if (lane == 0) {
+      // verdict for k_pfl_ltt / k_replan_tail: bit 0 = trajectory written and valid, bit 1 = longer than the slot;
+      // slowest = its length
+      PlanHead o = head;
+      o.ok = ((ok && all_in) ? 1 : 0) | (int)trunc;
+      o.slowest = len;
+      S.plan_head[idx] = o;
+      if (TAIL) replan_tail_env(S, c, e, o, t[e]);  // (the samples it interpolates were written by this warp: visible after
+                                                    // the __syncwarp above, global memory is coherent within a thread block)
+      HRG_TRACE_TASK(2, idx, len);
     }
-    __syncthreads();  // idx_s, q_s, len_s are re-used by the next env
+    __syncwarp(full);  // q_s, jbuf_s are re-used by the next env
   }
-}
-
-// Thread per replanning env: install the new trajectory (safety_shield.cc:593-604, long_term_traj.h:108-116) and run the
-// rest of the env's step up to the reach / verify hand-over. The envs that do not replan got this from k_plan while the
-// chain was running.
-__global__ void __launch_bounds__(128) k_replan_tail(DevState S, const double* __restrict__ t) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= *S.replan_count) return;
-  const HrgConfig& c = *S.cfg;
-  const int J = S.J, N = S.N;
-  const int e = S.replan_list[idx];
-  uint32_t f = S.flags[e];
-  const int pend = (f & F_LIVE_SLOT) ? 0 : 1;
-  const PlanHead h = S.plan_head[idx];
-  const bool ok = (h.ok & 1) != 0;
-  uint32_t status = HRG_ST_REPLANNED;
-  if (h.ok & 2) status |= HRG_ST_LTT_TRUNCATED;
-  const bool pfl = ((f & F_TYPE_MASK) >> F_TYPE_SHIFT) == HRG_SHIELD_PFL;
-  if (ok) {
-    for (int j = 0; j < J; ++j) {
-      S.replan_q[(size_t)j * N + e] = cur_at(S, j, e);  // last_replan_start_motion_ = current_motion (:593)
-      // SSM / OFF: alpha_i_ = alpha_i_max (long_term_traj.h:108-116); PFL: written by k_pfl_ltt
-      if (!pfl) S.ltt_alpha[((size_t)pend * J + j) * N + e] = c.alpha_i_max;
-    }
-    S.ltt_len[(size_t)pend * N + e] = h.slowest;
-    S.ltt_cur[(size_t)pend * N + e] = 0;
-    S.ltt_start[(size_t)pend * N + e] = S.path_sd[e];
-    S.ltt_t0[(size_t)pend * N + e] = S.path_s[e];
-    S.ltt_ts[(size_t)pend * N + e] = c.sample_time;
-    f |= F_NEW_LTT;
-    f &= ~F_NEW_LTT_PROCESSED;
-  } else {
-    f &= ~F_NEW_LTT;
-    status |= HRG_ST_REPLAN_FAILED;
-  }
-  f &= ~F_PENDING_REPLAN;
-  f |= status << F_STATUS_SHIFT;
-  plan_env(S, c, e, t[e], f);
-  S.flags[e] = f;
 }
 
 }  // namespace hrg

@@ -12,6 +12,9 @@ struct LtpLimits {  // limits of ONE joint (LongTermPlanner members, long_term_p
   // only for degrees other than the planner's 4..6, which go to the register-resident solver of ltp_roots_reg.cuh).
   // NULL = a local array on the host; the device needs shared memory here.
   double* mat = nullptr;
+  // 0: every root through the exact restatement of the reference's QR iteration; 1: the derivative-chain root finder of
+  // ltp_roots_fast.cuh, QR only where its margin is small (the product default, HRG_ROOT_MODE)
+  int root_mode = 0;
 };
 
 HRG_HD int isign(double v) { return (0.0 < v) - (v < 0.0); }  // long_term_planner.h sign()
@@ -215,16 +218,30 @@ HRG_HD void real_schur_hessenberg(SmallMat& T) {
 
 }  // namespace hrg
 #include "ltp_roots_reg.cuh"
+#include "ltp_roots_fast.cuh"
 namespace hrg {
 
+#if defined(HRG_POLY_LOG) && !defined(__CUDA_ARCH__)
+void hrg_poly_log(const double* coef, int ncoef);
+#endif
 // roots() + getSmallestPositiveNonComplexRoot (roots.h:22-50): coef[0] is the leading coefficient, ncoef = degree+1.
 // Returns +inf if there is no real root > 1e-7.
 HRG_HD_CALL double smallest_positive_real_root(const LtpLimits& L, const double* coef, int ncoef) {
-#if defined(__CUDA_ARCH__) || defined(HRG_HOST_USE_RR)
-  // one problem per lane: the register-resident solver (bit-identical, ltp_roots_reg.cuh) for the planner's degrees
-  // (HRG_HOST_USE_RR: the host emulation can be built on it too, tests/host_emul/build.sh)
-  if (rr_has_degree(ncoef)) return rr_root(coef, ncoef);
+#if defined(HRG_POLY_LOG) && !defined(__CUDA_ARCH__)
+  hrg_poly_log(coef, ncoef);  // host-only instrumentation (profiles/harvest_polys.py)
 #endif
+  if (rr_has_degree(ncoef)) {
+    if (L.root_mode == 1) {  // derivative-chain finder; the QR iteration below stays the arbiter of close calls
+      double margin;
+      const double r = fr_root(coef, ncoef, margin);
+      if (margin >= kRootMargin) return r;
+    }
+#if defined(__CUDA_ARCH__) || defined(HRG_HOST_USE_RR)
+    // one problem per lane: the register-resident solver (bit-identical, ltp_roots_reg.cuh) for the planner's degrees
+    // (HRG_HOST_USE_RR: the host emulation can be built on it too, tests/host_emul/build.sh)
+    return rr_root(coef, ncoef);
+#endif
+  }
   SmallMat C;
 #if defined(__CUDA_ARCH__)
   // every device caller hands in per-lane shared-memory scratch; telling the compiler so turns the matrix accesses of the

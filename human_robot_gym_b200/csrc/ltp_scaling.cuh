@@ -138,6 +138,89 @@ HRG_HD double ltp_scaling_vdrive(const LtpLimits& L, int cand, double root, doub
   return sq(root) / jm;
 }
 
+// A timeScaling candidate that is rejected WHATEVER the reference's eigen-solve answers - the one family of close calls
+// that is common: a start from exact rest (v_0 = a_0 = 0) makes the candidate polynomials x^k q(x) with k >= 2 EXACT
+// trailing zeros. Their companion matrix has a defective k-fold eigenvalue 0, which the QR iteration returns as k
+// rounding-noise values of size ~(eps |C|)^(1/k) - up to 1e-3 - in every direction of the complex plane; when one of them
+// comes out real and above the 1e-7 cut, roots.h:46 hands it to the planner as "the smallest positive root" in place of
+// the true one. Which of the two happens is decided by rounding, so only the exact restatement of the iteration can tell
+// (~25 sweeps of a 6x6 matrix: the slowest thing left on the tick's critical path). But the planner only uses the root
+// through the trial `optSwitchTimes(v_drive(root))` + acceptance window (:398-405), so if BOTH alternatives are rejected
+// the candidate is rejected without knowing which one the iteration picks:
+//   * the true root r_t = smallest root > 1e-7 of the deflated q (degree <= 2: closed form), tried as usual;
+//   * a noise root g in (1e-7, g_hi]: from rest v_drive(g) = +-g^2 / (c jm) - either <= 0 for every g (candidate 5, rejected
+//     by `v_drive > 0`), or a cruise speed of at most g_hi^2 / jm, for which the profile takes T_6 >= |q_goal - q_0| /
+//     v_drive; T_6 falls monotonically with the cruise speed, so if the FASTEST noise root already misses the acceptance
+//     window by a full second (T_6 - t_required >= 1), every noise root is rejected.
+// g_hi = 0.05 is 50x the largest noise root the bound above allows for |C| <= 1e6 and 500x the largest one seen
+// (profiles/r02p_rest_start_candidates.md); r_t must lie clear of that range. Anything else (true root accepted, true root
+// small, deflated degree > 2, a move so short that the window could be met) returns false and the QR iteration decides.
+#if defined(HRG_RULE_DEBUG) && !defined(__CUDA_ARCH__)
+static long long hrg_rule_dbg[8];
+#endif
+HRG_HD_CALL bool ltp_cand_rejected_from_rest(const LtpLimits& L, int cand, const double* A, int ncoef, double q_goal,
+                                             double q_0, double v_0, double a_0, double v_orig, double a_orig, double tr,
+                                             OptRootCache* cache) {
+  if (!(v_0 == 0.0 && a_0 == 0.0)) return false;
+  int k = 0;
+  while (k < ncoef - 1 && A[ncoef - 1 - k] == 0.0) ++k;
+  if (k < 2 || A[0] == 0.0) return false;
+  const int nd = ncoef - k;  // coefficients of the deflated polynomial q
+  double rt = INFINITY;
+  if (nd == 2) {
+    const double x = -A[1] / A[0];
+    if (x > 1e-7) rt = x;
+  } else if (nd == 3) {
+    const double disc = A[1] * A[1] - 4.0 * A[0] * A[2];
+    if (disc >= 0.0) {
+      const double sd = sqrt(disc);
+      const double q = -0.5 * (A[1] + (A[1] >= 0.0 ? sd : -sd));
+      const double r1 = q / A[0], r2 = (q != 0.0) ? A[2] / q : r1;
+      if (r1 > 1e-7) rt = fmin(rt, r1);
+      if (r2 > 1e-7) rt = fmin(rt, r2);
+      if (!(disc > 1e-6 * A[1] * A[1])) return false;  // q itself has a close call: not ours to decide
+    } else if (!(-disc > 1e-6 * A[1] * A[1])) {
+      return false;
+    }
+  } else if (nd > 3) {
+    return false;
+  }
+  const double g_hi = 0.05;
+#if defined(HRG_RULE_DEBUG) && !defined(__CUDA_ARCH__)
+#define HRG_RD(i) (++hrg_rule_dbg[i])
+#else
+#define HRG_RD(i) ((void)0)
+#endif
+  if (!(rt > 10.0 * g_hi)) { HRG_RD(0); return false; }  // (INFINITY passes)
+  double T[7];
+  int mod = 0;
+  ltp_zero7(T);
+  if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, ltp_scaling_vdrive(L, cand, rt, v_0, a_0), tr, T, mod, cache)) { HRG_RD(1); return false; }
+  const double vd_g = ltp_scaling_vdrive(L, cand, g_hi, v_0, a_0);
+  if (vd_g <= 0.0) return true;  // -g^2 / (2 jm): no noise root passes `v_drive > 0`
+  if (!(vd_g > 0.0)) return false;
+  double trash;
+  ltp_zero7(T);
+  if (!ltp_opt_switch_times(L, q_goal, q_0, v_orig, a_orig, vd_g, T, trash, mod, cache)) { HRG_RD(2); return false; }
+  if (T[6] - tr >= 1.0) return true;
+  // a joint that is (almost) at its goal: optSwitchTimes returns the braking times before it ever looks at v_drive (:95-99,
+  // |q_goal - (q_0 + q_stop)| < 4e-3), so every positive v_drive - noise root or true root - gets the SAME verdict, which
+  // the trial of the true root above has already shown to be a rejection
+  {
+    double tb[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    double q_stop = 0.0, d;
+    ltp_opt_braking(L, v_orig, a_orig, q_stop, tb, d);
+    const double vd_t = ltp_scaling_vdrive(L, cand, rt, v_0, a_0);
+    if (fabs(q_goal - (q_0 + q_stop)) < 4e-3 && vd_t > 0.0) return true;
+  }
+  HRG_RD(3);
+  return false;
+}
+
+#if defined(HRG_CAND_LOG) && !defined(__CUDA_ARCH__)
+void hrg_cand_log(const LtpLimits& L, int cand, const double* A, int ncoef, double q_goal, double q_0, double v_0, double a_0,
+                  double v_orig, double a_orig, double tr, OptRootCache* cache);
+#endif
 // Sequential form: the candidates one after the other, first accepted wins (host tests, stage kernel).
 HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0, double v_0, double a_0, double dir,
                                   double tr /*t_required*/, double* T /*scaled_t*/, double& v_drive,
@@ -151,7 +234,26 @@ HRG_HD_CALL bool ltp_time_scaling(const LtpLimits& L, double q_goal, double q_0,
     double A[7];
     int ncoef;
     v_drive = ltp_scaling_setup(L, cand, q_goal, q_0, v_0, a_0, dir, tr, A, ncoef);
-    if (ncoef) v_drive = ltp_scaling_vdrive(L, cand, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
+#if defined(HRG_CAND_LOG) && !defined(__CUDA_ARCH__)
+    if (ncoef) hrg_cand_log(L, cand, A, ncoef, q_goal, q_0, v_0, a_0, v_orig, a_orig, tr, cache);
+#endif
+    if (ncoef) {
+      if (L.root_mode == 1 && rr_has_degree(ncoef)) {
+        double margin;
+        const double r = fr_root(A, ncoef, margin);
+        if (margin >= kRootMargin) {
+          v_drive = ltp_scaling_vdrive(L, cand, r, v_0, a_0);
+        } else if (ltp_cand_rejected_from_rest(L, cand, A, ncoef, q_goal, q_0, v_0, a_0, v_orig, a_orig, tr, cache)) {
+          continue;  // rejected whichever way the QR iteration's rounding falls (a rejected trial leaves nothing behind)
+        } else {
+          LtpLimits Lx = L;
+          Lx.root_mode = 0;
+          v_drive = ltp_scaling_vdrive(L, cand, smallest_positive_real_root(Lx, A, ncoef), v_0, a_0);
+        }
+      } else {
+        v_drive = ltp_scaling_vdrive(L, cand, smallest_positive_real_root(L, A, ncoef), v_0, a_0);
+      }
+    }
     if (ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, v_drive, tr, T, mod_jerk_profile, cache)) return true;
   }
   // no valid solution (:640-644)

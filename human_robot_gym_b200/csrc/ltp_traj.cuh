@@ -216,8 +216,17 @@ HRG_HD int ltp_plan_env_seq(const HrgConfig& c, const double* q_goal, const doub
   for (int j = 0; j < J; ++j) {
     L[j].v_max = c.v_max[j]; L[j].a_max = c.a_max_ltt[j]; L[j].j_max = c.j_max_ltt[j]; L[j].t_sample = c.sample_time;
     L[j].mat = mat;
+    L[j].root_mode = c.root_mode;
     if (!ltp_check_inputs_joint(L[j], c.q_min[j], c.q_max[j], q_0[j], v_0[j], a_0[j])) return 0;
   }
+#if defined(HRG_TRACE_PREFILL) && !defined(__CUDA_ARCH__)
+  for (int j = 0; j < J; ++j)  // host-only instrumentation: what k_replan_plan's unconditional prefill solves
+    for (int w = 0; w < 2; ++w) {
+      OptRootCache tmp;
+      opt_cache_clear(tmp);
+      opt_prefill_root(L[j], q_goal[j], q_0[j], v_0[j], a_0[j], w, tmp);
+    }
+#endif
   for (int j = 0; j < J; ++j) {
     ltp_zero7(opt[j].T);
     opt_cache_clear(rc[j]);

@@ -52,7 +52,9 @@ typedef struct HrgConfig {
   int32_t n_bodies;     /* Vel and Accel capsules each */
   int32_t n_ext;        /* Pos spheres */
   int32_t ltt_capacity; /* samples per long-term-trajectory slot (two slots per env) */
-  int32_t reserved0;
+  int32_t root_mode;    /* planner root finder: 0 = every polynomial through the restatement of the reference's QR
+                         * iteration (roots.h:22-50); 1 = derivative-chain root finder, QR only where its margin to a
+                         * different verdict is small (csrc/ltp_roots_fast.cuh) */
   double sample_time;
   double max_s_stop, v_safe, alpha_i_max; /* trajectory_parameters_*.yaml */
   double secure_radius;                   /* robot_parameters_*.yaml */

@@ -11,11 +11,26 @@
 #include <cstring>
 #include <vector>
 
+#if defined(HRG_POLY_LOG)
+#include <vector>
+static std::vector<double> g_poly_log;  // rows of 8: ncoef, coef[0..6]
+static bool g_poly_log_on = false;
+namespace hrg {
+void hrg_poly_log(const double* coef, int ncoef) {
+  if (!g_poly_log_on || ncoef > 7) return;
+  g_poly_log.push_back((double)ncoef);
+  for (int i = 0; i < 7; ++i) g_poly_log.push_back(i < ncoef ? coef[i] : 0.0);
+}
+}  // namespace hrg
+#endif
 #include "../../human_robot_gym_b200/csrc/ltp_math.cuh"
 #include "../../human_robot_gym_b200/csrc/step_logic.cuh"
 #include "../../human_robot_gym_b200/csrc/pfl_math.cuh"
 #include "../../human_robot_gym_b200/csrc/kernels_human.cuh"
 
+#if defined(HRG_CAND_LOG)
+#include "/tmp/emul_tr/candlog.inc"
+#endif
 using namespace hrg;
 
 struct Emul {
@@ -305,6 +320,35 @@ void emul_rr_trace(long long* out /*[8][64]*/, int clear) {
   }
 }
 #endif
+#if defined(HRG_POLY_LOG)
+long long emul_poly_log(int on, double* out, long long cap_rows) {  // copies and clears the log; returns the row count
+  g_poly_log_on = on != 0;
+  const long long rows = (long long)(g_poly_log.size() / 8);
+  if (out) {
+    memcpy(out, g_poly_log.data(), sizeof(double) * 8 * (size_t)(rows < cap_rows ? rows : cap_rows));
+    g_poly_log.clear();
+  }
+  return rows;
+}
+#endif
+// planner-wide root-finder mode of the emulation (LtpLimits::root_mode): 0 exact QR, 1 fast with QR fallback
+static int g_emul_root_mode = 0;
+void emul_set_root_mode(int m) { g_emul_root_mode = m; }
+// the derivative-chain root finder (csrc/ltp_roots_fast.cuh) next to the exact one, for many polynomials of one degree
+void emul_poly_root_fast_batch(long long n, int ncoef, const double* coef, double* out_fast, double* out_margin,
+                               double* out_reg) {
+  for (long long i = 0; i < n; ++i) {
+    double m = 0.0;
+    out_fast[i] = rr_has_degree(ncoef) ? fr_root(coef + (size_t)i * ncoef, ncoef, m) : NAN;
+    out_margin[i] = m;
+    if (rr_has_degree(ncoef)) {  // the mixed-degree form must return the same bits
+      double m2 = 0.0;
+      const double r2 = fr_root_mixed(coef + (size_t)i * ncoef, ncoef, m2);
+      if (memcmp(&r2, &out_fast[i], 8) != 0 || memcmp(&m2, &m, 8) != 0) out_margin[i] = -1.0;
+    }
+    if (out_reg) out_reg[i] = rr_has_degree(ncoef) ? rr_root(coef + (size_t)i * ncoef, ncoef) : NAN;
+  }
+}
 double emul_poly_root(const double* coef, int ncoef) { LtpLimits L{}; return smallest_positive_real_root(L, coef, ncoef); }
 // the register-resident solver the device uses for one-problem-per-lane kernels (csrc/ltp_roots_reg.cuh), degrees 4..6
 double emul_poly_root_reg(const double* coef, int ncoef) { return rr_has_degree(ncoef) ? rr_root(coef, ncoef) : NAN; }

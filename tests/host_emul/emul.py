@@ -49,6 +49,8 @@ def lib():
         L.emul_poly_root_reg.restype = C.c_double
         L.emul_poly_root_reg.argtypes = [_p, C.c_int]
         L.emul_poly_root_batch.argtypes = [C.c_int, C.c_int, _p, _p, _p]
+        L.emul_poly_root_fast_batch.argtypes = [C.c_longlong, C.c_int, _p, _p, _p, _p]
+        L.emul_set_root_mode.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -148,6 +150,17 @@ def poly_root_batch(coefs):
     a, b = np.zeros(n), np.zeros(n)
     lib().emul_poly_root_batch(n, ncoef, _ptr(c), _ptr(a), _ptr(b))
     return a, b
+
+
+def poly_root_fast_batch(coefs):
+    """Derivative-chain root finder (csrc/ltp_roots_fast.cuh) next to the exact QR restatement for coefs [n, ncoef], ncoef
+    5..7: (fast root, margin in units of the QR iteration's noise, exact root). margin == -1 marks a polynomial on which the
+    mixed-degree form (k_replan_deep) and the per-degree form returned different bits."""
+    c = _a(coefs)
+    n, ncoef = c.shape
+    f, m, r = np.zeros(n), np.zeros(n), np.zeros(n)
+    lib().emul_poly_root_fast_batch(n, ncoef, _ptr(c), _ptr(f), _ptr(m), _ptr(r))
+    return f, m, r
 
 
 def ltp_opt_braking(ts, lim, v0, a0):

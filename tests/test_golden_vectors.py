@@ -394,3 +394,62 @@ def test_capsule_markers_match_reference_plot_capsule():
     assert np.array_equal(pos, z["pos"]) and np.array_equal(size, z["size"])
     assert np.abs(mat - z["mat"]).max() < 1e-15
     assert (z["size"][200:210, 2] == 0.00001).all() and np.array_equal(z["mat"][225], np.eye(3))  # sphere / -z branches hit
+
+
+# ---- the derivative-chain root finder (csrc/ltp_roots_fast.cuh) against the exact restatement of roots.h:22-50 ---------
+# HrgConfig.root_mode 1 (the product default) answers "smallest real root > 1e-7" without the companion-matrix QR iteration
+# and hands the close calls (margin < kRootMargin = 1e4 units of the QR iteration's noise) to the exact path. Pinned here:
+# wherever the margin is trusted the verdict root / no root is the QR iteration's and the value agrees to 1e-9 relative.
+ROOT_MARGIN = 1e4
+
+
+def _check_fast_roots(coefs, what):
+    fast, margin, exact = emul.poly_root_fast_batch(coefs)
+    assert not (margin == -1).any(), f"{what}: mixed-degree and per-degree form differ"
+    trusted = margin >= ROOT_MARGIN
+    fin_f, fin_e = np.isfinite(fast), np.isfinite(exact)
+    bad_class = trusted & (fin_f != fin_e)
+    assert not bad_class.any(), f"{what}: verdict differs on {coefs[bad_class][:3]} (margin {margin[bad_class][:3]})"
+    both = trusted & fin_f & fin_e
+    rel = np.abs(fast[both] - exact[both]) / np.abs(exact[both])
+    assert rel.size == 0 or rel.max() < 1e-9, f"{what}: root differs by {rel.max()}"
+    return trusted.mean(), (rel.max() if rel.size else 0.0)
+
+
+def test_fast_roots_match_qr_on_planner_polynomials():
+    """Polynomials harvested from the bench workload (profiles/harvest_polys.py: every optSwitchTimes quartic, also the ones
+    k_replan_plan solves ahead of need, and every timeScaling candidate of degree 4, 5, 6; Schunk and Panda)."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "planner_polys.npz"))
+    for deg in (4, 5, 6):
+        frac, worst = _check_fast_roots(z[f"deg{deg}"], f"degree {deg}")
+        print(f"degree {deg}: {len(z[f'deg{deg}'])} polynomials, trusted {frac:.4f}, worst relative difference {worst:.2e}")
+        assert frac > (0.95 if deg == 4 else 0.5)     # degree 5 / 6 only occur deep in the ladder, often from rest
+
+
+@pytest.mark.parametrize("deg", [4, 5, 6])
+def test_fast_roots_near_double_roots(deg):
+    """(x - r)(x - r (1 + d)) q(x) and (x - r)^2 q(x) + e: pairs of real roots that merge / turn complex as d, e -> 0 - the
+    classification the QR iteration decides by rounding. The margin has to hand exactly those to the exact path."""
+    rng = np.random.default_rng(40 + deg)
+    rows = []
+    for _ in range(4000):
+        r = 10 ** rng.uniform(-3, 1.5)
+        rest = rng.uniform(-5, 5, deg - 2) * rng.choice([1, 1, 0.01], deg - 2)   # the other roots, some tiny
+        d = rng.choice([0.0, 1e-15, 1e-13, 1e-11, 1e-9, 1e-7, 1e-5, 1e-3, 1e-1])
+        p = np.poly(np.concatenate([[r, r * (1 + d)], rest])) * rng.uniform(0.5, 200)
+        e = rng.choice([0.0, 0.0, 1e-14, -1e-14, 1e-10, -1e-10, 1e-6, -1e-6]) * np.abs(p).max()
+        p[-1] += e
+        rows.append(p)
+    frac, worst = _check_fast_roots(np.array(rows), f"near-double degree {deg}")
+    assert 0.2 < frac < 0.95                          # the merged pairs are NOT trusted, the separated ones are
+
+
+def test_fast_roots_from_rest_structure():
+    """x^k q(x) with exact trailing zeros (a start from rest): a k-fold zero eigenvalue the QR iteration returns as noise -
+    never trusted for k >= 2."""
+    rng = np.random.default_rng(7)
+    for deg, k in ((4, 2), (5, 4), (6, 4), (6, 2)):
+        c = np.zeros((500, deg + 1))
+        c[:, :deg + 1 - k] = rng.uniform(-200, 200, (500, deg + 1 - k))
+        fast, margin, exact = emul.poly_root_fast_batch(c)
+        assert (margin < ROOT_MARGIN).all()

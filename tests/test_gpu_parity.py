@@ -144,6 +144,16 @@ def test_closed_loop_matches_checker(robot, n_envs, ticks, seed):
     assert res["branch_hist"][0] > 0 and res["branch_hist"][2] > 0   # branch 1: tests/test_parity_gaps.py
 
 
+@pytest.mark.parametrize("robot,n_envs,ticks,seed", [("schunk", 1024, 150, 1011), ("panda", 512, 150, 1012)])
+def test_closed_loop_exact_root_mode_matches_checker(robot, n_envs, ticks, seed, monkeypatch):
+    """HrgConfig.root_mode 0: every planner polynomial through the exact restatement of the reference's QR iteration (the
+    arbiter the default mode 1 falls back to), product configuration."""
+    monkeypatch.setenv("HRG_ROOT_MODE", "0")
+    res = pu.closed_loop_compare(pu.default_files(robot), n_envs=n_envs, ticks=ticks, seed=seed, store_capsules=False)
+    print(res)
+    pu.assert_parity(res)
+
+
 @pytest.mark.parametrize("robot,n_envs,ticks,seed,shield_type", [("schunk", 1024, 150, 3001, 1), ("panda", 517, 150, 3002, 1),
                                                                   ("schunk", 384, 150, 3004, 2)])
 def test_verification_cascade_matches_checker(robot, n_envs, ticks, seed, shield_type):
