@@ -80,7 +80,7 @@ struct HrgShield {
   size_t reach_smem = 0, reach_smem_p0 = 0;
   size_t measure_smem = 0;
   // k_replan runs on its own stream, concurrently with the first reach + verify pass (envs that do not replan)
-  cudaStream_t side = nullptr;
+  cudaStream_t side = nullptr, meas = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_meas = nullptr;
   bool overlap = true;
   bool debug_sync = false;
@@ -247,6 +247,7 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
     if (const char* v = getenv("HRG_DEEP_PER_WARP"))
       if (atoi(v) >= 1 && atoi(v) <= 4) h->deep_per_warp = atoi(v);
   }
+  if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&h->meas, cudaStreamNonBlocking);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_meas, cudaEventDisableTiming);
@@ -292,6 +293,7 @@ int hrg_shield_destroy(HrgShield* s) {
   for (void* p : s->allocs) cudaFree(p);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
   if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+  if (s->meas) cudaStreamDestroy(s->meas);
   if (s->ev_join) cudaEventDestroy(s->ev_join);
   if (s->ev_meas) cudaEventDestroy(s->ev_meas);
   for (int k = 0; k < 2; ++k) {
@@ -428,29 +430,33 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
   };
   mark(-1);
   const bool fork = s->overlap && !prof;
-  if (kp && !fork) {
-    k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
-    s->launches++;
-    mark(HRG_PROF_MEASURE);
-  }
-  k_pre<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, goal_mask, goal_q);
-  mark(HRG_PROF_PRE);
-  if (!fork) {
-    k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
-    mark(HRG_PROF_PLAN);
-  }
-  cudaStream_t rs = fork ? s->side : st;
-  if (fork) {
-    // replan || reach + verify of the envs that do not replan, then the replanned envs
-    CK(cudaEventRecord(s->ev_fork, st));
-    CK(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
-  }
-  // from here to the join an early return would leave the side stream un-joined for the next tick: collect the first
-  // error instead and join in any case
+  // In a tick that measures, the measurement time IS t: the path planning takes it from there instead of waiting for
+  // k_measure to store it (k_measure writes the same value to last_meas)
+  const double* meas_t = kp ? t : nullptr;
   cudaError_t err = cudaSuccess;
   auto keep = [&](cudaError_t e) {
     if (err == cudaSuccess && e != cudaSuccess) err = e;
   };
+  if (kp && !fork) {
+    k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
+    mark(HRG_PROF_MEASURE);
+    s->launches++;
+  }
+  k_pre<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, goal_mask, goal_q);
+  mark(HRG_PROF_PRE);
+  if (!fork) {
+    k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t, meas_t);
+    mark(HRG_PROF_PLAN);
+  }
+  cudaStream_t rs = fork ? s->side : st;
+  if (fork) {
+    // main stream: path planning + reach / verify + determineNextMotion of the envs that do not replan;
+    // side stream (high priority): the replan chain, then reach / verify + determineNextMotion of the replanned envs
+    keep(cudaEventRecord(s->ev_fork, st));
+    keep(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
+  }
+  // (from the first fork to the join an early return would leave a stream un-joined for the next tick: the first error is
+  // collected instead and the streams are joined in any case)
   {
     // the replan list length is only known on the device: the kernels fetch their work from device counters, their grids
     // only bound residency (one warp per block, so that the few hundred busy warps spread over all schedulers)
@@ -458,51 +464,56 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
     const int cap = s->sm_count * 16;
     int g_plan = grid_for(N, s->plan_envs_per_warp), g_samp = N, g_deep = grid_for(N * J, s->deep_per_warp);
     if (g_plan > cap) g_plan = cap;
-    if (g_samp > cap) g_samp = cap;
+    if (g_samp > s->sm_count * HRG_SAMPLE_MINBLOCKS) g_samp = s->sm_count * HRG_SAMPLE_MINBLOCKS;
     if (g_deep > cap) g_deep = cap;
     k_replan_plan<<<g_plan, kReplanBlock, 0, rs>>>(s->S, s->plan_envs_per_warp);
     mark(HRG_PROF_PLAN_LTT);
     k_replan_deep<<<g_deep, kReplanBlock, 0, rs>>>(s->S, s->deep_per_warp);
     mark(HRG_PROF_DEEP);
-    if (fork && kp) {
-      // the tail of the chain (plan_env) reads last_meas: k_measure (main stream) must be through by then
-      k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, st>>>(s->S, nullptr, kp, t);
-      s->launches++;
-      keep(cudaEventRecord(s->ev_meas, st));
-      keep(cudaStreamWaitEvent(s->side, s->ev_meas, 0));
-    }
+    k_replan_sample<<<g_samp, kSampleBlock, 0, rs>>>(s->S);
+    mark(HRG_PROF_SAMPLE);
     if (s->pfl) {
-      k_replan_sample<false><<<g_samp, kSampleBlock, 0, rs>>>(s->S, t);
-      mark(HRG_PROF_SAMPLE);
       int pgrid = s->sm_count * 8;
       if (pgrid > N) pgrid = N;
       k_pfl_ltt<<<pgrid, kPflBlock, 0, rs>>>(s->S);
       mark(HRG_PROF_PFL);
-      k_replan_tail<<<grid_for(N, 128), 128, 0, rs>>>(s->S, t);
-      mark(HRG_PROF_TAIL);
-      s->launches += 2;
-    } else {
-      // SSM / OFF handles: the env tail runs at the end of the sampler (one launch and one kernel boundary less)
-      k_replan_sample<true><<<g_samp, kSampleBlock, 0, rs>>>(s->S, t);
-      mark(HRG_PROF_SAMPLE);
+      s->launches++;
     }
+    k_replan_tail<<<grid_for(N, 128), 128, 0, rs>>>(s->S, t, meas_t);
+    mark(HRG_PROF_TAIL);
   }
   if (fork) {
-    keep(cudaEventRecord(s->ev_join, s->side));
-    k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t);
+    k_plan<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, t, meas_t);
+    if (kp) {
+      // k_measure: only reach + verify read the keypoints, and the path planning takes the measurement time from t, so it
+      // gets a stream of its own NEXT to k_plan - launched after k_pre, the head of the chain and k_plan, which its 2 048
+      // blocks would otherwise keep waiting for SM slots
+      keep(cudaStreamWaitEvent(s->meas, s->ev_fork, 0));
+      k_measure<<<tile_grid(N), kMeasureWarps * 32, s->measure_smem, s->meas>>>(s->S, nullptr, kp, t);
+      keep(cudaEventRecord(s->ev_meas, s->meas));
+      s->launches++;
+    }
+    if (kp) {  // reach + verify read the keypoints
+      keep(cudaStreamWaitEvent(st, s->ev_meas, 0));
+      keep(cudaStreamWaitEvent(s->side, s->ev_meas, 0));
+    }
     verify_pass0(s, st, s->reach_smem_p0, mark);
-    // determineNextMotion of the envs that did not replan: off the critical path, next to the replan chain
+    // determineNextMotion of the envs that did not replan
     k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status, 0);
     s->launches++;
-    keep(cudaStreamWaitEvent(st, s->ev_join, 0));
   } else {
     verify_pass0(s, st, s->reach_smem, mark);
   }
-  k_reach_verify<2><<<tile_grid(N), 32 * s->S.J * 2, s->reach_smem, st>>>(s->S, 1);
+  // the replanned envs: reach + verify pass 1 and determineNextMotion, behind the chain (fork: on its stream)
+  k_reach_verify<2><<<tile_grid(N), 32 * s->S.J * 2, s->reach_smem, rs>>>(s->S, 1);
   mark(HRG_PROF_VERIFY_P1);
-  k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status, fork ? 1 : -1);
+  k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, rs>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status, fork ? 1 : -1);
   mark(HRG_PROF_SELECT);
-  s->launches += 8;
+  if (fork) {
+    keep(cudaEventRecord(s->ev_join, s->side));
+    keep(cudaStreamWaitEvent(st, s->ev_join, 0));
+  }
+  s->launches += 9;
   keep(cudaGetLastError());
   if (err != cudaSuccess) return fail(HRG_ECUDA, "hrg_shield_step: launch failed", err);
   return HRG_OK;
@@ -608,6 +619,23 @@ extern "C" int hrg_trace_read(unsigned long long* dst_host) {
   void* p = nullptr;
   CK(cudaGetSymbolAddress(&p, hrg::g_task_trace));
   CK(cudaMemset(p, 0, sizeof(hrg::g_task_trace)));
+  return HRG_OK;
+}
+// kernel spans [16][2] u64 (earliest block start, latest block end); re-armed (start = ~0, end = 0)
+extern "C" int hrg_trace_read_spans(unsigned long long* dst_host) {
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(dst_host, hrg::g_kernel_span, sizeof(hrg::g_kernel_span)));
+  unsigned long long init[16][2];
+  for (auto& r : init) {
+    r[0] = ~0ull;
+    r[1] = 0ull;
+  }
+  CK(cudaMemcpyToSymbol(hrg::g_kernel_span, init, sizeof(init)));
+  return HRG_OK;
+}
+extern "C" int hrg_trace_read_counts(unsigned long long* dst_host /*[4]*/) {
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(dst_host, hrg::g_qr_count, sizeof(hrg::g_qr_count)));
   return HRG_OK;
 }
 #endif

@@ -34,6 +34,7 @@ constexpr int kHumDoubles = 11;
 __global__ void __launch_bounds__(kMeasureWarps * 32)
     k_measure(DevState S, const uint8_t* __restrict__ mask, const double* __restrict__ kp_in,
               const double* __restrict__ t) {
+  HRG_TRACE_SPAN(4);
   extern __shared__ double tile[];  // [32][K3 | 1]
   const int K3 = S.K * 3, ld = K3 | 1, N = S.N;
   const int e0 = blockIdx.x * kTileEnvs;
@@ -95,6 +96,7 @@ template <int PARTS, bool CASCADE = false>
 __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS,
                                   PARTS == 1 ? (CASCADE ? HRG_CASCADE_MINBLOCKS : HRG_REACH_MINBLOCKS) : 1)
     k_reach_verify(DevState S, int pass) {
+  HRG_TRACE_SPAN(pass == 0 ? 7 : 11);
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
   __shared__ unsigned bits_s[HRG_MAX_JOINTS * PARTS][kTileEnvs];
@@ -274,6 +276,7 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS,
 // model clears becomes safe; otherwise it goes on to the Accel stage or stays unsafe.
 template <int MODEL>
 __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_STAGE_MINBLOCKS) k_verify_stage(DevState S) {
+  HRG_TRACE_SPAN(7 + MODEL);
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
   __shared__ unsigned bits_s[HRG_MAX_JOINTS][kTileEnvs];

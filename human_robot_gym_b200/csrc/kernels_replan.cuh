@@ -26,11 +26,18 @@
 #include "ltp_math.cuh"
 #include "step_logic.cuh"
 #include "pfl_math.cuh"
-#include "task_trace.cuh"
 
 namespace hrg {
 
 enum { CTR_PLAN = 0, CTR_SAMPLE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, N_CTR = 4 };
+// Residency: a tick has up to N / 25 replanning envs (2 621 at 65 536) and every task wants a warp of its own AT ONCE - a
+// second round doubles the kernel. Registers per thread are capped accordingly (148 SMs x minBlocks warps).
+#ifndef HRG_PLAN_MINBLOCKS
+#define HRG_PLAN_MINBLOCKS 12
+#endif
+#ifndef HRG_SAMPLE_MINBLOCKS
+#define HRG_SAMPLE_MINBLOCKS 20
+#endif
 constexpr int kReplanBlock = 32;  // one warp per block: a tick has a few hundred busy warps; this spreads them over all SM sub-partitions
 
 __device__ __forceinline__ LtpLimits joint_limits(const HrgConfig& c, int j) {
@@ -79,7 +86,8 @@ __device__ __forceinline__ int fetch_warp_tasks(int32_t* ctr, int per_warp, int 
 //      shuffles over its lanes;
 //   3. half h evaluates closed-form timeScaling candidate h (:378-436) - the reference tries (1) first and (2) only if
 //      (1) is rejected, so half 0's result wins when both are accepted.
-__global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S, int envs_per_warp) {
+__global__ void __launch_bounds__(kReplanBlock, HRG_PLAN_MINBLOCKS) k_replan_plan(DevState S, int envs_per_warp) {
+  HRG_TRACE_SPAN(0);
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -208,6 +216,7 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_plan(DevState S, int en
 //      comes BEFORE the first candidate already accepted in A, since the reference never gets to the later ones.
 // With root_mode 0 every candidate is a close call by definition and B is the whole kernel.
 __global__ void __launch_bounds__(kReplanBlock) k_replan_deep(DevState S, int joints_per_warp) {
+  HRG_TRACE_SPAN(1);
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -265,6 +274,7 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_deep(DevState S, int jo
           r.v_drive = ltp_scaling_vdrive(L, cand, root, v_0, a_0);
           r.len = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, r.v_drive, t_required, r.T, r.mod, &rc) ? 1 : 0;
         } else if (ltp_cand_rejected_from_rest(L, cand, A, ncoef, q_goal, q_0, v_0, a_0, v_orig, a_orig, t_required, &rc)) {
+          HRG_TRACE_COUNT(2);
           need_qr = false;  // a start from rest: rejected whichever way the QR iteration's rounding falls (ltp_scaling.cuh)
           ltp_zero7(r.T);
           r.mod = opt.mod;
@@ -275,6 +285,7 @@ __global__ void __launch_bounds__(kReplanBlock) k_replan_deep(DevState S, int jo
     const unsigned acc = (__ballot_sync(full, act && !need_qr && r.len != 0) >> (grp * 8)) & 0x3fu;
     const int first_acc = acc ? (__ffs(acc) - 1) : 6;
     if (act && need_qr && ci < first_acc) {
+      HRG_TRACE_COUNT(0);
       r.v_drive = ltp_scaling_vdrive(L, cand, rr_root(A, ncoef), v_0, a_0);
       r.len = ltp_try_vdrive(L, q_goal, q_0, v_orig, a_orig, r.v_drive, t_required, r.T, r.mod, &rc) ? 1 : 0;
     }
@@ -349,7 +360,8 @@ __device__ __forceinline__ double jerk_reg_at(const JerkSamplerReg& S, int i) {
 // Install the new trajectory of one replanning env (safety_shield.cc:593-604, long_term_traj.h:108-116) and run the rest of
 // the env's step up to the reach / verify hand-over. The envs that do not replan got this from k_plan while the chain was
 // running. `h` = the sampler's verdict (ok bit 0: trajectory valid, bit 1: longer than the slot; slowest = its length).
-__device__ __forceinline__ void replan_tail_env(const DevState& S, const HrgConfig& c, int e, const PlanHead& h, double t) {
+__device__ __forceinline__ void replan_tail_env(const DevState& S, const HrgConfig& c, int e, const PlanHead& h, double t,
+                                             double last_meas) {
   const int J = S.J, N = S.N;
   uint32_t f = S.flags[e];
   const int pend = (f & F_LIVE_SLOT) ? 0 : 1;
@@ -384,17 +396,19 @@ __device__ __forceinline__ void replan_tail_env(const DevState& S, const HrgConf
   }
   f &= ~F_PENDING_REPLAN;
   f |= status << F_STATUS_SHIFT;
-  plan_env(S, c, e, t, f);
+  plan_env(S, c, e, t, f, last_meas);
   S.flags[e] = f;
 }
 
-// The tail as a kernel of its own (thread per replanning env): PFL handles, whose k_pfl_ltt runs between the sampler and
-// the tail. SSM handles run it at the end of k_replan_sample<true>.
-__global__ void __launch_bounds__(128) k_replan_tail(DevState S, const double* __restrict__ t) {
+// Thread per replanning env. A kernel of its own: inside the sampler its ~250 registers would cap the residency of the
+// sampling loop (fused and uncapped: 9 warps / SM, a second round above 1 332 replans; capped to 128: the loop spills and
+// runs at half speed - both measured, profiles/r02_summary.md). PFL handles run k_pfl_ltt between the two.
+__global__ void __launch_bounds__(128) k_replan_tail(DevState S, const double* __restrict__ t,
+                                                     const double* __restrict__ meas_t) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= *S.replan_count) return;
   const int e = S.replan_list[idx];
-  replan_tail_env(S, *S.cfg, e, S.plan_head[idx], t[e]);
+  replan_tail_env(S, *S.cfg, e, S.plan_head[idx], t[e], meas_t ? meas_t[e] : S.last_meas[e]);
 }
 
 // What replan_tail_env / plan_env will read of env e, asked for ahead of time by all lanes of the env's warp (field-major
@@ -402,7 +416,7 @@ __global__ void __launch_bounds__(128) k_replan_tail(DevState S, const double* _
 __device__ __forceinline__ void prefetch_tail_inputs(const DevState& S, int e, int lane) {
   const int J = S.J;
   const size_t N = (size_t)S.N;
-  auto pf = [](const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); };
+  auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); };
   for (int k = lane; k < N_PATHS * PATH_FIELDS; k += 32) pf(S.paths + (size_t)k * N + e);
   for (int k = lane; k < 4 * J + 1; k += 32) pf(S.cur + (size_t)k * N + e);
   for (int k = lane; k < J; k += 32) pf(S.prev_dq + (size_t)k * N + e);
@@ -416,7 +430,6 @@ __device__ __forceinline__ void prefetch_tail_inputs(const DevState& S, int e, i
   }
   if (lane == 2) pf(S.path_s + e);
   if (lane == 3) pf(S.path_sd + e);
-  if (lane == 4) pf(S.last_meas + e);
 }
 
 // One env per warp (one warp per block, so the blocks of a tick are all resident at once and spread over every
@@ -429,8 +442,8 @@ __device__ __forceinline__ void prefetch_tail_inputs(const DevState& S, int e, i
 // then lanes 0..J-1 integrate the chunk and stream the samples out.
 constexpr int kSampleBlock = 32;
 constexpr int kSampleChunk = 128;
-template <bool TAIL>
-__global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S, const double* __restrict__ t) {
+__global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_sample(DevState S) {
+  HRG_TRACE_SPAN(2);
   __shared__ JerkSamplerReg q_s[HRG_MAX_JOINTS];
   __shared__ double jbuf_s[HRG_MAX_JOINTS][kSampleChunk + 1];  // + 1: the J consumer lanes read one column of it
   const HrgConfig& c = *S.cfg;
@@ -445,7 +458,7 @@ __global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S, cons
     if (idx >= count) break;
     HRG_TRACE_T0();
     const int e = S.replan_list[idx];
-    if (TAIL) prefetch_tail_inputs(S, e, lane);
+    prefetch_tail_inputs(S, e, lane);  // for k_replan_tail, which follows: one lane per env chasing ~100 cache lines
     const int pend = (S.flags[e] & F_LIVE_SLOT) ? 0 : 1;
     const PlanHead head = S.plan_head[idx];
     bool ok = head.ok != 0;
@@ -513,28 +526,31 @@ __global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S, cons
       double *out_v = out_q + J, *out_a = out_q + 2 * J;
       const size_t stride = (size_t)4 * J;
       double a = a_0, v = v_0, q = q_0;
+      // the lane's share of the jerk fill: joint fr = lane / (32 / J), samples fl, fl + 32 / J, ...
+      const int lpj = 32 / J, fr = lane / lpj, fl = lane - fr * lpj;
+      int fs[7];
+      double fjp[7];
+#pragma unroll
+      for (int k = 0; k < 7; ++k) {
+        fs[k] = q_s[fr < J ? fr : 0].s[k];
+        fjp[k] = q_s[fr < J ? fr : 0].jp[k];
+      }
 #if defined(HRG_TASK_TRACE)
       unsigned long long tr_fill = 0, tr_cons = 0, tr_a = trace_now();
       const unsigned long long tr_init = tr_a - trace_t0;
 #endif
       for (int c0 = 0; c0 < len; c0 += kSampleChunk) {
         const int c1 = (c0 + kSampleChunk < len) ? c0 + kSampleChunk : len;
-        // fill: index i always belongs to lane (i - c0) & 31, so the phases can overwrite each other in the reference's
-        // order (jerk_reg_at: the LAST matching range wins) without a barrier
-        for (int r = 0; r < J; ++r) {
-          const JerkSamplerReg& R = q_s[r];
-          double* jb = jbuf_s[r];
-          for (int u = lane; u < c1 - c0; u += 32) jb[u] = 0.0;
-          int lo = -2147483647 - 1;
+        // fill: 32 / J lanes per joint, each evaluates the phase of its samples from the joint's switch indices held in
+        // registers (jerk_reg_at without the corrections: the LAST matching range wins) - branch free, all joints at once
+        if (fr < J) {
+          double* jb = jbuf_s[fr];
+          for (int u = fl; u < c1 - c0; u += lpj) {
+            const int i = c0 + u;
+            double jv = (i < fs[0]) ? fjp[0] : 0.0;
 #pragma unroll
-          for (int k = 0; k < 7; ++k) {
-            const int hi = R.s[k];
-            const int a0i = lo > c0 ? lo : c0, a1i = hi < c1 ? hi : c1;
-            if (a0i < a1i) {  // warp-uniform
-              const double jp = R.jp[k];
-              for (int i = a0i + ((lane - (a0i - c0)) & 31); i < a1i; i += 32) jb[i - c0] = jp;
-            }
-            lo = hi;
+            for (int k = 1; k < 7; ++k) jv = (i >= fs[k - 1] && i < fs[k]) ? fjp[k] : jv;
+            jb[u] = jv;
           }
         }
         __syncwarp(full);
@@ -624,8 +640,6 @@ __global__ void __launch_bounds__(kSampleBlock) k_replan_sample(DevState S, cons
       o.ok = ((ok && all_in) ? 1 : 0) | (int)trunc;
       o.slowest = len;
       S.plan_head[idx] = o;
-      if (TAIL) replan_tail_env(S, c, e, o, t[e]);  // (the samples it interpolates were written by this warp: visible after
-                                                    // the __syncwarp above, global memory is coherent within a thread block)
       HRG_TRACE_TASK(2, idx, len);
     }
     __syncwarp(full);  // q_s, jbuf_s are re-used by the next env

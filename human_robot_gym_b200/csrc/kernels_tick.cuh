@@ -19,6 +19,7 @@ __global__ void k_new_goal(DevState S, const uint8_t* __restrict__ mask, const d
 // goal_mask / goal_q != NULL: newLongTermTrajectory for the masked envs first (the tick entry points fold k_new_goal in).
 __global__ void __launch_bounds__(kTickBlock) k_pre(DevState S, const uint8_t* __restrict__ goal_mask,
                                                     const double* __restrict__ goal_q) {
+  HRG_TRACE_SPAN(5);
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= S.N) return;
   const HrgConfig& c = *S.cfg;
@@ -35,12 +36,16 @@ __global__ void __launch_bounds__(kTickBlock) k_pre(DevState S, const uint8_t* _
 
 // Middle part of step() for the envs that do NOT replan this tick (the others get it from k_replan_tail once their
 // new trajectory exists). Runs next to the replan chain.
-__global__ void __launch_bounds__(kTickBlock) k_plan(DevState S, const double* __restrict__ t) {
+// meas_t: the measurement time of a tick that measures (k_measure then runs NEXT to this kernel and writes the same value to
+// last_meas), NULL = the stored last_meas.
+__global__ void __launch_bounds__(kTickBlock) k_plan(DevState S, const double* __restrict__ t,
+                                                     const double* __restrict__ meas_t) {
+  HRG_TRACE_SPAN(6);
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= S.N || S.replan_mark[e]) return;
   const HrgConfig& c = *S.cfg;
   uint32_t f = S.flags[e];
-  plan_env(S, c, e, t[e], f);
+  plan_env(S, c, e, t[e], f, meas_t ? meas_t[e] : S.last_meas[e]);
   S.flags[e] = f;
 }
 
@@ -51,6 +56,7 @@ __global__ void __launch_bounds__(kTickBlock)
   // which: -1 = every env; 0 = the envs that did not replan this tick (runs while the replan chain is still busy: they are
   // 96 % of the batch and nothing of theirs depends on it); 1 = the replanned envs, and the tick's last launch (re-arms the
   // work counters).
+  HRG_TRACE_SPAN(which == 0 ? 10 : 12);
   constexpr int NC = 10;
   __shared__ unsigned long long s_cnt[NC];
   __shared__ double s_min;
@@ -58,11 +64,14 @@ __global__ void __launch_bounds__(kTickBlock)
   if (threadIdx.x < NC) s_cnt[threadIdx.x] = 0ull;
   if (threadIdx.x == 0) s_min = INFINITY;
   __syncthreads();
+  // re-arm the work lists for the next tick: each launch resets what only kernels BEFORE it on its own stream read
+  // (which 0 runs behind the cascade stages on the main stream, which 1 behind the replan chain and pass 1 on the side
+  // stream; the two may overlap)
   if (e == 0 && which != 0) {
     *S.replan_count = 0;
     for (int k = 0; k < N_CTR; ++k) S.replan_ctr[k] = 0;
-    S.verify_cnt[0] = S.verify_cnt[1] = 0;
   }
+  if (e == 0 && which != 1) S.verify_cnt[0] = S.verify_cnt[1] = 0;
   unsigned long long my[NC] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum, truncated, steps
   double my_min = INFINITY;
   if (e < S.N && (which < 0 || (int)S.replan_mark[e] == which)) {

@@ -235,6 +235,9 @@ HRG_HD_CALL double smallest_positive_real_root(const LtpLimits& L, const double*
       double margin;
       const double r = fr_root(coef, ncoef, margin);
       if (margin >= kRootMargin) return r;
+#if defined(__CUDA_ARCH__) && defined(HRG_TASK_TRACE)
+      HRG_TRACE_COUNT(1);
+#endif
     }
 #if defined(__CUDA_ARCH__) || defined(HRG_HOST_USE_RR)
     // one problem per lane: the register-resident solver (bit-identical, ltp_roots_reg.cuh) for the planner's degrees

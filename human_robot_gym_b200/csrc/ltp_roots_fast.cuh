@@ -19,7 +19,8 @@
 // point, or at the cut, is measured in units of that noise; the smallest such ratio is returned as `margin`, and the
 // caller runs the exact restatement of the QR iteration (ltp_roots_reg.cuh) whenever margin < kRootMargin, so decisions
 // stay those of the reference. The same noise bounds how far the iteration's VALUE of an ill-conditioned root can be
-// from the true one (noise / |p'(r)|): a root it could move by more than 1e-9 relative is handed over as well.
+// from the true one (noise / |p'(r)|): a root it could move by more than 1e-11 relative (1e-7 at kRootMargin units of
+// noise) is handed over as well.
 // Validation: profiles/r02k_root_check.md (device check mode over > 1e7 polynomials of the bench workload) and
 // tests/test_golden_vectors.py::test_fast_roots_*.
 #pragma once
@@ -29,6 +30,7 @@ namespace hrg {
 #define HRG_FR_UNROLL _Pragma("unroll")
 constexpr double kRootCut = 1e-7;        // roots.h:46
 constexpr double kRootMargin = 1e4;      // |p| below this many units of the QR iteration's noise: the exact path decides
+constexpr double kRootValueTol = 1e-7;   // relative distance the iteration's noise may move a root that is still trusted
 
 // NMAX = compile-time bound on the degree (array sizes, unrolling), n = the degree at run time (n <= NMAX). With n == NMAX a
 // literal the guards fold away; with NMAX = 6 and n = 4..6 one instruction stream serves lanes of different degrees
@@ -158,10 +160,11 @@ HRG_HD int fr_level(const FastRootPoly<NMAX>& P, bool top, double a, double B, c
       const double r = fr_bracket<NMAX, K>(P, lo, hi, flo, fhi, top);
       if (top) {
         // the VALUE is a close call too when the root is ill conditioned: the QR iteration's noise moves it by
-        // noise / |p'(r)|; trusted only while that stays below 1e-9 relative (scaled so that kRootMargin is the threshold)
+        // noise / |p'(r)|; trusted only while kRootMargin units of noise stay below kRootValueTol relative (the bound is
+        // generous: the largest difference seen on 9 M planner polynomials is 8e-10, profiles/r02k_root_check.md)
         double gr, dgr;
         fr_eval<NMAX, K>(P, r, gr, dgr);
-        margin = fmin(margin, fr_margin<NMAX, K>(P, r, dgr * r, normC) * (kRootMargin * 1e-9));
+        margin = fmin(margin, fr_margin<NMAX, K>(P, r, dgr * r, normC) * (kRootMargin * kRootValueTol));
         first = r;
         return 1;
       }
@@ -218,11 +221,12 @@ struct FrChain<NMAX, 2> {
   }
 };
 
-// coef[0] x^n + ... + coef[n], 3 <= n <= NMAX. Returns the smallest real root > 1e-7 (INFINITY if none) and, in `margin`,
+// coef[0] x^n + ... + coef[n], 3 <= n <= NMAX. Returns the smallest real root > cut (1e-7: roots.h:46; ltp_scaling.cuh also
+// asks for the smallest root above the noise range of a root cluster at 0) - INFINITY if none - and, in `margin`,
 // how many units of the QR iteration's noise the closest call was away (0: degenerate input) - below kRootMargin the
 // exact path must decide.
 template <int NMAX>
-HRG_HD double fr_solve(const double* coef, int n, double& margin) {
+HRG_HD double fr_solve(const double* coef, int n, double& margin, double cut = kRootCut) {
   margin = INFINITY;
   FastRootPoly<NMAX> P;
   double cmax = 0.0;
@@ -261,7 +265,8 @@ HRG_HD double fr_solve(const double* coef, int n, double& margin) {
     }
   }
   double R[NMAX], first = INFINITY;
-  FrChain<NMAX, NMAX>::run(P, n, kRootCut, B, R, first, margin);
+  if (!(B > cut)) return INFINITY;  // no root above the cut
+  FrChain<NMAX, NMAX>::run(P, n, cut, B, R, first, margin);
   return first;
 }
 

@@ -8,6 +8,7 @@
 // (SS/include/safety_shield/safety_shield.h:70-293).
 #pragma once
 #include "geom_math.cuh"
+#include "task_trace.cuh"
 
 namespace hrg {
 

@@ -118,7 +118,9 @@ HRG_HD void potential_env(const DevState& S, const HrgConfig& c, int e, uint32_t
 }
 
 // Middle part of step() (:606-637): potential trajectory, joint-limit check, hand-over to reach + verify.
-HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uint32_t& f) {
+// `last_meas` = HumanReach::last_meas_timestep_ (S.last_meas[e], or - inside a tick that measures - the tick's own
+// measurement time, so that this part does not have to wait for k_measure).
+HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uint32_t& f, double last_meas) {
   const int J = S.J, N = S.N;
   const uint32_t type = (f & F_TYPE_MASK) >> F_TYPE_SHIFT;
   // :612-614
@@ -144,7 +146,7 @@ HRG_HD void plan_env(const DevState& S, const HrgConfig& c, int e, double t, uin
           cq[j] = cur_at(S, j, e);
           al[j] = S.ltt_alpha[((size_t)gslot * J + j) * N + e];  // getAlphaI() (:606-610)
         }
-      const double cur_s = cur_at(S, 4 * J, e), last = S.last_meas[e];
+      const double cur_s = cur_at(S, 4 * J, e), last = last_meas;
       HRG_UNROLL
       for (int j = 0; j < HRG_MAX_JOINTS; ++j)
         if (j < J) {

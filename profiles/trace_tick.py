@@ -31,7 +31,11 @@ total = W + 8
 t_d = (torch.arange(total, dtype=torch.float64, device=dev) * bench.SAMPLE_TIME)[:, None].expand(total, n).contiguous()
 L = cabi.load_library()
 L.hrg_trace_read.argtypes = [C.c_void_p]
+L.hrg_trace_read_spans.argtypes = [C.c_void_p]
 buf = np.zeros((4, 1 << 15, 4), dtype=np.uint64)
+spans = np.zeros((16, 2), dtype=np.uint64)
+SPAN_NAMES = {0: "k_replan_plan", 1: "k_replan_deep", 2: "k_replan_sample", 4: "k_measure", 5: "k_pre", 6: "k_plan", 7: "k_reach_verify p0",
+              8: "k_verify_stage<1>", 9: "k_verify_stage<2>", 10: "k_select (not replanned)", 11: "k_reach_verify p1", 12: "k_select (last)"}
 
 
 def tick(k):
@@ -44,10 +48,17 @@ for k in range(W):
 torch.cuda.synchronize()
 res = []
 for k in range(W, W + 3):
-    assert L.hrg_trace_read(buf.ctypes.data) == 0
+    assert L.hrg_trace_read(buf.ctypes.data) == 0 and L.hrg_trace_read_spans(spans.ctypes.data) == 0
     tick(k)
     torch.cuda.synchronize()
-    assert L.hrg_trace_read(buf.ctypes.data) == 0
+    assert L.hrg_trace_read(buf.ctypes.data) == 0 and L.hrg_trace_read_spans(spans.ctypes.data) == 0
+    sp = spans.astype(np.int64)
+    ok = sp[:, 1] > 0
+    z0 = sp[ok, 0].min()
+    print(f"tick {k} timeline (us from the first block of the tick):")
+    for i in np.argsort(np.where(ok, sp[:, 0], np.iinfo(np.int64).max)):
+        if ok[i]:
+            print(f"    {SPAN_NAMES.get(int(i), i):26s} {(sp[i, 0] - z0) / 1e3:7.1f} -> {(sp[i, 1] - z0) / 1e3:7.1f}  ({(sp[i, 1] - sp[i, 0]) / 1e3:6.1f})")
     res.append(buf.copy())
     t00 = None
     r3 = buf[3]
@@ -73,5 +84,11 @@ for k in range(W, W + 3):
         # the slowest tasks
         order = np.argsort(-d)[:5]
         print("      slowest:", [(int(np.flatnonzero(m)[i]), round(float(d[i]), 1), int(sm[i]), int(r[m, 3][i])) for i in order])
+cnt = np.zeros(4, dtype=np.uint64)
+L.hrg_trace_read_counts.argtypes = [C.c_void_p]
+L.hrg_trace_read_counts(cnt.ctypes.data)
+st = shield.stats()
+print(f"exact QR solves over {W + 3} ticks ({st['n_replan']} replans): deep phase B {cnt[0]}, inline close calls {cnt[1]}; "
+      f"candidates settled by the rest-start rule {cnt[2]}")
 if out:
     np.savez_compressed(out, trace=np.stack(res))

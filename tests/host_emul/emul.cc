@@ -29,7 +29,7 @@ void hrg_poly_log(const double* coef, int ncoef) {
 #include "../../human_robot_gym_b200/csrc/kernels_human.cuh"
 
 #if defined(HRG_CAND_LOG)
-#include "/tmp/emul_tr/candlog.inc"
+#include "../../profiles/candlog.inc"  // host experiment of profiles/rest_start_candidates.py
 #endif
 using namespace hrg;
 
@@ -260,7 +260,7 @@ void emul_step(void* h, const double* t, double* q, double* dq, double* ddq, dou
       f &= ~F_PENDING_REPLAN;
       f |= st << F_STATUS_SHIFT;
     }
-    plan_env(S, c, e, t[e], f);
+    plan_env(S, c, e, t[e], f, S.last_meas[e]);
     if (f & F_VERIFY) emul_reach_verify(E, e, f);
     select_env(S, c, e, f, q, dq, ddq, dddq);
     f |= F_NEW_LTT_PROCESSED | F_STEPPED;

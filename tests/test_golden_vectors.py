@@ -399,11 +399,12 @@ def test_capsule_markers_match_reference_plot_capsule():
 # ---- the derivative-chain root finder (csrc/ltp_roots_fast.cuh) against the exact restatement of roots.h:22-50 ---------
 # HrgConfig.root_mode 1 (the product default) answers "smallest real root > 1e-7" without the companion-matrix QR iteration
 # and hands the close calls (margin < kRootMargin = 1e4 units of the QR iteration's noise) to the exact path. Pinned here:
-# wherever the margin is trusted the verdict root / no root is the QR iteration's and the value agrees to 1e-9 relative.
+# wherever the margin is trusted the verdict root / no root is the QR iteration's and the value agrees to 1e-9 relative on
+# the planner's own polynomials (1e-7 = kRootValueTol on adversarial ones).
 ROOT_MARGIN = 1e4
 
 
-def _check_fast_roots(coefs, what):
+def _check_fast_roots(coefs, what, tol=1e-9):
     fast, margin, exact = emul.poly_root_fast_batch(coefs)
     assert not (margin == -1).any(), f"{what}: mixed-degree and per-degree form differ"
     trusted = margin >= ROOT_MARGIN
@@ -412,7 +413,7 @@ def _check_fast_roots(coefs, what):
     assert not bad_class.any(), f"{what}: verdict differs on {coefs[bad_class][:3]} (margin {margin[bad_class][:3]})"
     both = trusted & fin_f & fin_e
     rel = np.abs(fast[both] - exact[both]) / np.abs(exact[both])
-    assert rel.size == 0 or rel.max() < 1e-9, f"{what}: root differs by {rel.max()}"
+    assert rel.size == 0 or rel.max() < tol, f"{what}: root differs by {rel.max()}"
     return trusted.mean(), (rel.max() if rel.size else 0.0)
 
 
@@ -440,7 +441,9 @@ def test_fast_roots_near_double_roots(deg):
         e = rng.choice([0.0, 0.0, 1e-14, -1e-14, 1e-10, -1e-10, 1e-6, -1e-6]) * np.abs(p).max()
         p[-1] += e
         rows.append(p)
-    frac, worst = _check_fast_roots(np.array(rows), f"near-double degree {deg}")
+    # kRootValueTol: a trusted root is one the QR iteration's noise cannot move by more than 1e-7 relative
+    frac, worst = _check_fast_roots(np.array(rows), f"near-double degree {deg}", tol=1e-7)
+    print(f"degree {deg}: trusted {frac:.3f}, worst relative difference {worst:.2e}")
     assert 0.2 < frac < 0.95                          # the merged pairs are NOT trusted, the separated ones are
 
 
