@@ -214,13 +214,28 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def traffic_per_launch(kernel):
-    """dram bytes per launch of `kernel` from the committed ncu --set full summary, if one exists."""
-    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-    if os.path.exists(p):
-        with open(p) as f:
-            return json.load(f).get(kernel)
-    return None
+def _ncu_table(fname, kernel, n_envs, replans):
+    """Per-tick figure of launch group `kernel` from a committed ncu capture of one steady-state tick at 65 536 envs
+    (profiles/ncu_summarize.py), scaled to this run: the replan chain by the replans per tick, the rest by the batch."""
+    p = os.path.join(ROOT, "profiles", fname)
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        d = json.load(f)
+    if kernel not in d:
+        return None
+    scale = replans / d["_replans_in_captured_tick"] if kernel == "k_replan" else n_envs / d["_envs"]
+    return d[kernel] * scale
+
+
+def traffic_per_launch(kernel, n_envs=65536, replans=1117):
+    """dram__bytes_read.sum + dram__bytes_write.sum per tick of launch group `kernel` (ncu, profiles/roofline_traffic.json)."""
+    return _ncu_table("roofline_traffic.json", kernel, n_envs, replans)
+
+
+def fp64_inst_per_launch(kernel, n_envs=65536, replans=1117):
+    """Thread-level FP64 add + mul + fma instructions per tick of launch group `kernel` (ncu, profiles/fp64_counts.json)."""
+    return _ncu_table("fp64_counts.json", kernel, n_envs, replans)
 
 
 def run_reference(args, files, sc, names, rank):
@@ -641,10 +656,19 @@ def main():
         dom_ms = kms[dom] / max(ksteps, 1)
         alg = alg_bytes[dom]
         achieved = alg / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
-        per_kernel = {kk: {"ms": kms[kk] / max(ksteps, 1), "algorithmic_bytes": alg_bytes[kk],
-                           "GBps": alg_bytes[kk] / (kms[kk] / max(ksteps, 1) / 1e3) / 1e9 if kms[kk] > 0 else 0.0,
-                           "frac_of_hbm_peak": alg_bytes[kk] / (kms[kk] / max(ksteps, 1) / 1e3) / 1e9 / peak
-                           if kms[kk] > 0 else 0.0} for kk in kms}
+        # FP-pipe side of the roofline: ncu-counted thread-level FP64 instructions per tick over the CUDA-event time of the
+        # group, against the measured register-resident DMUL + DADD issue rate (the library is compiled -fmad=false; the
+        # few DFMA are the ones inside division / sqrt)
+        ginst_peak = fp64_peak["dmul_dadd"]["ginst"] * 1e9 if fp64_peak else None
+        per_kernel = {}
+        for kk in kms:
+            k_ms = kms[kk] / max(ksteps, 1)
+            gbps = alg_bytes[kk] / (k_ms / 1e3) / 1e9 if k_ms > 0 else 0.0
+            inst = fp64_inst_per_launch(kk, N, replans_per_step)
+            per_kernel[kk] = {"ms": k_ms, "algorithmic_bytes": alg_bytes[kk], "GBps": gbps, "frac_of_hbm_peak": gbps / peak,
+                              "traffic": traffic_per_launch(kk, N, replans_per_step), "fp64_thread_inst": inst,
+                              "fp64_frac": inst / (k_ms / 1e3) / ginst_peak if inst and ginst_peak and k_ms > 0 else None}
+        dom_fp64 = per_kernel[dom]["fp64_frac"]
         b_tick = 48 * K + 770 + 136 * J
         b_step = b_tick + (32 * J * L_mean + 16 * J) / GOAL_PERIOD
         value = n_total * S / (ms_total / 1e3)
@@ -656,13 +680,18 @@ def main():
                        "l2_note": f"per-step working set {N * b_tick / 1e6:.0f} MB of state + {N * K * 24 / 1e6:.0f} MB "
                                   "of new keypoints exceeds the 126 MB L2; no explicit flush",
                        "ltt_capacity": args.ltt_capacity, "mean_ltt_len": L_mean},
-            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic_per_launch(dom), "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg, "kernel_ms": dom_ms,
-                         "note": "k_replan = the four k_replan_* launches of one tick, timed serially (in the timed "
-                                 "region they overlap k_reach_verify pass 0 on a second stream); latency bound: FP64 pipe "
-                                 "24 / 23 / 14 / 15 % busy in opt / scale / deep / sample (ncu, "
-                                 "profiles/r01l_replan_ncu_summary.md)"},
+            "roofline": {"bound": "hbm" if not dom_fp64 or achieved / peak >= dom_fp64 else "fp64", "kernel": dom,
+                         "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic_per_launch(dom, N, replans_per_step), "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg, "kernel_ms": dom_ms, "fp64_frac": dom_fp64,
+                         "fp64_peak_ginst": fp64_peak["dmul_dadd"]["ginst"] if fp64_peak else None,
+                         "note": "dominant launch group by CUDA-event time of the serialised profile pass (in the timed region "
+                                 "the replan chain and the bulk kernels run on two streams). achieved / frac: algorithmic bytes "
+                                 "over that time against the measured HBM peak; fp64_frac: ncu-counted FP64 thread instructions "
+                                 "(profiles/fp64_counts.json) over the same time against the measured DMUL+DADD issue rate; "
+                                 "`bound` names the larger. k_reach_verify is FP64-issue bound (pipe 21-35 % busy at 30 % "
+                                 "occupancy), k_replan a dependent-latency chain of a few thousand problems "
+                                 "(profiles/r02x_ncu_summary.md)"},
             "kernel_ms_per_step": {kk: v / max(ksteps, 1) for kk, v in kms.items()},
             "kernel_ms_per_launch": {kk: v / max(ksteps, 1) for kk, v in kdetail.items() if v > 0},
             "fp64_peak_measured": fp64_peak,
