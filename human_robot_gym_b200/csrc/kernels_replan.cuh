@@ -29,7 +29,7 @@
 
 namespace hrg {
 
-enum { CTR_PLAN = 0, CTR_SAMPLE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, N_CTR = 4 };
+enum { CTR_PLAN = 0, CTR_SAMPLE = 1, CTR_DEEP = 2, CTR_DEEP_COUNT = 3, CTR_SELECT_DONE = 4, N_CTR = 5 };
 // Residency: a tick has up to N / 25 replanning envs (2 621 at 65 536) and every task wants a warp of its own AT ONCE - a
 // second round doubles the kernel. Registers per thread are capped accordingly (148 SMs x minBlocks warps).
 #ifndef HRG_PLAN_MINBLOCKS

@@ -78,7 +78,7 @@ struct DevState {
   double* min_dist;   // [3][N]
   int32_t* replan_list;   // [N]
   int32_t* replan_count;  // [1]
-  int32_t* replan_ctr;    // [4] work counters of the replan kernels + length of the deep list (kernels_replan.cuh CTR_*)
+  int32_t* replan_ctr;    // [N_CTR] work counters of the replan kernels + length of the deep list (kernels_replan.cuh CTR_*)
   PlanRec* plan_opt;      // [N][HRG_MAX_JOINTS] time-optimal plan per joint (k_replan_plan); len = this joint ok
   PlanRec* plan_sc;       // [N][HRG_MAX_JOINTS] plan scaled to the slowest joint (k_replan_plan / k_replan_sample); len < 0 = -(deep slot + 1)
   PlanHead* plan_head;    // [N]
