@@ -237,6 +237,21 @@ class BatchedSafetyShield:
         cabi.check(self.lib.hrg_shield_stats(self._h, _ptr(self._stats), int(clear), self._stream()), "hrg_shield_stats")
         return self._stats
 
+    def state_dict(self) -> dict:
+        """Checkpoint of every env's shield state (hrg_shield_state_save): paths, flags, both long-term-trajectory slots,
+        the human measurement history, base poses, statistics. Call between ticks; synchronises the device."""
+        n = int(self.lib.hrg_shield_state_bytes(self._h))
+        blob = torch.empty(n, dtype=torch.uint8)
+        with torch.cuda.device(self.device):
+            cabi.check(self.lib.hrg_shield_state_save(self._h, blob.data_ptr(), n), "hrg_shield_state_save")
+        return {"blob": blob, "n_envs": self.n_envs, "nb_joints": self.J, "ltt_capacity": self.ltt_capacity}
+
+    def load_state_dict(self, state: dict):
+        """Restore a state_dict() of a shield of the same shape; the next tick continues bit-identically."""
+        blob = state["blob"].contiguous()
+        with torch.cuda.device(self.device):
+            cabi.check(self.lib.hrg_shield_state_load(self._h, blob.data_ptr(), blob.numel()), "hrg_shield_state_load")
+
     def profile(self, max_steps: int):
         cabi.check(self.lib.hrg_shield_profile(self._h, int(max_steps)), "hrg_shield_profile")
 

@@ -140,6 +140,9 @@ SYMBOLS = {
     "hrg_human_keypoints": (C.c_int, [C.c_void_p, C.c_void_p, _dp, _i32p, _i32p, _vp]),
     "hrg_shield_tick_replay_host": (C.c_int, [C.c_void_p, C.c_void_p] + [C.c_void_p] * 8 + [_vp]),
     "hrg_human_launch_count": (C.c_int64, [C.c_void_p]),
+    "hrg_shield_state_bytes": (C.c_int64, [C.c_void_p]),
+    "hrg_shield_state_save": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
+    "hrg_shield_state_load": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "hrg_microbench_fp64": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "hrg_microbench_fp64_latency": (C.c_int, [C.c_int, C.c_void_p]),
     "hrg_stage_capsule_dist": (C.c_int, [C.c_int, _dp, _dp, _dp, _vp]),

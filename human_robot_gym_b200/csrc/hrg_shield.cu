@@ -58,6 +58,7 @@ struct HrgShield {
   bool pfl = false;
   long long launches = 0;
   std::vector<void*> allocs;
+  std::vector<std::pair<void*, size_t>> persistent;  // what a checkpoint holds (hrg_shield_state_*)
   // staging for the *_host tick
   double* d_kp = nullptr;
   double* d_t = nullptr;
@@ -194,6 +195,15 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   AL(S.plan_sc, (size_t)N * HRG_MAX_JOINTS);
   AL(S.plan_head, N);
   AL(S.stats, 1);
+  // the state that survives a tick (everything else is scratch the next tick rewrites): SafetyShield members as SoA
+#define PERSIST(ptr, count) h->persistent.emplace_back((void*)(ptr), (size_t)(count) * sizeof(*(ptr)))
+  PERSIST(S.paths, (size_t)N_PATHS * PATH_FIELDS * N);
+  PERSIST(S.path_s, N); PERSIST(S.path_sd, N); PERSIST(S.flags, N);
+  PERSIST(S.prev_dq, (size_t)J * N); PERSIST(S.goal_q, (size_t)J * N); PERSIST(S.replan_q, (size_t)J * N);
+  PERSIST(S.ltt_len, 2 * N); PERSIST(S.ltt_cur, 2 * N); PERSIST(S.ltt_start, 2 * N);
+  PERSIST(S.ltt_t0, 2 * N); PERSIST(S.ltt_ts, 2 * N); PERSIST(S.ltt_alpha, (size_t)2 * J * N);
+  PERSIST(S.base_T, 12 * N); PERSIST(S.kp_pos, (size_t)K * 3 * N); PERSIST(S.kp_vel, (size_t)K * 3 * N);
+  PERSIST(S.last_meas, N); PERSIST(S.ltt, (size_t)N * 2 * L * 4 * J); PERSIST(S.stats, 1);
   S.ltt_cart = nullptr;
   S.robot_caps = nullptr;
   S.human_caps = nullptr;
@@ -346,6 +356,8 @@ int hrg_shield_enable_pfl(HrgShield* s) {
   s->S.ltt_cart = cart;
   s->S.ltt_time = tm;
   s->pfl = true;
+  s->persistent.emplace_back((void*)cart, nb);
+  s->persistent.emplace_back((void*)tm, nb);
   return HRG_OK;
 }
 

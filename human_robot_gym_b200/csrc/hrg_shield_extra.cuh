@@ -344,6 +344,62 @@ int hrg_microbench_fp64_latency(int device, double* cycles_host /*[6]*/) {
   return HRG_OK;
 }
 
+// ---- checkpoint (state_dict / load_state_dict of the new framework; no counterpart in the reference) ------
+// Blob = header {magic, N, J, K, L, pfl, n_segments, bytes} + the persistent arrays back to back.
+struct StateHeader {
+  uint64_t magic;
+  int32_t N, J, K, L, pfl, n_seg;
+  int64_t bytes;
+};
+constexpr uint64_t kStateMagic = 0x4852475348314c44ull;  // "HRGSH1LD"
+
+int64_t hrg_shield_state_bytes(const HrgShield* s) {
+  if (!s) return 0;
+  int64_t b = sizeof(StateHeader);
+  for (const auto& seg : s->persistent) b += (int64_t)seg.second;
+  return b;
+}
+
+int hrg_shield_state_save(HrgShield* s, void* dst_host, int64_t bytes) {
+  if (!s || !dst_host) return fail(HRG_EINVAL, "hrg_shield_state_save: NULL argument");
+  if (bytes < hrg_shield_state_bytes(s)) return fail(HRG_EINVAL, "hrg_shield_state_save: buffer smaller than hrg_shield_state_bytes");
+  CK(cudaSetDevice(s->device));
+  CK(cudaDeviceSynchronize());  // between ticks: nothing of this handle may be in flight
+  StateHeader h{kStateMagic, s->S.N, s->S.J, s->S.K, s->S.L, s->pfl ? 1 : 0, (int32_t)s->persistent.size(),
+                hrg_shield_state_bytes(s)};
+  char* p = static_cast<char*>(dst_host);
+  memcpy(p, &h, sizeof h);
+  p += sizeof h;
+  for (const auto& seg : s->persistent) {
+    CK(cudaMemcpy(p, seg.first, seg.second, cudaMemcpyDeviceToHost));
+    p += seg.second;
+  }
+  return HRG_OK;
+}
+
+int hrg_shield_state_load(HrgShield* s, const void* src_host, int64_t bytes) {
+  if (!s || !src_host) return fail(HRG_EINVAL, "hrg_shield_state_load: NULL argument");
+  StateHeader h;
+  if (bytes < (int64_t)sizeof h) return fail(HRG_EINVAL, "hrg_shield_state_load: truncated blob");
+  memcpy(&h, src_host, sizeof h);
+  if (h.magic != kStateMagic) return fail(HRG_EINVAL, "hrg_shield_state_load: not a shield state blob");
+  if (h.pfl && !s->pfl) {
+    if (int rc = hrg_shield_enable_pfl(s)) return rc;
+  }
+  if (h.N != s->S.N || h.J != s->S.J || h.K != s->S.K || h.L != s->S.L || h.pfl != (s->pfl ? 1 : 0) ||
+      h.n_seg != (int32_t)s->persistent.size() || h.bytes != hrg_shield_state_bytes(s) || bytes < h.bytes)
+    return fail(HRG_EINVAL, "hrg_shield_state_load: blob was saved from a handle of another shape (envs, joints, keypoints, "
+                            "ltt_capacity or PFL capability differ)");
+  CK(cudaSetDevice(s->device));
+  CK(cudaDeviceSynchronize());
+  const char* p = static_cast<const char*>(src_host) + sizeof h;
+  for (const auto& seg : s->persistent) {
+    CK(cudaMemcpy(seg.first, p, seg.second, cudaMemcpyHostToDevice));
+    p += seg.second;
+  }
+  return HRG_OK;
+}
+
 // ---- per-stage entry points ------------------------------------------------------------------------------------
 int hrg_stage_capsule_dist(int n, const double* c1, const double* c2, double* dist, void* stream) {
   if (n < 0 || !c1 || !c2 || !dist) return fail(HRG_EINVAL, "hrg_stage_capsule_dist: bad argument");

@@ -212,6 +212,14 @@ int hrg_shield_ltt_max_window(HrgShield* s, const int32_t* index, int window_k, 
 /* Accumulated statistics since the last clear; `out` is a DEVICE pointer to one HrgStats. */
 int hrg_shield_stats(HrgShield* s, HrgStats* out, int clear, void* stream);
 
+/* Checkpoint of every env's shield state (paths, flags, both long-term-trajectory slots, human measurement history, base
+ * poses, statistics) - SURVEY.md 5 "state_dict / load_state_dict"; the reference has no counterpart (its state lives in the
+ * C++ object). HOST buffers, synchronous, between ticks. A blob only loads into a handle of the same shape (envs, joints,
+ * keypoints, ltt_capacity); a PFL blob makes the handle PFL-capable. After a load the next tick continues bit-identically. */
+int64_t hrg_shield_state_bytes(const HrgShield* s);
+int hrg_shield_state_save(HrgShield* s, void* dst_host, int64_t bytes);
+int hrg_shield_state_load(HrgShield* s, const void* src_host, int64_t bytes);
+
 /* Per-kernel device timing of the tick for the next `max_steps` steps (0 = off): a CUDA event is recorded on the step's
  * stream after EVERY kernel launch of a step (the replan chain is not overlapped while profiling, so each interval is one
  * kernel). hrg_shield_profile_read_kernels synchronises on the last event and returns the summed milliseconds per launch

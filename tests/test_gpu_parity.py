@@ -378,3 +378,39 @@ def test_set_ltt_batch_equals_one_by_one():
     assert float(a.q[3].abs().max()) > 0 and float(a.q[1].abs().max()) == 0  # env 3 follows its user trajectory, env 1 rests
     a.close()
     b.close()
+
+
+@pytest.mark.gpu
+def test_state_dict_round_trip_is_bit_identical():
+    """state_dict / load_state_dict (hrg_shield_state_*): after a restore the closed loop repeats itself bit for bit, replans
+    and pending trajectories included; a blob of another shape is refused."""
+    from human_robot_gym_b200 import cabi
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    from human_robot_gym_b200.config import ShieldConfig
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+    files = pu.default_files("schunk")
+    sc = ShieldConfig.from_files(0.004, *files)
+    n = 300
+    scen = SyntheticScenario(n, pu.mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, 4242)
+    sh = BatchedSafetyShield(n, 0.004, *files, init_qpos=scen.init_q, device="cuda:0", ltt_capacity=512, config=sc)
+    goals = [torch.from_numpy(scen.next_goal()).cuda() for _ in range(4)]
+    mask = torch.from_numpy((np.arange(n) % 25)[None] == np.arange(25)[:, None]).to(torch.uint8).cuda()
+
+    def run(k0, k1):
+        out = []
+        for k in range(k0, k1):
+            t = torch.full((n,), k * 0.004, dtype=torch.float64, device="cuda:0")
+            kp = torch.from_numpy(scen.keypoints(k * 0.004)).cuda()
+            sh.tick_device(kp, t, mask[k % 25], goals[(k // 25) % 4])
+            out.append(torch.cat([sh.q.flatten(), sh.dq.flatten(), sh.ddq.flatten(), sh.is_safe.double(), sh.branch.double()]).clone())
+        return torch.stack(out)
+
+    run(0, 40)
+    state = sh.state_dict()
+    a = run(40, 90)
+    sh.load_state_dict(state)
+    b = run(40, 90)
+    assert torch.equal(a, b)
+    other = BatchedSafetyShield(n + 1, 0.004, *files, init_qpos=np.zeros((n + 1, 6)), device="cuda:0", ltt_capacity=512, config=sc)
+    with pytest.raises(cabi.ShieldLibraryError):
+        other.load_state_dict(state)
