@@ -95,7 +95,7 @@ def make_cfg(sc: ShieldConfig, ltt_capacity: int = 1024) -> HrgConfig:
 
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhrg_shield.so")
+LIB_PATH = os.environ.get("HRG_LIB_PATH") or os.path.join(_HERE, "libhrg_shield.so")  # HRG_LIB_PATH: profiling builds (profiles/build_trace.sh)
 _lib = None
 
 _vp, _dp, _u8p, _i32p, _u32p = C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p  # device pointers as ints

@@ -474,7 +474,7 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
     // only bound residency (one warp per block, so that the few hundred busy warps spread over all schedulers)
     const int J = s->S.J;
     const int cap = s->sm_count * 16;
-    int g_plan = grid_for(N, s->plan_envs_per_warp), g_samp = N, g_deep = grid_for(N * J, s->deep_per_warp);
+    int g_plan = grid_for(N, s->plan_envs_per_warp), g_samp = grid_for(N, kSampleEnvs), g_deep = grid_for(N * J, s->deep_per_warp);
     if (g_plan > cap) g_plan = cap;
     if (g_samp > s->sm_count * HRG_SAMPLE_MINBLOCKS) g_samp = s->sm_count * HRG_SAMPLE_MINBLOCKS;
     if (g_deep > cap) g_deep = cap;

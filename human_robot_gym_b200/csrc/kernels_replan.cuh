@@ -442,35 +442,59 @@ __device__ __forceinline__ void prefetch_tail_inputs(const DevState& S, int e, i
 // then lanes 0..J-1 integrate the chunk and stream the samples out.
 constexpr int kSampleBlock = 32;
 constexpr int kSampleChunk = 128;
+// Envs per warp: env g of a warp owns lanes [8g, 8g + J). The recurrence is one instruction stream for all of them, so two
+// envs per warp halve the warp instructions of the kernel (it is issue bound: 2 621 warps of ~12 k instructions on 592
+// schedulers) at the price of a loop as long as the longer of the two trajectories.
+#ifndef HRG_SAMPLE_ENVS
+#define HRG_SAMPLE_ENVS 2
+#endif
+constexpr int kSampleEnvs = HRG_SAMPLE_ENVS;
+static_assert(kSampleEnvs == 1 || kSampleEnvs == 2 || kSampleEnvs == 4, "envs per sampler warp");
 __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_sample(DevState S) {
   HRG_TRACE_SPAN(2);
-  __shared__ JerkSamplerReg q_s[HRG_MAX_JOINTS];
-  __shared__ double jbuf_s[HRG_MAX_JOINTS][kSampleChunk + 1];  // + 1: the J consumer lanes read one column of it
+  __shared__ JerkSamplerReg q_s[kSampleEnvs][HRG_MAX_JOINTS];
+  __shared__ double jbuf_s[kSampleEnvs][HRG_MAX_JOINTS][kSampleChunk + 1];  // + 1: the owner lanes read one column of it
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int J = S.J;
+  const int g = lane >> 3, jl8 = lane & 7;          // env slot of the lane, joint of the lane
+  const bool slot = g < kSampleEnvs;
+  const int gs = slot ? g : 0;
+  const int j = jl8 < J ? jl8 : 0;
   const int count = *S.replan_count;
+  // the lane's share of the jerk fill: the kSampleEnvs * J joints of the warp get 32 / (kSampleEnvs * J) lanes each
+  const int TJ = kSampleEnvs * J, lpj = 32 / TJ;
+  const int fr = lane / lpj, fl = lane - fr * lpj;
+  const bool filler = fr < TJ;
+  const int fg = filler ? fr / J : 0, fj = filler ? fr - (fr / J) * J : 0;
   for (;;) {
-    int idx = 0;
-    if (lane == 0) idx = atomicAdd(S.replan_ctr + CTR_SAMPLE, 1);
-    idx = __shfl_sync(full, idx, 0);
-    if (idx >= count) break;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(S.replan_ctr + CTR_SAMPLE, kSampleEnvs);
+    base = __shfl_sync(full, base, 0);
+    if (base >= count) break;
     HRG_TRACE_T0();
-    const int e = S.replan_list[idx];
-    prefetch_tail_inputs(S, e, lane);  // for k_replan_tail, which follows: one lane per env chasing ~100 cache lines
-    const int pend = (S.flags[e] & F_LIVE_SLOT) ? 0 : 1;
-    const PlanHead head = S.plan_head[idx];
-    bool ok = head.ok != 0;
-    const bool jl = lane < J;  // the lane that owns joint `lane`
-    const int j = lane < J ? lane : 0;
+    const int idx = base + gs;
+    const bool valid = slot && idx < count;
+    const bool own = valid && jl8 < J;  // the lane that owns joint j of env slot g
+    const int e = valid ? S.replan_list[idx] : -1;
+#pragma unroll
+    for (int k = 0; k < kSampleEnvs; ++k) {  // for k_replan_tail, which follows: one lane per env chasing ~100 cache lines
+      const int ek = __shfl_sync(full, e, 8 * k);
+      if (ek >= 0) prefetch_tail_inputs(S, ek, lane);
+    }
+    const int pend = (valid && (S.flags[e] & F_LIVE_SLOT)) ? 0 : 1;
+    PlanHead head;
+    head.ok = 0; head.slowest = -1; head.t_required = 0.0;
+    if (valid) head = S.plan_head[idx];
+    bool ok = valid && head.ok != 0;
     const LtpLimits L = joint_limits(c, j);
     JointPlan sc;
     ltp_zero7(sc.T);
     sc.dir = 0.0; sc.v_drive = 0.0; sc.mod = 0;
     double q_0 = 0.0, v_0 = 0.0, a_0 = 0.0;
     int len_j = 0;
-    if (jl) {
+    if (own) {
       q_0 = cur_at(S, j, e); v_0 = cur_at(S, J + j, e); a_0 = cur_at(S, 2 * J + j, e);
       if (ok) {
         PlanRec rec = S.plan_sc[(size_t)idx * HRG_MAX_JOINTS + j];
@@ -495,12 +519,12 @@ __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_s
         for (int k = 0; k < 7; ++k) sc.T[k] = rec.T[k];
         sc.dir = rec.dir; sc.v_drive = rec.v_drive; sc.mod = rec.mod;
         len_j = rec.len;
-        sampler_reg_init(L, sc, q_s[j]);
+        sampler_reg_init(L, sc, q_s[gs][j]);
       }
     }
     __syncwarp(full);
-    int len = len_j;  // trajectory length of the env = max over its joints (:716-719)
-    for (int o = 16; o >= 1; o >>= 1) {
+    int len = len_j;  // trajectory length of the env = max over its joints (:716-719): over the 8 lanes of its slot
+    for (int o = 4; o >= 1; o >>= 1) {
       const int other = __shfl_xor_sync(full, len, o);
       len = other > len ? other : len;
     }
@@ -513,39 +537,50 @@ __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_s
         ok = false;
       }
     }
+    const int len_run = ok ? len : 0;  // samples this slot integrates
+    int len_warp = len_run;            // ... and the longest of the warp
+    for (int o = 16; o >= 8; o >>= 1) {
+      const int other = __shfl_xor_sync(full, len_warp, o);
+      len_warp = other > len_warp ? other : len_warp;
+    }
+    const int flen = __shfl_sync(full, len_run, 8 * fg);  // length of the env whose joint this lane helps to fill
     bool in = true;
-    if (ok) {
+    {
       const double ts = L.t_sample;
       const double v_cruise = sc.v_drive * sc.dir;
-      const JerkSamplerReg& Q = q_s[j];
-      const int s6 = Q.s[6];
-      const int cr_lo = Q.s[2] + 1;
-      const bool phase4 = Q.s[3] - Q.s[2] > 2;
+      const JerkSamplerReg& Q = q_s[gs][j];
+      const bool run = own && ok;
+      const int s6 = run ? Q.s[6] : 0;
+      const int cr_lo = run ? Q.s[2] + 1 : 1;
+      const bool phase4 = run && Q.s[3] - Q.s[2] > 2;
       const unsigned cr_span = (phase4 && Q.s[3] - 1 > cr_lo) ? (unsigned)(Q.s[3] - 1 - cr_lo) : 0u;
-      double* out_q = ltt_sample_w(S, e, pend, 0) + j;  // sample i: [i * 4J + {0, J, 2J, 3J}] = q, v, a, j
+      double* out_q = run ? ltt_sample_w(S, e, pend, 0) + j : nullptr;  // sample i: [i * 4J + {0, J, 2J, 3J}] = q, v, a, j
       double *out_v = out_q + J, *out_a = out_q + 2 * J;
       const size_t stride = (size_t)4 * J;
       double a = a_0, v = v_0, q = q_0;
-      // the lane's share of the jerk fill: joint fr = lane / (32 / J), samples fl, fl + 32 / J, ...
-      const int lpj = 32 / J, fr = lane / lpj, fl = lane - fr * lpj;
       int fs[7];
       double fjp[7];
+      if (flen > 0) {
 #pragma unroll
-      for (int k = 0; k < 7; ++k) {
-        fs[k] = q_s[fr < J ? fr : 0].s[k];
-        fjp[k] = q_s[fr < J ? fr : 0].jp[k];
+        for (int k = 0; k < 7; ++k) {
+          fs[k] = q_s[fg][fj].s[k];
+          fjp[k] = q_s[fg][fj].jp[k];
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+          fs[k] = 0;
+          fjp[k] = 0.0;
+        }
       }
-#if defined(HRG_TASK_TRACE)
-      unsigned long long tr_fill = 0, tr_cons = 0, tr_a = trace_now();
-      const unsigned long long tr_init = tr_a - trace_t0;
-#endif
-      for (int c0 = 0; c0 < len; c0 += kSampleChunk) {
-        const int c1 = (c0 + kSampleChunk < len) ? c0 + kSampleChunk : len;
-        // fill: 32 / J lanes per joint, each evaluates the phase of its samples from the joint's switch indices held in
-        // registers (jerk_reg_at without the corrections: the LAST matching range wins) - branch free, all joints at once
-        if (fr < J) {
-          double* jb = jbuf_s[fr];
-          for (int u = fl; u < c1 - c0; u += lpj) {
+      for (int c0 = 0; c0 < len_warp; c0 += kSampleChunk) {
+        // fill: every joint of the warp gets 32 / (envs * J) lanes, each evaluates the phase of its samples from the
+        // joint's switch indices held in registers (jerk_reg_at without the corrections: the LAST matching range wins) -
+        // branch free, all joints at once
+        if (filler) {
+          double* jb = jbuf_s[fg][fj];
+          const int fn = (flen - c0 < kSampleChunk) ? flen - c0 : kSampleChunk;
+          for (int u = fl; u < fn; u += lpj) {
             const int i = c0 + u;
             double jv = (i < fs[0]) ? fjp[0] : 0.0;
 #pragma unroll
@@ -554,15 +589,10 @@ __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_s
           }
         }
         __syncwarp(full);
-#if defined(HRG_TASK_TRACE)
-        {
-          const unsigned long long nw = trace_now();
-          tr_fill += nw - tr_a;
-          tr_a = nw;
-        }
-#endif
-        if (jl) {  // the one-sample corrections of the lane's own joint, in slot order (two of them can hit one sample)
-          double* jb = jbuf_s[j];
+        if (run && c0 < len) {
+          const int c1 = (c0 + kSampleChunk < len) ? c0 + kSampleChunk : len;
+          double* jb = jbuf_s[gs][j];
+          // the one-sample corrections of the lane's own joint, in slot order (two of them can hit one sample)
 #pragma unroll
           for (int k = 0; k < 12; ++k) {
             const int ci = Q.cidx[k];
@@ -614,35 +644,21 @@ __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_s
           }
         }
         __syncwarp(full);
-#if defined(HRG_TASK_TRACE)
-        {
-          const unsigned long long nw = trace_now();
-          tr_cons += nw - tr_a;
-          tr_a = nw;
-        }
-#endif
       }
-#if defined(HRG_TASK_TRACE)
-      if (lane == 0 && idx < kTraceTasks) {
-        g_task_trace[3][idx][0] = tr_init;
-        g_task_trace[3][idx][1] = tr_fill;
-        g_task_trace[3][idx][2] = tr_cons;
-        g_task_trace[3][idx][3] = (unsigned long long)len;
-      }
-#endif
-      if (jl) in = !(q < c.q_min[j] || q > c.q_max[j]);  // (:59-61)
+      if (run) in = !(q < c.q_min[j] || q > c.q_max[j]);  // (:59-61)
     }
-    const bool all_in = __all_sync(full, in);  // every joint of the env must end inside its limits
-    if (lane == 0) {
+    const unsigned inb = __ballot_sync(full, in);
+    const bool all_in = ((inb >> (8 * gs)) & 0xffu) == 0xffu;  // every joint of the env must end inside its limits
+    if (valid && jl8 == 0) {
       // verdict for k_pfl_ltt / k_replan_tail: bit 0 = trajectory written and valid, bit 1 = longer than the slot;
       // slowest = its length
       PlanHead o = head;
       o.ok = ((ok && all_in) ? 1 : 0) | (int)trunc;
       o.slowest = len;
       S.plan_head[idx] = o;
-      HRG_TRACE_TASK(2, idx, len);
     }
-    __syncwarp(full);  // q_s, jbuf_s are re-used by the next env
+    HRG_TRACE_TASK(2, base / kSampleEnvs, len_warp);
+    __syncwarp(full);  // q_s, jbuf_s are re-used by the next envs
   }
 }
 
