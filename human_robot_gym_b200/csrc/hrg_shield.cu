@@ -84,6 +84,8 @@ struct HrgShield {
   cudaStream_t side = nullptr, meas = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_meas = nullptr;
   bool overlap = true;
+  bool pdl_now = false;  // (pdl && this tick runs forked: verify_pass0 reads it)
+  int pdl = 0;  // programmatic dependent launch (HRG_PDL): 0 off, 1 on the replan chain's stream, 2 on both branches
   bool debug_sync = false;
   int deep_per_warp = 2;  // deep-list joints per warp of k_replan_deep, <= 4 (HRG_DEEP_PER_WARP)
   int plan_envs_per_warp = 2;  // envs per warp of k_replan_plan, <= 16 / J (HRG_PLAN_ENVS_PER_WARP)
@@ -108,6 +110,22 @@ struct HrgShield {
 };
 
 namespace {
+// Launch with programmatic stream serialisation (pdl): the kernel may be staged while its predecessor on the stream still
+// runs and synchronises on it with hrg_grid_dep_wait() - takes the ~3.5 us launch gap off a kernel boundary.
+template <class... KArgs, class... Args>
+inline cudaError_t launch_k(void (*k)(KArgs...), int grid, int block, size_t smem, cudaStream_t st, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, k, static_cast<KArgs>(args)...);
+}
 inline int grid_for(int n, int block) { return (n + block - 1) / block; }
 inline int tile_grid(int n) { return (n + kTileEnvs - 1) / kTileEnvs; }
 
@@ -249,6 +267,7 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
     cudaDeviceGetStreamPriorityRange(&lo, &hi);
     ce = cudaStreamCreateWithPriority(&h->side, cudaStreamNonBlocking, hi);
     if (const char* v = getenv("HRG_NO_OVERLAP")) h->overlap = !(atoi(v) > 0);
+    if (const char* v = getenv("HRG_PDL")) h->pdl = atoi(v);
     if (const char* v = getenv("HRG_NO_CASCADE")) h->cascade = !(atoi(v) > 0);
     if (const char* v = getenv("HRG_DEBUG_SYNC")) h->debug_sync = atoi(v) > 0;
     h->plan_envs_per_warp = 16 / J > 2 ? 2 : 16 / J;
@@ -407,9 +426,9 @@ static void verify_pass0(HrgShield* s, cudaStream_t st, size_t smem, Mark&& mark
     if (stage_smem < (size_t)J * kTileEnvs * sizeof(double)) stage_smem = (size_t)J * kTileEnvs * sizeof(double);
     k_reach_verify<1, true><<<tile_grid(N), 32 * J, smem, st>>>(s->S, 0);
     mark(HRG_PROF_VERIFY_P0);
-    k_verify_stage<1><<<tile_grid(N), 32 * J, stage_smem, st>>>(s->S);
+    launch_k(k_verify_stage<1>, tile_grid(N), 32 * J, stage_smem, st, s->pdl_now, s->S);
     mark(HRG_PROF_STAGE_VEL);
-    k_verify_stage<2><<<tile_grid(N), 32 * J, stage_smem, st>>>(s->S);
+    launch_k(k_verify_stage<2>, tile_grid(N), 32 * J, stage_smem, st, s->pdl_now, s->S);
     mark(HRG_PROF_STAGE_ACC);
     s->launches += 2;
   } else {
@@ -442,6 +461,8 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
   };
   mark(-1);
   const bool fork = s->overlap && !prof;
+  const bool pdl = fork && s->pdl >= 1;  // (the profile pass records an event between the kernels: ordinary launches)
+  s->pdl_now = fork && s->pdl >= 2;
   // In a tick that measures, the measurement time IS t: the path planning takes it from there instead of waiting for
   // k_measure to store it (k_measure writes the same value to last_meas)
   const double* meas_t = kp ? t : nullptr;
@@ -480,9 +501,9 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
     if (g_deep > cap) g_deep = cap;
     k_replan_plan<<<g_plan, kReplanBlock, 0, rs>>>(s->S, s->plan_envs_per_warp);
     mark(HRG_PROF_PLAN_LTT);
-    k_replan_deep<<<g_deep, kReplanBlock, 0, rs>>>(s->S, s->deep_per_warp);
+    launch_k(k_replan_deep, g_deep, kReplanBlock, 0, rs, pdl, s->S, s->deep_per_warp);
     mark(HRG_PROF_DEEP);
-    k_replan_sample<<<g_samp, kSampleBlock, 0, rs>>>(s->S);
+    launch_k(k_replan_sample, g_samp, kSampleBlock, 0, rs, pdl, s->S);
     mark(HRG_PROF_SAMPLE);
     if (s->pfl) {
       int pgrid = s->sm_count * 8;
@@ -491,7 +512,7 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
       mark(HRG_PROF_PFL);
       s->launches++;
     }
-    k_replan_tail<<<grid_for(N, 128), 128, 0, rs>>>(s->S, t, meas_t);
+    launch_k(k_replan_tail, grid_for(N, 128), 128, 0, rs, pdl && !s->pfl, s->S, t, meas_t);
     mark(HRG_PROF_TAIL);
   }
   if (fork) {
@@ -511,7 +532,8 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
     }
     verify_pass0(s, st, s->reach_smem_p0, mark);
     // determineNextMotion of the envs that did not replan
-    k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, st>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status, 0);
+    launch_k(k_select, grid_for(N, kTickBlock), kTickBlock, 0, st, s->pdl_now && s->cascade && !s->S.human_caps, s->S, q, dq, ddq, dddq,
+             is_safe, branch, status, 0);
     s->launches++;
   } else {
     verify_pass0(s, st, s->reach_smem, mark);
@@ -519,7 +541,8 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
   // the replanned envs: reach + verify pass 1 and determineNextMotion, behind the chain (fork: on its stream)
   k_reach_verify<2><<<tile_grid(N), 32 * s->S.J * 2, s->reach_smem, rs>>>(s->S, 1);
   mark(HRG_PROF_VERIFY_P1);
-  k_select<<<grid_for(N, kTickBlock), kTickBlock, 0, rs>>>(s->S, q, dq, ddq, dddq, is_safe, branch, status, fork ? 1 : -1);
+  launch_k(k_select, grid_for(N, kTickBlock), kTickBlock, 0, rs, pdl, s->S, q, dq, ddq, dddq, is_safe, branch, status,
+           fork ? 1 : -1);
   mark(HRG_PROF_SELECT);
   if (fork) {
     keep(cudaEventRecord(s->ev_join, s->side));

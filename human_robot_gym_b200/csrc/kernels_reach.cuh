@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS,
                                   PARTS == 1 ? (CASCADE ? HRG_CASCADE_MINBLOCKS : HRG_REACH_MINBLOCKS) : 1)
     k_reach_verify(DevState S, int pass) {
   HRG_TRACE_SPAN(pass == 0 ? 7 : 11);
+  hrg_grid_dep_launch();
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
   __shared__ unsigned bits_s[HRG_MAX_JOINTS * PARTS][kTileEnvs];
@@ -277,6 +278,8 @@ __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32 * PARTS,
 template <int MODEL>
 __global__ void __launch_bounds__(HRG_MAX_JOINTS * 32, HRG_STAGE_MINBLOCKS) k_verify_stage(DevState S) {
   HRG_TRACE_SPAN(7 + MODEL);
+  hrg_grid_dep_wait();
+  hrg_grid_dep_launch();
   extern __shared__ double smem[];
   __shared__ HrgConfig cfg_s;
   __shared__ unsigned bits_s[HRG_MAX_JOINTS][kTileEnvs];

@@ -88,6 +88,7 @@ __device__ __forceinline__ int fetch_warp_tasks(int32_t* ctr, int per_warp, int 
 //      (1) is rejected, so half 0's result wins when both are accepted.
 __global__ void __launch_bounds__(kReplanBlock, HRG_PLAN_MINBLOCKS) k_replan_plan(DevState S, int envs_per_warp) {
   HRG_TRACE_SPAN(0);
+  hrg_grid_dep_launch();
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -217,6 +218,8 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_PLAN_MINBLOCKS) k_replan_pla
 // With root_mode 0 every candidate is a close call by definition and B is the whole kernel.
 __global__ void __launch_bounds__(kReplanBlock) k_replan_deep(DevState S, int joints_per_warp) {
   HRG_TRACE_SPAN(1);
+  hrg_grid_dep_wait();
+  hrg_grid_dep_launch();
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -405,6 +408,8 @@ __device__ __forceinline__ void replan_tail_env(const DevState& S, const HrgConf
 // runs at half speed - both measured, profiles/r02_summary.md). PFL handles run k_pfl_ltt between the two.
 __global__ void __launch_bounds__(128) k_replan_tail(DevState S, const double* __restrict__ t,
                                                      const double* __restrict__ meas_t) {
+  hrg_grid_dep_wait();
+  hrg_grid_dep_launch();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= *S.replan_count) return;
   const int e = S.replan_list[idx];
@@ -452,6 +457,8 @@ constexpr int kSampleEnvs = HRG_SAMPLE_ENVS;
 static_assert(kSampleEnvs == 1 || kSampleEnvs == 2 || kSampleEnvs == 4, "envs per sampler warp");
 __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_sample(DevState S) {
   HRG_TRACE_SPAN(2);
+  hrg_grid_dep_wait();
+  hrg_grid_dep_launch();
   __shared__ JerkSamplerReg q_s[kSampleEnvs][HRG_MAX_JOINTS];
   __shared__ double jbuf_s[kSampleEnvs][HRG_MAX_JOINTS][kSampleChunk + 1];  // + 1: the owner lanes read one column of it
   const HrgConfig& c = *S.cfg;

@@ -57,6 +57,8 @@ __global__ void __launch_bounds__(kTickBlock)
   // 96 % of the batch and nothing of theirs depends on it); 1 = the replanned envs, and the tick's last launch (re-arms the
   // work counters).
   HRG_TRACE_SPAN(which == 0 ? 10 : 12);
+  hrg_grid_dep_wait();
+  hrg_grid_dep_launch();
   constexpr int NC = 10;
   __shared__ unsigned long long s_cnt[NC];
   __shared__ double s_min;

@@ -10,6 +10,18 @@
 #include "geom_math.cuh"
 #include "task_trace.cuh"
 
+// Programmatic dependent launch (sm_90+): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may be
+// scheduled while its predecessor on the stream is still running; it must not touch the predecessor's results before
+// hrg_grid_dep_wait() (returns once the predecessor has completed and its writes are visible). hrg_grid_dep_launch() lets the
+// NEXT kernel of the stream be staged. Both are no-ops in a kernel launched the ordinary way.
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ void hrg_grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void hrg_grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#else
+inline void hrg_grid_dep_wait() {}
+inline void hrg_grid_dep_launch() {}
+#endif
+
 namespace hrg {
 
 // flag word (one per env)
