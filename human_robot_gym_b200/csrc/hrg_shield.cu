@@ -512,7 +512,11 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
       mark(HRG_PROF_PFL);
       s->launches++;
     }
-    launch_k(k_replan_tail, grid_for(N, 128), 128, 0, rs, pdl && !s->pfl, s->S, t, meas_t);
+    {
+      int g_tail = grid_for(N, 4);
+      if (g_tail > s->sm_count * 16) g_tail = s->sm_count * 16;
+      launch_k(k_replan_tail, g_tail, kTailBlock, 0, rs, pdl && !s->pfl, s->S, t, meas_t);
+    }
     mark(HRG_PROF_TAIL);
   }
   if (fork) {

@@ -406,35 +406,58 @@ __device__ __forceinline__ void replan_tail_env(const DevState& S, const HrgConf
 // Thread per replanning env. A kernel of its own: inside the sampler its ~250 registers would cap the residency of the
 // sampling loop (fused and uncapped: 9 warps / SM, a second round above 1 332 replans; capped to 128: the loop spills and
 // runs at half speed - both measured, profiles/r02_summary.md). PFL handles run k_pfl_ltt between the two.
-__global__ void __launch_bounds__(128) k_replan_tail(DevState S, const double* __restrict__ t,
-                                                     const double* __restrict__ meas_t) {
-  hrg_grid_dep_wait();
-  hrg_grid_dep_launch();
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= *S.replan_count) return;
-  const int e = S.replan_list[idx];
-  replan_tail_env(S, *S.cfg, e, S.plan_head[idx], t[e], meas_t ? meas_t[e] : S.last_meas[e]);
-}
-
 // What replan_tail_env / plan_env will read of env e, asked for ahead of time by all lanes of the env's warp (field-major
 // state: every field is its own cache line, and the tail is one lane chasing ~100 of them one after the other).
-__device__ __forceinline__ void prefetch_tail_inputs(const DevState& S, int e, int lane) {
+template <bool L1>
+__device__ __forceinline__ void prefetch_tail_inputs(const DevState& S, int e, int lane, int nl = 32) {
   const int J = S.J;
   const size_t N = (size_t)S.N;
-  auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); };
-  for (int k = lane; k < N_PATHS * PATH_FIELDS; k += 32) pf(S.paths + (size_t)k * N + e);
-  for (int k = lane; k < 4 * J + 1; k += 32) pf(S.cur + (size_t)k * N + e);
-  for (int k = lane; k < J; k += 32) pf(S.prev_dq + (size_t)k * N + e);
-  for (int k = lane; k < 2 * J; k += 32) pf(S.ltt_alpha + (size_t)k * N + e);
-  if (lane < 2) {
-    pf(S.ltt_len + (size_t)lane * N + e);
-    pf(S.ltt_cur + (size_t)lane * N + e);
-    pf(S.ltt_start + (size_t)lane * N + e);
-    pf(S.ltt_t0 + (size_t)lane * N + e);
-    pf(S.ltt_ts + (size_t)lane * N + e);
+  auto pf = [](const void* p) {
+    if (L1)
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+    else
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  };
+  for (int k = lane; k < N_PATHS * PATH_FIELDS; k += nl) pf(S.paths + (size_t)k * N + e);
+  for (int k = lane; k < 4 * J + 1; k += nl) pf(S.cur + (size_t)k * N + e);
+  for (int k = lane; k < J; k += nl) pf(S.prev_dq + (size_t)k * N + e);
+  for (int k = lane; k < 2 * J; k += nl) pf(S.ltt_alpha + (size_t)k * N + e);
+  for (int k = lane; k < 2; k += nl) {
+    pf(S.ltt_len + (size_t)k * N + e);
+    pf(S.ltt_cur + (size_t)k * N + e);
+    pf(S.ltt_start + (size_t)k * N + e);
+    pf(S.ltt_t0 + (size_t)k * N + e);
+    pf(S.ltt_ts + (size_t)k * N + e);
   }
-  if (lane == 2) pf(S.path_s + e);
-  if (lane == 3) pf(S.path_sd + e);
+  if (lane == 2 % nl) pf(S.path_s + e);
+  if (lane == 3 % nl) pf(S.path_sd + e);
+}
+
+constexpr int kTailBlock = 32;
+__global__ void __launch_bounds__(kTailBlock) k_replan_tail(DevState S, const double* __restrict__ t,
+                                                            const double* __restrict__ meas_t) {
+  hrg_grid_dep_wait();
+  hrg_grid_dep_launch();
+  // four envs per warp: the 8 lanes of a slot first pull their env's state into L1 (the tail is one lane chasing ~100
+  // cache lines one after the other: out of L1 that is ~40 cycles each instead of ~300 out of L2), then lane 0 of the slot
+  // runs the tail
+  const int lane = threadIdx.x & 31, g = lane >> 3, l8 = lane & 7;
+  const int count = *S.replan_count;
+  for (int base = blockIdx.x * 4; base < count; base += gridDim.x * 4) {
+    const int idx = base + g;
+    const bool valid = idx < count;
+    const int e = valid ? S.replan_list[idx] : 0;
+    if (valid) {
+      prefetch_tail_inputs<true>(S, e, l8, 8);
+      // the head of the trajectory just planned (the goal motion is interpolated there) and the live sample in use
+      const int pend = (S.flags[e] & F_LIVE_SLOT) ? 0 : 1;
+      const char* p0 = reinterpret_cast<const char*>(ltt_sample(S, e, pend, 0));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(p0 + 128 * l8));
+    }
+    __syncwarp();
+    if (valid && l8 == 0) replan_tail_env(S, *S.cfg, e, S.plan_head[idx], t[e], meas_t ? meas_t[e] : S.last_meas[e]);
+    __syncwarp();
+  }
 }
 
 // One env per warp (one warp per block, so the blocks of a tick are all resident at once and spread over every
@@ -488,7 +511,7 @@ __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_s
 #pragma unroll
     for (int k = 0; k < kSampleEnvs; ++k) {  // for k_replan_tail, which follows: one lane per env chasing ~100 cache lines
       const int ek = __shfl_sync(full, e, 8 * k);
-      if (ek >= 0) prefetch_tail_inputs(S, ek, lane);
+      if (ek >= 0) prefetch_tail_inputs<false>(S, ek, lane);
     }
     const int pend = (valid && (S.flags[e] & F_LIVE_SLOT)) ? 0 : 1;
     PlanHead head;
