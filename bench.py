@@ -403,15 +403,17 @@ def time_shield(args, sc, files, names, dev, rank, world, n, W, S, seed, with_e2
     out = {"envs_total": n_all, "envs_per_gpu": n, "value": n_all * S / (ms / 1e3), "ms_per_step": ms / S,
            "n_replan_local": st["n_replan"]}
     if with_e2e:
-        ms_e, k, _ = time_e2e_piped(shield, kp_h, goals_h, masks_h, n, J, dev, max(3, min(W, 10)), S, world, k, sync_all)
+        ms_e, k, _ = time_e2e_piped(shield, kp_h, goals_h, masks_h, n, J, dev, max(3, min(W, 10)), S, world, k, sync_all, sparse=True)
         out["e2e"] = {"value": n_all * S / (ms_e / 1e3), "ms_per_step": ms_e / S}
     shield.close()
     return out
 
 
-def time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, W, S, world, k0, sync_all, plain=False):
+def time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, W, S, world, k0, sync_all, plain=False, sparse=False):
     """S ticks through the host-buffer C ABI (pinned host inputs in, pinned host setpoints out, one stream sync per tick):
     double-buffered upload of tick k+1 during tick k (plain=True: hrg_shield_tick_host, copy -> kernels -> copy).
+    sparse=True: the goals travel as (env, goal) pairs of the envs whose policy step starts on the tick
+    (hrg_shield_upload_inputs_sparse) instead of a mask and a goal for every env.
     Returns (ms over ranks' max, next tick index, launches)."""
     import torch
     import torch.distributed as dist
@@ -424,9 +426,19 @@ def time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, W, S, world, k0, s
     copy_stream = torch.cuda.Stream(device=dev)
     main = torch.cuda.current_stream(dev)
 
+    if sparse:  # what the caller of a vectorised env holds anyway: which envs got a new goal, and those goals
+        idx_p = [torch.from_numpy(np.flatnonzero(masks_h[p]).astype(np.int32)).pin_memory() for p in range(GOAL_PERIOD)]
+        gsp_p = [[torch.from_numpy(np.ascontiguousarray(goals_h[g][np.flatnonzero(masks_h[p])])).pin_memory()
+                  for p in range(GOAL_PERIOD)] for g in range(goals_h.shape[0])]
+        time_e2e_piped.sparse_goal_bytes = float(np.mean([i.numel() for i in idx_p])) * (4 + 8 * J)
+
     def upload(kk):
         slot = kk & 1
         t_p[slot].fill_(kk * SAMPLE_TIME)
+        if sparse:
+            p, g = kk % GOAL_PERIOD, (kk // GOAL_PERIOD) % goals_h.shape[0]
+            shield.upload_inputs_sparse(slot, kp_p[ring_index(kk, R)], t_p[slot], idx_p[p], gsp_p[g][p], copy_stream=copy_stream)
+            return
         shield.upload_inputs(slot, kp_p[ring_index(kk, R)], t_p[slot], masks_p[kk % GOAL_PERIOD],
                              goals_p[(kk // GOAL_PERIOD) % goals_p.shape[0]], copy_stream)
 
@@ -593,13 +605,20 @@ def main():
     if not args.no_e2e:
         Wx = max(3, min(W, 10))
         ms_plain, k, _ = time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, Wx, S, world, k, sync_all, plain=True)
-        ms_piped, k, l_e = time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, Wx, S, world, k, sync_all)
-        h2d = N * (K * 3 * 8 + 8 + 1 + J * 8)
+        ms_dense, k, _ = time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, Wx, S, world, k, sync_all)
+        ms_piped, k, l_e = time_e2e_piped(shield, kp_h, goals_h, masks_h, N, J, dev, Wx, S, world, k, sync_all, sparse=True)
+        h2d = int(N * (K * 3 * 8 + 8) + time_e2e_piped.sparse_goal_bytes)
+        h2d_dense = N * (K * 3 * 8 + 8 + 1 + J * 8)
         copy_gbs = h2d_copy_rate(dev, world, h2d)
         e2e = {"value": n_total * S / (ms_piped / 1e3), "unit": METRIC,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": N * (3 * J * 8 + 1),
                "ms_per_step": ms_piped / S, "gpu_launches": l_e,
-               "mode": "double-buffered upload of tick k+1 during tick k; stream sync per tick; host wall clock",
+               "mode": "double-buffered upload of tick k+1 during tick k (hrg_shield_upload_inputs_sparse: keypoints + clock of "
+                       "every env, goals as (env, goal) pairs of the 1 in 25 envs that start a policy step); "
+                       "hrg_shield_tick_staged; stream sync per tick; host wall clock",
+               "dense_goal_arrays": {"value": n_total * S / (ms_dense / 1e3), "ms_per_step": ms_dense / S,
+                                     "h2d_bytes_per_step": h2d_dense,
+                                     "mode": "hrg_shield_upload_inputs: goal mask + goal of every env each tick"},
                "unpipelined": {"value": n_total * S / (ms_plain / 1e3), "ms_per_step": ms_plain / S},
                "h2d_copy_alone": {"GBps_per_rank_min": copy_gbs, "ranks_copying": world,
                                   "ms_for_one_tick_of_inputs": h2d / copy_gbs / 1e6,

@@ -298,6 +298,16 @@ class BatchedSafetyShield:
                                                      _ptr(goal_mask_host), _ptr(goal_q_host), cs),
                    "hrg_shield_upload_inputs")
 
+    def upload_inputs_sparse(self, slot: int, kp_host, t_host, goal_env_host=None, goal_q_host=None, n_goals=None,
+                             copy_stream=None):
+        """upload_inputs with the goals as (env index, goal) pairs: goal_env_host [>= n_goals] int32 and goal_q_host
+        [>= n_goals, J], pinned HOST tensors; only the envs that start a policy step this tick travel."""
+        cs = (copy_stream or torch.cuda.current_stream(self.device)).cuda_stream
+        n = 0 if goal_env_host is None else int(goal_env_host.numel() if n_goals is None else n_goals)
+        cabi.check(self.lib.hrg_shield_upload_inputs_sparse(self._h, int(slot), kp_host.data_ptr(), t_host.data_ptr(), n,
+                                                            _ptr(goal_env_host), _ptr(goal_q_host), cs),
+                   "hrg_shield_upload_inputs_sparse")
+
     def tick_staged(self, slot: int, q_host, dq_host, ddq_host, flags_host):
         """humanMeasurement + [newLongTermTrajectory] + step on a previously uploaded slot; setpoints to pinned HOST."""
         cabi.check(self.lib.hrg_shield_tick_staged(self._h, int(slot), _ptr(q_host), _ptr(dq_host), _ptr(ddq_host),

@@ -119,6 +119,8 @@ SYMBOLS = {
     "hrg_shield_tick_device": (C.c_int, [C.c_void_p, _dp, _dp, _u8p, _dp, _dp, _dp, _dp, _dp, _u8p, _u8p, _u32p, _vp]),
     "hrg_shield_tick_host": (C.c_int, [C.c_void_p] + [C.c_void_p] * 8 + [_vp]),
     "hrg_shield_upload_inputs": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [_vp]),
+    "hrg_shield_upload_inputs_sparse": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                                  C.c_void_p, _vp]),
     "hrg_shield_tick_staged": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [_vp]),
     "hrg_shield_get_capsules": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _vp]),
     "hrg_capsule_markers": (C.c_int, [C.c_int, _dp, _dp, _dp, _dp, _vp]),

@@ -69,6 +69,8 @@ struct HrgShield {
   double* d_t2[2] = {nullptr, nullptr};
   double* d_goal2[2] = {nullptr, nullptr};
   uint8_t* d_goal_mask2[2] = {nullptr, nullptr};
+  int32_t* d_goal_idx2[2] = {nullptr, nullptr};  // sparse goals of hrg_shield_upload_inputs_sparse: env indices ...
+  double* d_goal_sp2[2] = {nullptr, nullptr};    // ... and their goals [n_goals, J]
   bool slot_has_goal[2] = {false, false};
   bool slot_used[2] = {false, false};
   cudaEvent_t ev_up[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
@@ -128,6 +130,17 @@ inline cudaError_t launch_k(void (*k)(KArgs...), int grid, int block, size_t sme
 }
 inline int grid_for(int n, int block) { return (n + block - 1) / block; }
 inline int tile_grid(int n) { return (n + kTileEnvs - 1) / kTileEnvs; }
+
+// (env index, goal) pairs -> the mask / goal arrays the tick reads; indices out of range are dropped
+__global__ void k_scatter_goals(int n, int J, int N, const int32_t* __restrict__ idx, const double* __restrict__ val,
+                                uint8_t* __restrict__ mask, double* __restrict__ goal) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int e = idx[i];
+  if (e < 0 || e >= N) return;
+  mask[e] = 1;
+  for (int j = 0; j < J; ++j) goal[(size_t)e * J + j] = val[(size_t)i * J + j];
+}
 
 __global__ void k_pack_flags(int n, const uint8_t* __restrict__ safe, const uint8_t* __restrict__ branch,
                              uint8_t* __restrict__ out) {
@@ -244,6 +257,10 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   AL(h->d_t2[1], N);
   AL(h->d_goal2[1], (size_t)J * N);
   AL(h->d_goal_mask2[1], N);
+  for (int k = 0; k < 2; ++k) {
+    AL(h->d_goal_idx2[k], N);
+    AL(h->d_goal_sp2[k], (size_t)J * N);
+  }
   AL(h->d_q, (size_t)J * N);
   AL(h->d_dq, (size_t)J * N);
   AL(h->d_ddq, (size_t)J * N);
@@ -616,6 +633,34 @@ int hrg_shield_upload_inputs(HrgShield* s, int slot, const double* keypoints_hos
   if (s->slot_has_goal[slot]) {
     CK(cudaMemcpyAsync(s->d_goal_mask2[slot], goal_mask_host, N, cudaMemcpyHostToDevice, cs));
     CK(cudaMemcpyAsync(s->d_goal2[slot], goal_q_host, N * J * sizeof(double), cudaMemcpyHostToDevice, cs));
+  }
+  CK(cudaEventRecord(s->ev_up[slot], cs));
+  return HRG_OK;
+}
+
+// Sparse form: only the envs whose policy period starts on this tick carry a goal (1 in 25 in human-robot-gym), so the goals
+// travel as (env index, goal) pairs instead of a mask and a goal for every env - 7 % fewer bytes per tick on a link that the
+// end-to-end tick saturates. goal_env_host [n_goals] i32 (distinct envs), goal_q_host [n_goals, J]; n_goals may be 0.
+int hrg_shield_upload_inputs_sparse(HrgShield* s, int slot, const double* keypoints_host, const double* t_host, int n_goals,
+                                    const int32_t* goal_env_host, const double* goal_q_host, void* copy_stream) {
+  if (!s || !keypoints_host || !t_host || slot < 0 || slot > 1 || n_goals < 0 || n_goals > s->S.N ||
+      (n_goals > 0 && (!goal_env_host || !goal_q_host)))
+    return fail(HRG_EINVAL, "hrg_shield_upload_inputs_sparse: bad argument");
+  CK(cudaSetDevice(s->device));
+  cudaStream_t cs = static_cast<cudaStream_t>(copy_stream);
+  const size_t N = s->S.N, J = s->S.J, K3 = (size_t)s->S.K * 3;
+  if (s->slot_used[slot]) CK(cudaStreamWaitEvent(cs, s->ev_done[slot], 0));
+  CK(cudaMemcpyAsync(s->d_kp2[slot], keypoints_host, N * K3 * sizeof(double), cudaMemcpyHostToDevice, cs));
+  CK(cudaMemcpyAsync(s->d_t2[slot], t_host, N * sizeof(double), cudaMemcpyHostToDevice, cs));
+  s->slot_has_goal[slot] = n_goals > 0;
+  if (n_goals > 0) {
+    CK(cudaMemcpyAsync(s->d_goal_idx2[slot], goal_env_host, (size_t)n_goals * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
+    CK(cudaMemcpyAsync(s->d_goal_sp2[slot], goal_q_host, (size_t)n_goals * J * sizeof(double), cudaMemcpyHostToDevice, cs));
+    CK(cudaMemsetAsync(s->d_goal_mask2[slot], 0, N, cs));
+    k_scatter_goals<<<grid_for(n_goals, 128), 128, 0, cs>>>(n_goals, (int)J, (int)N, s->d_goal_idx2[slot], s->d_goal_sp2[slot],
+                                                            s->d_goal_mask2[slot], s->d_goal2[slot]);
+    s->launches++;
+    CK(cudaGetLastError());
   }
   CK(cudaEventRecord(s->ev_up[slot], cs));
   return HRG_OK;

@@ -188,6 +188,12 @@ int hrg_shield_upload_inputs(HrgShield* s, int slot, const double* keypoints_hos
                              const uint8_t* goal_mask_host, const double* goal_q_host, void* copy_stream);
 int hrg_shield_tick_staged(HrgShield* s, int slot, double* q_host, double* dq_host, double* ddq_host,
                            uint8_t* flags_host, void* stream);
+/* hrg_shield_upload_inputs with the goals as (env, goal) pairs: goal_env_host [n_goals] i32 (distinct envs, out-of-range
+ * entries are dropped), goal_q_host [n_goals, J]; n_goals = 0: no new goals this tick. newLongTermTrajectory is called for
+ * one env in 25 per tick (failsafe_controller.py:252-300 once per policy step), so this saves the mask and the 8J bytes of
+ * goal per env that the dense form sends for all of them. */
+int hrg_shield_upload_inputs_sparse(HrgShield* s, int slot, const double* keypoints_host, const double* t_host, int n_goals,
+                                    const int32_t* goal_env_host, const double* goal_q_host, void* copy_stream);
 
 /* getRobotReachCapsules / getHumanReachCapsules — bindings :111-112 / safety_shield.h:549-574 — of the last step.
  * robot [N,J,7], human [N,H,7] with H = n_ext + 2*n_bodies ordered Pos, Vel, Accel; min_dist [N,3] = per human model

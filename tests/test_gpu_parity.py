@@ -414,3 +414,43 @@ def test_state_dict_round_trip_is_bit_identical():
     other = BatchedSafetyShield(n + 1, 0.004, *files, init_qpos=np.zeros((n + 1, 6)), device="cuda:0", ltt_capacity=512, config=sc)
     with pytest.raises(cabi.ShieldLibraryError):
         other.load_state_dict(state)
+
+
+@pytest.mark.gpu
+def test_sparse_goal_upload_equals_dense():
+    """hrg_shield_upload_inputs_sparse ((env, goal) pairs) against hrg_shield_upload_inputs (mask + goal of every env): the
+    same ticks bit for bit, including ticks without goals and an out-of-range index that must be dropped."""
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    from human_robot_gym_b200.config import ShieldConfig
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+    files = pu.default_files("schunk")
+    sc = ShieldConfig.from_files(0.004, *files)
+    n, J = 257, 6
+    scen = SyntheticScenario(n, pu.mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, 99)
+    mk = lambda: BatchedSafetyShield(n, 0.004, *files, init_qpos=scen.init_q, device="cuda:0", ltt_capacity=512, config=sc)  # noqa: E731
+    a, b = mk(), mk()
+    pin = dict(pin_memory=True)
+    outs = [[torch.zeros(n, J, dtype=torch.float64, **pin) for _ in range(3)] + [torch.zeros(n, dtype=torch.uint8, **pin)]
+            for _ in range(2)]
+    goals = [scen.next_goal() for _ in range(3)]
+    for k in range(70):
+        kp = torch.from_numpy(scen.keypoints(k * 0.004)).pin_memory()
+        t = torch.full((n,), k * 0.004, dtype=torch.float64).pin_memory()
+        sel = np.flatnonzero(np.arange(n) % 25 == k % 25) if k % 3 else np.zeros(0, dtype=np.int64)   # some ticks: no goals
+        g = goals[(k // 25) % 3]
+        mask = np.zeros(n, dtype=np.uint8)
+        mask[sel] = 1
+        if len(sel):
+            a.upload_inputs(0, kp, t, torch.from_numpy(mask).pin_memory(), torch.from_numpy(g).pin_memory())
+        else:
+            a.upload_inputs(0, kp, t)
+        idx = np.concatenate([sel, [n + 5]]).astype(np.int32) if len(sel) else None      # + one index out of range
+        val = np.concatenate([g[sel], np.zeros((1, J))]) if len(sel) else None
+        b.upload_inputs_sparse(0, kp, t, None if idx is None else torch.from_numpy(idx).pin_memory(),
+                               None if val is None else torch.from_numpy(np.ascontiguousarray(val)).pin_memory())
+        a.tick_staged(0, *outs[0])
+        b.tick_staged(0, *outs[1])
+        torch.cuda.synchronize()
+        for x, y in zip(outs[0], outs[1]):
+            assert torch.equal(x, y), k
+    assert a.stats()["n_replan"] == b.stats()["n_replan"] > n
