@@ -721,6 +721,9 @@ def main():
                              "branch_hist": counts[2:5], "n_replan": counts[5], "n_replan_failed": counts[6],
                              "n_near_threshold": counts[7], "min_dist": gs["min_dist"]},
             "clocks": clk, "gpu_launches": int(launches),
+            "parity_note": "checker of tests / smoke = the reference C++ compiled against oracle/eigen_shim (Eigen 3.4 absent here; shim "
+                           "pinned by the reference's 71 gtests + LAPACK cross-check); planner roots: derivative-chain finder with "
+                           "the eigen-solve restatement as arbiter of close calls (HRG_ROOT_MODE=0: eigen-solve for everything)",
         }
         if strong:
             strong["note"] = ("BASELINE config 3: this many shields IN TOTAL, sharded env-wise; the per-GPU batch shrinks with N, so "
