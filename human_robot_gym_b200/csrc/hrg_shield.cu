@@ -520,7 +520,12 @@ static int step_impl(HrgShield* s, const double* kp, const uint8_t* goal_mask, c
     mark(HRG_PROF_PLAN_LTT);
     launch_k(k_replan_deep, g_deep, kReplanBlock, 0, rs, pdl, s->S, s->deep_per_warp);
     mark(HRG_PROF_DEEP);
-    launch_k(k_replan_sample, g_samp, kSampleBlock, 0, rs, pdl, s->S);
+    if (J == 6)
+      launch_k(k_replan_sample<6>, g_samp, kSampleBlock, 0, rs, pdl, s->S);
+    else if (J == 7)
+      launch_k(k_replan_sample<7>, g_samp, kSampleBlock, 0, rs, pdl, s->S);
+    else
+      launch_k(k_replan_sample<0>, g_samp, kSampleBlock, 0, rs, pdl, s->S);
     mark(HRG_PROF_SAMPLE);
     if (s->pfl) {
       int pgrid = s->sm_count * 8;

@@ -478,6 +478,9 @@ constexpr int kSampleChunk = 128;
 #endif
 constexpr int kSampleEnvs = HRG_SAMPLE_ENVS;
 static_assert(kSampleEnvs == 1 || kSampleEnvs == 2 || kSampleEnvs == 4, "envs per sampler warp");
+// JT: the joint count as a compile-time constant (6 Schunk, 7 Panda; 0 = read it from the state): with it the sample stride
+// 4J is an immediate and the four stores of a sample need no 64-bit pointer arithmetic (a third of the recurrence loop).
+template <int JT>
 __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_sample(DevState S) {
   HRG_TRACE_SPAN(2);
   hrg_grid_dep_wait();
@@ -487,7 +490,7 @@ __global__ void __launch_bounds__(kSampleBlock, HRG_SAMPLE_MINBLOCKS) k_replan_s
   const HrgConfig& c = *S.cfg;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  const int J = S.J;
+  const int J = JT > 0 ? JT : S.J;
   const int g = lane >> 3, jl8 = lane & 7;          // env slot of the lane, joint of the lane
   const bool slot = g < kSampleEnvs;
   const int gs = slot ? g : 0;
