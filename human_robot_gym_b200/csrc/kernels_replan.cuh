@@ -121,6 +121,9 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_PLAN_MINBLOCKS) k_replan_pla
       ok_j = ltp_check_inputs_joint(L, c.q_min[j], c.q_max[j], q_0, v_0, a_0);
       if (ok_j) opt_prefill_root(L, q_goal, q_0, v_0, a_0, half, rc);  // 1.
     }
+#if defined(HRG_TASK_TRACE)
+    const unsigned long long tr_p1 = trace_now();
+#endif
     {  // the partner's root
       const double other = __shfl_xor_sync(full, rc.root[half], 1);
       rc.root[half ^ 1] = other;
@@ -147,6 +150,9 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_PLAN_MINBLOCKS) k_replan_pla
     }
     if (h.slowest == -1) ok = false;
     h.ok = ok ? 1 : 0;
+#if defined(HRG_TASK_TRACE)
+    const unsigned long long tr_p2 = trace_now();
+#endif
     // 3. candidate `half`
     double T[7];
     ltp_zero7(T);
@@ -183,6 +189,15 @@ __global__ void __launch_bounds__(kReplanBlock, HRG_PLAN_MINBLOCKS) k_replan_pla
       }
     }
     HRG_TRACE_TASK(0, base / E, 0);
+#if defined(HRG_TASK_TRACE)
+    if (lane == 0 && base / E < kTraceTasks) {
+      unsigned long long* r3 = g_task_trace[3][base / E];
+      r3[0] = tr_p1 - trace_t0;        // checkInputs + the two quartic roots
+      r3[1] = tr_p2 - tr_p1;           // optSwitchTimes + slowest joint
+      r3[2] = trace_now() - tr_p2;     // closed-form candidates
+      r3[3] = 1;
+    }
+#endif
     if (!act || half != 0) continue;  // (the other lanes wait in the next fetch's shuffle)
     opt.len = h.ok;
     PlanRec sc = opt;

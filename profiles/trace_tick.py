@@ -64,8 +64,8 @@ for k in range(W, W + 3):
     r3 = buf[3]
     m3 = r3[:, 3] > 0
     if m3.any():
-        print(f"tick {k} sampler phases (us, mean / max): init {r3[m3, 0].mean() / 1e3:.1f} / {r3[m3, 0].max() / 1e3:.1f}  fill {r3[m3, 1].mean() / 1e3:.1f} / "
-              f"{r3[m3, 1].max() / 1e3:.1f}  corrections+recurrence {r3[m3, 2].mean() / 1e3:.1f} / {r3[m3, 2].max() / 1e3:.1f}  len mean {r3[m3, 3].mean():.0f}")
+        print(f"tick {k} k_replan_plan phases (us, mean / max): checkInputs + quartic roots {r3[m3, 0].mean() / 1e3:.1f} / {r3[m3, 0].max() / 1e3:.1f}  "
+              f"optSwitchTimes {r3[m3, 1].mean() / 1e3:.1f} / {r3[m3, 1].max() / 1e3:.1f}  closed-form candidates {r3[m3, 2].mean() / 1e3:.1f} / {r3[m3, 2].max() / 1e3:.1f}")
     for ki, name in enumerate(("plan", "deep", "sample+tail")):
         r = buf[ki]
         m = r[:, 1] > 0
