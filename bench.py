@@ -710,7 +710,7 @@ def main():
                                  "(profiles/fp64_counts.json) over the same time against the measured DMUL+DADD issue rate; "
                                  "`bound` names the larger. k_reach_verify is FP64-issue bound (pipe 21-35 % busy at 30 % "
                                  "occupancy), k_replan a dependent-latency chain of a few thousand problems "
-                                 "(profiles/r02x_ncu_summary.md)"},
+                                 "(profiles/r03l_ncu_summary.md)"},
             "kernel_ms_per_step": {kk: v / max(ksteps, 1) for kk, v in kms.items()},
             "kernel_ms_per_launch": {kk: v / max(ksteps, 1) for kk, v in kdetail.items() if v > 0},
             "fp64_peak_measured": fp64_peak,

@@ -62,25 +62,23 @@ __global__ void __launch_bounds__(kTickBlock)
   constexpr int NC = 10;
   __shared__ unsigned long long s_cnt[NC];
   __shared__ double s_min;
-  // which 1 walks the replan list (a few thousand envs) instead of testing the mark of every env of the batch
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-  int e = tid;
-  if (which == 1) e = (tid < *S.replan_count) ? S.replan_list[tid] : S.N;
+  const int e = tid;
   if (threadIdx.x < NC) s_cnt[threadIdx.x] = 0ull;
   if (threadIdx.x == 0) s_min = INFINITY;
   __syncthreads();
   // re-arm the work lists for the next tick: each launch resets what only kernels BEFORE it on its own stream read
   // (which 0 runs behind the cascade stages on the main stream, which 1 behind the replan chain and pass 1 on the side
-  // stream; the two may overlap). The replan list is read by the blocks of this very launch, so there the LAST block to
-  // finish resets it (ticket in replan_ctr).
-  if (tid == 0 && which == -1) {
+  // stream; the two may overlap). (Walking the replan list instead of testing every env's mark was measured: the few dozen
+  // warps it concentrates the scattered loads of ~2 000 envs in take 18 us against 9 us for the marks.)
+  if (tid == 0 && which != 0) {
     *S.replan_count = 0;
     for (int k = 0; k < N_CTR; ++k) S.replan_ctr[k] = 0;
   }
   if (tid == 0 && which != 1) S.verify_cnt[0] = S.verify_cnt[1] = 0;
   unsigned long long my[NC] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // unsafe, b0, b1, b2, replan, failed, near, len_sum, truncated, steps
   double my_min = INFINITY;
-  if (e < S.N && (which != 0 || S.replan_mark[e] == 0)) {
+  if (e < S.N && (which < 0 || (int)S.replan_mark[e] == which)) {
     my[9] = 1;
     const HrgConfig& c = *S.cfg;
     uint32_t f = S.flags[e];
@@ -138,16 +136,6 @@ __global__ void __launch_bounds__(kTickBlock)
           if (prev == old) break;
           old = prev;
         }
-      }
-    }
-  }
-  if (which == 1) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      __threadfence();
-      if (atomicAdd(S.replan_ctr + CTR_SELECT_DONE, 1) == (int)gridDim.x - 1) {
-        *S.replan_count = 0;
-        for (int k = 0; k < N_CTR; ++k) S.replan_ctr[k] = 0;
       }
     }
   }
