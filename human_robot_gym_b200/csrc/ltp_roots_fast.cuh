@@ -44,9 +44,6 @@ struct FastRootPoly {
 // value and derivative of level K at x (Horner)
 template <int NMAX, int K>
 HRG_HD void fr_eval(const FastRootPoly<NMAX>& P, double x, double& g, double& dg) {
-#if defined(FR_COUNT_EVAL) && !defined(__CUDA_ARCH__)
-  FR_COUNT_EVAL();
-#endif
   g = P.D[K][0];
   dg = 0.0;
   HRG_FR_UNROLL
@@ -99,9 +96,6 @@ HRG_HD double fr_bracket(const FastRootPoly<NMAX>& P, double lo, double hi, doub
   for (int it = 0; it < 100; ++it) {
     double g, dg;
     fr_eval<NMAX, K>(P, x, g, dg);
-#if defined(FR_DEBUG) && !defined(__CUDA_ARCH__)
-    printf("  K=%d it=%d lo=%.17g hi=%.17g x=%.17g g=%g dg=%g\n", K, it, lo, hi, x, g, dg);
-#endif
     if (g == 0.0) return x;
     if ((g < 0.0) == up)
       lo = x;
