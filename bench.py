@@ -620,10 +620,12 @@ def main():
                                      "h2d_bytes_per_step": h2d_dense,
                                      "mode": "hrg_shield_upload_inputs: goal mask + goal of every env each tick"},
                "unpipelined": {"value": n_total * S / (ms_plain / 1e3), "ms_per_step": ms_plain / S},
+               "h2d_GBps_achieved_per_rank": h2d / (ms_piped / S / 1e3) / 1e9,
                "h2d_copy_alone": {"GBps_per_rank_min": copy_gbs, "ranks_copying": world,
                                   "ms_for_one_tick_of_inputs": h2d / copy_gbs / 1e6,
-                                  "note": "one pinned host->device copy of a tick's inputs per rank, all ranks at once, no "
-                                          "kernels: the floor the box's PCIe / host memory puts under ms_per_step"},
+                                  "note": "a plain torch copy of one tick's worth of pinned bytes per rank, all ranks at once, no "
+                                          "kernels: shows how the box's host memory / PCIe rate falls with the number of ranks "
+                                          "copying (the e2e leg's own copies run at h2d_GBps_achieved_per_rank)"},
                "checksum": time_e2e_piped.checksum}
 
     # ---- end to end with the RECORDED human (the reference's own workload: the human is a clip replay, BASELINE config 1) -----
