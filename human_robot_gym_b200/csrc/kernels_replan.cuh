@@ -1,27 +1,29 @@
 // calculateLongTermTrajectory (SS/src/safety_shield.cc:732-760) -> LongTermPlanner::planTrajectory
 // (LTP/src/long_term_planner.cc:7-63) for the envs on the replan list: the replan chain of a tick.
 //
-// One PROBLEM PER LANE. The planner is branchy FP64 code, 85 % of it companion-matrix eigen-solves; the first design gave
-// every (env, joint) problem an 8-lane group that shared each solve through a matrix in shared memory (four divergent
-// groups per warp, ~10 of 32 lanes active, 0.34 ms per tick for ~2 100 replans). Three changes replace it:
-//   * the solver keeps the matrix in registers (ltp_roots_reg.cuh), so a lane needs no partner and a warp runs 32 solves in
-//     one instruction stream;
-//   * optSwitchTimes' two quartic roots do not depend on v_drive (OptRootCache, ltp_profiles.cuh): they are solved once
-//     per (env, joint) in k_replan_plan and handed to every later call, which leaves ONE eigen-solve per timeScaling
-//     candidate instead of up to three;
+// ~2 100 of 65 536 envs replan per tick and the tick cannot end before the slowest of them has its trajectory: the chain is
+// a LATENCY problem (the GPU has ten times more lanes than there are problems), so everything here is shaped to shorten the
+// dependent chain of one warp (history and measurements: DESIGN.md section 3, profiles/r02_summary.md):
+//   * the planner's polynomial roots come from the derivative-chain root finder (ltp_roots_fast.cuh); the exact restatement of
+//     the reference's eigen-solve (ltp_roots_reg.cuh, one problem per lane, matrix in registers) only decides the close calls;
+//   * optSwitchTimes' two quartic roots do not depend on v_drive (OptRootCache, ltp_profiles.cuh): they are found once per
+//     (env, joint) in k_replan_plan and handed to every later call;
 //   * kernels follow the data flow of one env instead of one kernel per planner routine:
-//       k_replan_plan    lane = (env, joint), floor(32 / J) envs per warp: checkInputs + optSwitchTimes (:20-37), slowest
-//                        joint through shuffles over the env's lanes (:39-45), the two closed-form timeScaling candidates
-//                        (:378-436); joints that accept neither go on the `deep` list
-//       k_replan_deep    lane = (deep joint, polynomial candidate 2..7), tasks ordered by candidate so that a warp solves
-//                        polynomials of one degree (:449-629); all six are evaluated, the first accepted one in the
-//                        reference's order is taken later - what its sequential ladder returns
-//       k_replan_sample  lane = (env, joint): getTrajectory (:706-841) with the reference's sequential recurrence per
-//                        joint, joint-limit test (:59-61)
+//       k_replan_plan    lane = (env, joint, half), 2 envs per warp: checkInputs + the two quartic roots side by side,
+//                        optSwitchTimes (:20-37), slowest joint through shuffles over the env's lanes (:39-45), the two
+//                        closed-form timeScaling candidates side by side (:378-436); joints that accept neither go on the
+//                        `deep` list
+//       k_replan_deep    8-lane group = deep joint, lane = polynomial candidate 3..8 (:449-629) in one instruction stream
+//                        for all degrees; the first accepted candidate in the reference's order wins (a ballot); exact QR
+//                        only for close calls in front of it; starts from rest settled by ltp_cand_rejected_from_rest
+//       k_replan_sample  2 envs per warp, lane = (env, joint): getTrajectory (:706-841) - jerk filled phase by phase into
+//                        shared memory, the reference's sequential recurrence as three skewed chains, joint-limit test
+//                        (:59-61)
 //       [k_pfl_ltt       PFL handles: per-sample Cartesian velocities (pfl_math.cuh)]
-//       k_replan_tail    thread = env: install the trajectory and run the rest of the env's step up to the reach / verify
+//       k_replan_tail    4 envs per warp: install the trajectory and run the rest of the env's step up to the reach / verify
 //                        hand-over (plan_env)
-// Work is fetched from device counters (S.replan_ctr); grids only bound residency.
+// Work is fetched from device counters (S.replan_ctr); grids only bound residency, and registers are capped so that every
+// task of a tick has a resident warp.
 #pragma once
 #include "ltp_math.cuh"
 #include "step_logic.cuh"
