@@ -172,7 +172,7 @@ HRG_HD void pfl_ltt_env_seq(const HrgConfig& c, const double* base, size_t bs, c
 }
 
 #if defined(__CUDACC__)
-// The PFL LongTermTraj constructor (long_term_traj.cc:5-39) of the trajectories k_replan_sample<true> phase 1 has just
+// The PFL LongTermTraj constructor (long_term_traj.cc:5-39) of the trajectories k_replan_sample has just
 // written: block = replanning env (grid-stride over the replan list), thread = sample within a chunk of kPflBlock. The
 // samples are independent except for the neighbour difference of alpha_i, which goes through shared memory (row 0 carries
 // the last sample of the previous chunk). The first form ran inside the sampler with lane = sample, one warp per env:
