@@ -364,6 +364,7 @@ void emul_poly_root_batch(int n, int ncoef, const double* coef /*[n, ncoef]*/, d
 static LtpLimits lim1(double ts, const double* lim) {
   LtpLimits L{};
   L.v_max = lim[2]; L.a_max = lim[3]; L.j_max = lim[4]; L.t_sample = ts;
+  L.root_mode = g_emul_root_mode;  // emul_set_root_mode: 0 exact QR for every polynomial, 1 fast roots + rest-start rule
   return L;
 }
 void emul_ltp_opt_braking(double ts, const double* lim, double v0, double a0, double* q, double* t_rel, double* dir) {

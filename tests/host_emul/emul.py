@@ -163,6 +163,11 @@ def poly_root_fast_batch(coefs):
     return f, m, r
 
 
+def set_root_mode(mode):
+    """Root finder of the single-function entry points below (LtpLimits::root_mode): 0 exact QR, 1 fast + rest-start rule."""
+    lib().emul_set_root_mode(int(mode))
+
+
 def ltp_opt_braking(ts, lim, v0, a0):
     lim, t, q, d = _a(lim), np.zeros(7), np.zeros(1), np.zeros(1)
     lib().emul_ltp_opt_braking(ts, _ptr(lim), v0, a0, _ptr(q), _ptr(t), _ptr(d))

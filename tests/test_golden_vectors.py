@@ -484,3 +484,41 @@ def test_exact_roots_against_lapack():
                 worst = max(worst, abs(r - want) / abs(want))
         print(f"degree {deg}: {n_cmp} compared with LAPACK, verdict mismatches {bad}, worst relative difference {worst:.2e}")
         assert n_cmp > 1000 and bad == 0 and worst < 1e-8
+
+
+def test_time_scaling_ladder_same_in_both_root_modes():
+    """timeScaling (LTP/src/long_term_planner.cc:358-645) with the derivative-chain roots + the rest-start rejection rule
+    (root_mode 1) against the exact eigen-solve for every polynomial (root_mode 0): same verdict, same profile flag, same
+    switch times - for moving starts and, above all, for starts from exact rest, whose candidate polynomials x^k q(x) the QR
+    iteration answers with noise roots (csrc/ltp_scaling.cuh: ltp_cand_rejected_from_rest)."""
+    rng = np.random.default_rng(2024)
+    lims = [[-3.0, 3.0, 2.0, 2.0, 15.0], [-2.9, 2.9, 2.6, 10.0, 400.0], [-3.1, 3.1, 1.0, 4.0, 40.0]]
+    n_rest = n_acc = n = 0
+    try:
+        for trial in range(6000):
+            lim = lims[trial % 3]
+            rest = trial % 2 == 0
+            q0 = rng.uniform(-2.0, 2.0)
+            v0 = 0.0 if rest else rng.uniform(-0.8, 0.8) * lim[2]
+            a0 = 0.0 if rest else rng.uniform(-0.8, 0.8) * lim[3]
+            q_goal = float(np.clip(q0 + rng.choice([0.002, 0.05, 0.5, 2.0]) * rng.uniform(-1, 1), lim[0], lim[1]))
+            emul.set_root_mode(0)
+            ok, t_opt, direction, _ = emul.ltp_opt_switch_times(0.004, lim, q_goal, q0, v0, a0, lim[2])
+            if not ok:
+                continue
+            t_req = t_opt[6] * rng.uniform(1.02, 4.0) + rng.choice([0.0, 0.05, 1.0])
+            res = []
+            for mode in (0, 1):
+                emul.set_root_mode(mode)
+                res.append(emul.ltp_time_scaling(0.004, lim, q_goal, q0, v0, a0, direction, t_req))
+            (ok0, T0, vd0, m0), (ok1, T1, vd1, m1) = res
+            assert ok0 == ok1 and m0 == m1, (trial, lim, q_goal, q0, v0, a0, t_req, res)
+            assert np.abs(T0 - T1).max() <= 1e-9 * max(1.0, np.abs(T0).max()), (trial, T0, T1)
+            assert vd0 == vd1 or abs(vd0 - vd1) <= 1e-9 * max(1.0, abs(vd0)), (trial, vd0, vd1)
+            n += 1
+            n_rest += rest
+            n_acc += ok0
+    finally:
+        emul.set_root_mode(0)
+    print(f"{n} ladders ({n_rest} from rest), {n_acc} with an accepted candidate")
+    assert n > 4000 and n_rest > 1500 and 0.2 * n < n_acc < n
