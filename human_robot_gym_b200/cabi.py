@@ -141,6 +141,7 @@ SYMBOLS = {
     "hrg_human_reset": (C.c_int, [C.c_void_p, _u8p, _dp, _i32p, _vp]),
     "hrg_human_keypoints": (C.c_int, [C.c_void_p, C.c_void_p, _dp, _i32p, _i32p, _vp]),
     "hrg_shield_tick_replay_host": (C.c_int, [C.c_void_p, C.c_void_p] + [C.c_void_p] * 8 + [_vp]),
+    "hrg_shield_tick_replay_piped": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 8 + [_vp, _vp]),
     "hrg_human_launch_count": (C.c_int64, [C.c_void_p]),
     "hrg_shield_state_bytes": (C.c_int64, [C.c_void_p]),
     "hrg_shield_state_save": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),

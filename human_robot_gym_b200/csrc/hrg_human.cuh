@@ -172,6 +172,50 @@ int hrg_shield_tick_replay_host(HrgShield* s, HrgHuman* h, const int64_t* low_le
   return HRG_OK;
 }
 
+// Pipelined form of hrg_shield_tick_replay_host: the tick's kernels run on `stream`, its setpoints go into output slot 0/1 and
+// travel to the host on `copy_stream`, so the device->host copy of tick k overlaps the kernels of tick k + 1 (the shield never
+// reads the robot's measured state - it follows its own trajectory - so the next tick does not have to wait for the host to
+// have seen this one's setpoints). The caller waits for `copy_stream` (or the next call on the same slot) before reading the
+// host buffers of a slot; a slot is not overwritten before its copy has finished.
+int hrg_shield_tick_replay_piped(HrgShield* s, HrgHuman* h, int slot, const int64_t* low_level_time_host, const double* t_host,
+                                 const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
+                                 double* ddq_host, uint8_t* flags_host, void* stream, void* copy_stream) {
+  if (!s || !h || !low_level_time_host || !t_host || slot < 0 || slot > 1)
+    return fail(HRG_EINVAL, "hrg_shield_tick_replay_piped: bad argument");
+  if (h->H.N != s->S.N || h->H.K != s->S.K || h->device != s->device)
+    return fail(HRG_EINVAL, "hrg_shield_tick_replay_piped: the human batch and the shield batch differ (envs, keypoints or device)");
+  CK(cudaSetDevice(s->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream), cs = static_cast<cudaStream_t>(copy_stream);
+  const size_t N = s->S.N, J = s->S.J;
+  CK(cudaMemcpyAsync(h->d_clock, low_level_time_host, N * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(s->d_t, t_host, N * sizeof(double), cudaMemcpyHostToDevice, st));
+  const bool goal = goal_mask_host && goal_q_host;
+  if (goal) {
+    CK(cudaMemcpyAsync(s->d_goal_mask, goal_mask_host, N, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(s->d_goal, goal_q_host, N * J * sizeof(double), cudaMemcpyHostToDevice, st));
+  }
+  if (s->out_used[slot]) CK(cudaStreamWaitEvent(st, s->ev_copied[slot], 0));  // the slot's previous copy has left it
+  int rc = hrg_human_keypoints(h, h->d_clock, s->d_kp, nullptr, nullptr, stream);
+  if (rc) return rc;
+  double** o = s->d_out2[slot];
+  rc = hrg_shield_tick_device(s, s->d_kp, s->d_t, goal ? s->d_goal_mask : nullptr, goal ? s->d_goal : nullptr, o[0], o[1], o[2],
+                              nullptr, s->d_safe2[slot], s->d_branch2[slot], nullptr, stream);
+  if (rc) return rc;
+  if (flags_host) {
+    k_pack_flags<<<grid_for((int)N, 256), 256, 0, st>>>((int)N, s->d_safe2[slot], s->d_branch2[slot], s->d_flags82[slot]);
+    s->launches++;
+  }
+  CK(cudaEventRecord(s->ev_out[slot], st));
+  CK(cudaStreamWaitEvent(cs, s->ev_out[slot], 0));
+  if (q_host) CK(cudaMemcpyAsync(q_host, o[0], N * J * sizeof(double), cudaMemcpyDeviceToHost, cs));
+  if (dq_host) CK(cudaMemcpyAsync(dq_host, o[1], N * J * sizeof(double), cudaMemcpyDeviceToHost, cs));
+  if (ddq_host) CK(cudaMemcpyAsync(ddq_host, o[2], N * J * sizeof(double), cudaMemcpyDeviceToHost, cs));
+  if (flags_host) CK(cudaMemcpyAsync(flags_host, s->d_flags82[slot], N, cudaMemcpyDeviceToHost, cs));
+  CK(cudaEventRecord(s->ev_copied[slot], cs));
+  s->out_used[slot] = true;
+  return HRG_OK;
+}
+
 int64_t hrg_human_launch_count(const HrgHuman* h) { return h ? h->launches : 0; }
 
 }  // extern "C"

@@ -80,6 +80,13 @@ struct HrgShield {
   uint8_t* d_safe = nullptr;
   uint8_t* d_branch = nullptr;
   uint8_t* d_flags8 = nullptr;
+  // second set of output buffers + events of the pipelined replay tick (hrg_shield_tick_replay_piped)
+  double* d_out2[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+  uint8_t* d_safe2[2] = {nullptr, nullptr};
+  uint8_t* d_branch2[2] = {nullptr, nullptr};
+  uint8_t* d_flags82[2] = {nullptr, nullptr};
+  cudaEvent_t ev_out[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
+  bool out_used[2] = {false, false};
   size_t reach_smem = 0, reach_smem_p0 = 0;
   size_t measure_smem = 0;
   // k_replan runs on its own stream, concurrently with the first reach + verify pass (envs that do not replan)
@@ -267,6 +274,12 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
   AL(h->d_safe, N);
   AL(h->d_branch, N);
   AL(h->d_flags8, N);
+  for (int k = 0; k < 2; ++k) {
+    for (int c = 0; c < 3; ++c) AL(h->d_out2[k][c], (size_t)J * N);
+    AL(h->d_safe2[k], N);
+    AL(h->d_branch2[k], N);
+    AL(h->d_flags82[k], N);
+  }
 #undef AL
   h->reach_smem = (size_t)reach_smem_doubles(J, H) * sizeof(double);
   h->measure_smem = (size_t)kTileEnvs * ((K * 3) | 1) * sizeof(double);
@@ -294,6 +307,10 @@ int hrg_shield_create(const HrgConfig* cfg, int n_envs, int device, const double
       if (atoi(v) >= 1 && atoi(v) <= 4) h->deep_per_warp = atoi(v);
   }
   if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&h->meas, cudaStreamNonBlocking);
+  for (int k = 0; k < 2 && ce == cudaSuccess; ++k) {
+    ce = cudaEventCreateWithFlags(&h->ev_out[k], cudaEventDisableTiming);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_copied[k], cudaEventDisableTiming);
+  }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&h->ev_meas, cudaEventDisableTiming);
@@ -338,6 +355,10 @@ int hrg_shield_destroy(HrgShield* s) {
   cudaSetDevice(s->device);
   for (void* p : s->allocs) cudaFree(p);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
+  for (int k = 0; k < 2; ++k) {
+    if (s->ev_out[k]) cudaEventDestroy(s->ev_out[k]);
+    if (s->ev_copied[k]) cudaEventDestroy(s->ev_copied[k]);
+  }
   if (s->ev_fork) cudaEventDestroy(s->ev_fork);
   if (s->meas) cudaStreamDestroy(s->meas);
   if (s->ev_join) cudaEventDestroy(s->ev_join);

@@ -192,6 +192,18 @@ class BatchedHumanAnimation:
                 shield._h, self._h, _ptr(low_level_time_host), _ptr(t_host), _ptr(goal_mask_host), _ptr(goal_q_host),
                 _ptr(q_host), _ptr(dq_host), _ptr(ddq_host), _ptr(flags_host), self._stream()), "hrg_shield_tick_replay_host")
 
+    def tick_replay_piped(self, shield, slot, low_level_time_host, t_host, goal_mask_host, goal_q_host, q_host, dq_host,
+                          ddq_host, flags_host, copy_stream):
+        """tick_replay_host with the setpoints leaving on `copy_stream` (a torch.cuda.Stream) out of output slot 0/1, so that
+        the device->host copy of this tick overlaps the kernels of the next (hrg_shield_tick_replay_piped). Alternate the
+        slots, give each slot its own host buffers (inputs too), and wait for an event recorded on `copy_stream` after the
+        call before reading the slot's setpoints."""
+        with torch.cuda.device(self.device):
+            cabi.check(self.lib.hrg_shield_tick_replay_piped(
+                shield._h, self._h, int(slot), _ptr(low_level_time_host), _ptr(t_host), _ptr(goal_mask_host), _ptr(goal_q_host),
+                _ptr(q_host), _ptr(dq_host), _ptr(ddq_host), _ptr(flags_host), self._stream(), copy_stream.cuda_stream),
+                "hrg_shield_tick_replay_piped")
+
     @property
     def launch_count(self) -> int:
         return int(self.lib.hrg_human_launch_count(self._h))

@@ -308,6 +308,13 @@ int hrg_human_keypoints(HrgHuman* h, const int64_t* low_level_time, double* keyp
 int hrg_shield_tick_replay_host(HrgShield* s, HrgHuman* h, const int64_t* low_level_time_host, const double* t_host,
                                 const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
                                 double* ddq_host, uint8_t* flags_host, void* stream);
+/* hrg_shield_tick_replay_host with the setpoints of the tick copied to the host on `copy_stream` out of output slot 0/1, so
+ * that the copy overlaps the NEXT tick's kernels (the shield follows its own trajectory: a tick never needs the host to have
+ * seen the previous setpoints - SS/src/safety_shield.cc:555-647 reads no measured robot state). The host buffers of a slot are
+ * valid once `copy_stream` has passed the call (synchronise it, or call again on the same slot); alternate the slots. */
+int hrg_shield_tick_replay_piped(HrgShield* s, HrgHuman* h, int slot, const int64_t* low_level_time_host, const double* t_host,
+                                 const uint8_t* goal_mask_host, const double* goal_q_host, double* q_host, double* dq_host,
+                                 double* ddq_host, uint8_t* flags_host, void* stream, void* copy_stream);
 int64_t hrg_human_launch_count(const HrgHuman* h);
 
 /* Register-resident FP64 throughput of CUDA device `device` (the FP-pipe roofline denominator, not in

@@ -231,3 +231,60 @@ def test_tick_replay_host_equals_keypoints_then_tick():
     assert int((fl_p.numpy() >> 1).max()) <= 2
     for x in sh + hu:
         x.close()
+
+
+@pytest.mark.gpu
+def test_tick_replay_piped_equals_tick_replay_host():
+    """hrg_shield_tick_replay_piped (setpoints of tick k copied on a second stream while tick k + 1 computes, two output slots)
+    returns the setpoints of hrg_shield_tick_replay_host, tick for tick, when read one tick late."""
+    import torch
+    from human_robot_gym_b200.batched import BatchedSafetyShield
+    from human_robot_gym_b200.config import ShieldConfig
+    from human_robot_gym_b200.human_animation import BatchedHumanAnimation
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+    from tests.parity_util import default_files, mocap_joint_names
+    tree, clips = load_fixture()
+    files = default_files("schunk")
+    sc = ShieldConfig.from_files(0.004, *files)
+    n = 211
+    scen = SyntheticScenario(n, mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, 57)
+    rng = np.random.default_rng(57)
+    pos, quat = random_placements(rng, n, (-1.5, 0.0, 0.0), 0.7)
+    ids = rng.integers(0, 2, (n, 2)).astype(np.int32)
+    sh = [BatchedSafetyShield(n, 0.004, *files, init_qpos=scen.init_q, device="cuda:0") for _ in range(2)]
+    hu = [BatchedHumanAnimation(tree, clips, n, device="cuda:0", n_animations_per_env=2) for _ in range(2)]
+    for h in hu:
+        h.reset(pos, quat, ids)
+    pin = dict(pin_memory=True)
+    mk = lambda: [torch.zeros(n, 6, dtype=torch.float64, **pin) for _ in range(3)] + [torch.zeros(n, dtype=torch.uint8, **pin)]  # noqa: E731
+    ref_out, slots = mk(), [mk(), mk()]
+    clock = [torch.zeros(n, dtype=torch.int64, **pin) for _ in range(3)]
+    tt = [torch.zeros(n, dtype=torch.float64, **pin) for _ in range(3)]
+    copy_stream = torch.cuda.Stream(device="cuda:0")
+    want, evs = {}, [None, None]
+    T = 60
+    for k in range(T):
+        gmask = (np.arange(n) % 25) == (k % 25)
+        g = scen.next_goal(gmask)
+        gm_p, gq_p = torch.from_numpy(gmask.astype(np.uint8)).pin_memory(), torch.from_numpy(g).pin_memory()
+        clock[2].fill_(k + 230)
+        tt[2].fill_(k * 0.004)
+        hu[0].tick_replay_host(sh[0], clock[2], tt[2], gm_p, gq_p, *ref_out)
+        torch.cuda.synchronize()
+        want[k] = [x.clone() for x in ref_out]
+        sl = k & 1
+        clock[sl].fill_(k + 230)
+        tt[sl].fill_(k * 0.004)
+        hu[1].tick_replay_piped(sh[1], sl, clock[sl], tt[sl], gm_p, gq_p, *slots[sl], copy_stream)
+        ev = torch.cuda.Event()
+        ev.record(copy_stream)
+        evs[sl] = ev
+        if k >= 1:                                   # the setpoints of the PREVIOUS tick have arrived
+            evs[sl ^ 1].synchronize()
+            for a, b in zip(slots[sl ^ 1], want[k - 1]):
+                assert torch.equal(a, b), k
+        torch.cuda.synchronize()                     # (gm_p / gq_p are per-iteration buffers)
+    for a, b in zip(slots[(T - 1) & 1], want[T - 1]):
+        assert torch.equal(a, b)
+    for x in sh + hu:
+        x.close()
