@@ -492,7 +492,8 @@ def test_time_scaling_ladder_same_in_both_root_modes():
     switch times - for moving starts and, above all, for starts from exact rest, whose candidate polynomials x^k q(x) the QR
     iteration answers with noise roots (csrc/ltp_scaling.cuh: ltp_cand_rejected_from_rest)."""
     rng = np.random.default_rng(2024)
-    lims = [[-3.0, 3.0, 2.0, 2.0, 15.0], [-2.9, 2.9, 2.6, 10.0, 400.0], [-3.1, 3.1, 1.0, 4.0, 40.0]]
+    lims = [[-2.9, 2.9, 1.0, 2.0, 15.0],                    # Schunk / Panda: v_max_allowed, a_max_ltt, j_max_ltt
+            [-2.9, 2.9, 2.6, 10.0, 400.0], [-3.1, 3.1, 1.0, 4.0, 40.0]]
     n_rest = n_acc = n = 0
     try:
         for trial in range(6000):
