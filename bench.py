@@ -238,6 +238,26 @@ def fp64_inst_per_launch(kernel, n_envs=65536, replans=1117):
     return _ncu_table("fp64_counts.json", kernel, n_envs, replans)
 
 
+def reference_flop_count(args):
+    """F_step of BASELINE.md 3 for this workload: FP64 add / sub / mul / div / sqrt / min-max instructions per shield-step the
+    reference's own compiled code executes on it (profiles/r03_flop_count.md: basic-block counts of an instrumented build of
+    oracle/_ref joined with its disassembly). A committed number, read from profiles/; None for a workload without a count."""
+    tag = f"{args.robot}_{args.shield}"
+    if "full_body" in args.mocap:
+        tag += "_config4"
+    elif args.mocap != "mujoco_mocap":
+        return None
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", f"r03_flop_count_{tag}.json")) as f:
+            r = json.load(f)
+        p = r["per_step"]
+        return {"F_step": r["F_step"], "add_sub": p.get("add", 0.0), "mul": p.get("mul", 0.0), "div": p.get("div", 0.0),
+                "sqrt": p.get("sqrt", 0.0), "libm_calls": p.get("libm_calls", 0.0), "counted_on": r["workload"],
+                "source": f"profiles/r03_flop_count_{tag}.json"}
+    except (OSError, ValueError, KeyError, TypeError):
+        return None
+
+
 def run_reference(args, files, sc, names, rank):
     if rank != 0:
         return
@@ -772,6 +792,12 @@ def main():
                            "pinned by the reference's 71 gtests + LAPACK cross-check); planner roots: derivative-chain finder with "
                            "the eigen-solve restatement as arbiter of close calls (HRG_ROOT_MODE=0: eigen-solve for everything)",
         }
+        fc = reference_flop_count(args)
+        if fc:
+            # the reference's counted arithmetic at this run's rate, per GPU, against the measured DMUL + DADD issue rate
+            fc["algorithmic_TFLOPs_per_gpu"] = fc["F_step"] * value / world / 1e12
+            fc["frac_of_fp64_peak"] = fc["F_step"] * value / world / ginst_peak if ginst_peak else None
+            line["flop_count_reference"] = fc
         if strong:
             strong["note"] = ("BASELINE config 3: this many shields IN TOTAL, sharded env-wise; the per-GPU batch shrinks with N, so "
                               "the tick approaches the latency floor of its dependent kernel chain - strong-scaling efficiency "
