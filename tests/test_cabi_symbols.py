@@ -109,3 +109,49 @@ def test_human_replay_has_no_cpu_fallback_either():
     assert create(2, 0.5) == cabi.EINVAL               # animation faster than the simulation (human_env.py:1466)
     assert lib.hrg_human_keypoints(None, None, None, None, None, None) == cabi.EINVAL
     assert lib.hrg_capsule_markers(-1, None, None, None, None, None) == cabi.EINVAL
+
+
+def test_product_never_touches_the_oracle():
+    """oracle/ and tests/ are test infrastructure: the package and the importable drop-in never import them, no CUDA / C++
+    source of the library includes anything from there, bench.py executes oracle/ in its CPU leg only (cpu_loop: the
+    `cpu_baseline` key and --impl reference) and __graft_entry__ in build() (compiling the checker) and smoke() (checking)."""
+    import ast
+    import glob
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+    def oracle_imports(path):
+        """{enclosing top-level function or '<module>': [imported module names that start with oracle / tests]}"""
+        with open(path) as f:
+            tree = ast.parse(f.read())
+        found = {}
+
+        def visit(node, where):
+            for ch in ast.iter_child_nodes(node):
+                w = ch.name if where == "<module>" and isinstance(ch, (ast.FunctionDef, ast.ClassDef)) else where
+                names = []
+                if isinstance(ch, ast.Import):
+                    names = [a.name for a in ch.names]
+                elif isinstance(ch, ast.ImportFrom) and ch.module and ch.level == 0:
+                    names = [ch.module]
+                for nm in names:
+                    if nm.split(".")[0] in ("oracle", "tests"):
+                        found.setdefault(w, []).append(nm)
+                visit(ch, w)
+        visit(tree, "<module>")
+        return found
+
+    product = glob.glob(os.path.join(root, "human_robot_gym_b200", "**", "*.py"), recursive=True) \
+        + glob.glob(os.path.join(root, "safety_shield_py", "**", "*.py"), recursive=True)
+    assert len(product) > 5
+    for p in product:
+        assert oracle_imports(p) == {}, p
+    for p in glob.glob(os.path.join(root, "human_robot_gym_b200", "csrc", "*")) + glob.glob(os.path.join(root, "include", "*")):
+        with open(p, errors="replace") as f:
+            for line in f:
+                if line.lstrip().startswith("#include"):
+                    assert "oracle" not in line and "tests/" not in line and "host_emul" not in line, (p, line)
+    b = oracle_imports(os.path.join(root, "bench.py"))
+    assert set(b) <= {"cpu_loop"} and all(n.startswith("oracle") for n in b.get("cpu_loop", [])), b
+    g = oracle_imports(os.path.join(root, "__graft_entry__.py"))
+    assert set(g) <= {"smoke", "build"}, g
