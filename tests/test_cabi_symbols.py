@@ -155,3 +155,18 @@ def test_product_never_touches_the_oracle():
     assert set(b) <= {"cpu_loop"} and all(n.startswith("oracle") for n in b.get("cpu_loop", [])), b
     g = oracle_imports(os.path.join(root, "__graft_entry__.py"))
     assert set(g) <= {"smoke", "build"}, g
+
+
+def test_integration_doc_names_every_entry_point():
+    """INTEGRATION.md maps each function include/hrg_shield.h declares to the reference interface it replaces (or says it
+    has none): a new entry point must not ship without its row."""
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with open(os.path.join(root, "include", "hrg_shield.h")) as f:
+        names = sorted(set(re.findall(r"\b(hrg_[a-z0-9_]+)\s*\(", f.read())))
+    with open(os.path.join(root, "INTEGRATION.md")) as f:
+        doc = f.read()
+    wild = [m[:-1] for m in re.findall(r"`(hrg_[a-z0-9_]+\*)`", doc)]          # rows such as `hrg_stage_*`
+    missing = [n for n in names if n not in doc and not any(n.startswith(w) for w in wild)]
+    assert len(names) >= 40 and not missing, missing
