@@ -493,16 +493,17 @@ def test_time_scaling_ladder_same_in_both_root_modes():
     iteration answers with noise roots (csrc/ltp_scaling.cuh: ltp_cand_rejected_from_rest)."""
     rng = np.random.default_rng(2024)
     lims = [[-2.9, 2.9, 1.0, 2.0, 15.0],                    # Schunk / Panda: v_max_allowed, a_max_ltt, j_max_ltt
+            [-6.28318530718, 6.28318530718, 3.14, 2.0, 15.0], [-6.28318530718, 6.28318530718, 6.28, 2.0, 15.0],   # ur5e
             [-2.9, 2.9, 2.6, 10.0, 400.0], [-3.1, 3.1, 1.0, 4.0, 40.0]]
     n_rest = n_acc = n = 0
     try:
-        for trial in range(6000):
-            lim = lims[trial % 3]
-            rest = trial % 2 == 0
-            q0 = rng.uniform(-2.0, 2.0)
+        for trial in range(10000):
+            lim = lims[trial % len(lims)]
+            rest = (trial // len(lims)) % 2 == 0
+            q0 = rng.uniform(0.7 * lim[0], 0.7 * lim[1])
             v0 = 0.0 if rest else rng.uniform(-0.8, 0.8) * lim[2]
             a0 = 0.0 if rest else rng.uniform(-0.8, 0.8) * lim[3]
-            q_goal = float(np.clip(q0 + rng.choice([0.002, 0.05, 0.5, 2.0]) * rng.uniform(-1, 1), lim[0], lim[1]))
+            q_goal = float(np.clip(q0 + rng.choice([0.002, 0.05, 0.5, 2.0, 8.0]) * rng.uniform(-1, 1), lim[0], lim[1]))
             emul.set_root_mode(0)
             ok, t_opt, direction, _ = emul.ltp_opt_switch_times(0.004, lim, q_goal, q0, v0, a0, lim[2])
             if not ok:
@@ -522,4 +523,4 @@ def test_time_scaling_ladder_same_in_both_root_modes():
     finally:
         emul.set_root_mode(0)
     print(f"{n} ladders ({n_rest} from rest), {n_acc} with an accepted candidate")
-    assert n > 4000 and n_rest > 1500 and 0.2 * n < n_acc < n
+    assert n > 7000 and n_rest > 2500 and 0.2 * n < n_acc < n
