@@ -352,6 +352,18 @@ def test_tick_logic_matches_oracle_closed_loop(robot, mocap, traj, n, ticks, see
     assert hist[0] > 0 and hist[2] > 0
 
 
+@needs_ref
+@pytest.mark.parametrize("robot", ["iiwa", "jaco", "kinova3", "sawyer", "ur5e", "modrob0", "modrob1"])
+@pytest.mark.parametrize("shield_type", [1, 2])
+def test_tick_logic_matches_oracle_on_every_shipped_robot(robot, shield_type):
+    """The other robots the reference ships configs for (SS/config/robot_parameters_*.yaml, trajectory_parameters_*.yaml:
+    3 / 6 / 7 joints, their own kinematic chains and capsules, ur5e with its own velocity limits), SSM and PFL."""
+    mis, near, worst, hist = _closed_loop(pu.default_files(robot, "mujoco_mocap", None), 48, 160, 4242, shield_type)
+    assert mis == 0 and near <= 1, (mis, near)
+    assert worst < 1e-7            # north_star: 1e-5; root_mode 1 moves a switch time by up to ~1e-9 relative (jaco: 3e-9 here)
+    assert hist[0] > 0 and hist.sum() >= 48 * 160 - 48
+
+
 # ---- sliding-window maxima of a LongTermTraj (SURVEY.md 8(f)-4) ----------------------------------------------------------
 def _window_golden():
     """long_term_traj_tests.cc:66-193 (MaxAccWindowTest / MaxJerkWindowTest): 7 samples, 2 joints, k = 3."""
