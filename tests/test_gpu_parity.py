@@ -454,3 +454,16 @@ def test_sparse_goal_upload_equals_dense():
         for x, y in zip(outs[0], outs[1]):
             assert torch.equal(x, y), k
     assert a.stats()["n_replan"] == b.stats()["n_replan"] > n
+
+
+@pytest.mark.parametrize("robot,shield_type,store", [("modrob0", 1, False), ("modrob0", 2, True), ("ur5e", 1, False),
+                                                     ("iiwa", 1, True), ("jaco", 2, False), ("sawyer", 1, False)])
+def test_closed_loop_other_shipped_robots(robot, shield_type, store):
+    """Robots the reference ships configs for besides Schunk and Panda: 3 joints (modrob0: the generic-J forms of the sampler
+    and of the PFL constructor), 6 with their own velocity limits (ur5e), 7 (iiwa, jaco, sawyer); SSM and PFL, with and
+    without stored capsules (plain reach + verify / the model cascade)."""
+    res = pu.closed_loop_compare(pu.default_files(robot), n_envs=256, ticks=150, seed=5100, shield_type=shield_type,
+                                 store_capsules=store)
+    print(robot, res)
+    pu.assert_parity(res)
+    assert res["gpu_stats"]["n_replan"] > 0 and res["branch_hist"][0] > 0
