@@ -467,3 +467,16 @@ def test_closed_loop_other_shipped_robots(robot, shield_type, store):
     print(robot, res)
     pu.assert_parity(res)
     assert res["gpu_stats"]["n_replan"] > 0 and res["branch_hist"][0] > 0
+
+
+@pytest.mark.parametrize("robot,sample_time,shield_type", [("schunk", 0.001, 1), ("schunk", 0.002, 2), ("panda", 0.01, 1),
+                                                           ("schunk", 0.008, 1)])
+def test_closed_loop_other_sample_times(robot, sample_time, shield_type):
+    """The shield's sample time is a constructor argument (bindings :46-62; human-robot-gym runs 0.004, the reference's
+    tests 0.001): LTT sampling and the planner's rounding of switch times to whole samples; at 8-10 ms the reference starts to
+    reject plans (`t_rel[i] < -eps`, LTP/src/long_term_planner.cc:341-343), and so must the device, env for env."""
+    res = pu.closed_loop_compare(pu.default_files(robot), n_envs=128, ticks=200, seed=5300, shield_type=shield_type,
+                                 sample_time=sample_time, store_capsules=False, ltt_capacity=4096)
+    print(robot, sample_time, res)
+    pu.assert_parity(res)
+    assert res["gpu_stats"]["n_replan"] > 0 and res["branch_hist"][0] > 0 and res["branch_hist"][2] > 0
