@@ -11,6 +11,28 @@ from human_robot_gym_b200.workloads import (config_dir, configs, default_files, 
                                             mocap_joint_names)
 
 
+def variant_files(robot="schunk", mocap=None, traj=None):
+    """default_files(robot) with keys of the mocap and / or trajectory YAML overridden (written to a fresh temporary
+    directory): configurations the shipped files never exercise, e.g. a measurement delay and measurement errors
+    (all shipped mocap files carry zeros), per-joint limits that differ from joint to joint, other PFL parameters."""
+    import tempfile
+
+    import yaml
+    t, r, m = default_files(robot)
+    d = tempfile.mkdtemp(prefix="shield_cfg_variant_")
+    if mocap:
+        cfg = dict(configs()["mujoco_mocap"], **mocap)
+        m = os.path.join(d, "mujoco_mocap_variant.yaml")
+        with open(m, "w") as f:
+            yaml.safe_dump(cfg, f, default_flow_style=None)
+    if traj:
+        cfg = dict(configs()[f"trajectory_parameters_{robot}"], **traj)
+        t = os.path.join(d, f"trajectory_parameters_{robot}_variant.yaml")
+        with open(t, "w") as f:
+            yaml.safe_dump(cfg, f, default_flow_style=None)
+    return t, r, m
+
+
 def make_checker(files, n, base_pose, init_q, sample_time=0.004, shield_type=1, threads=8):
     """The CPU checker for a batch: the reference build (oracle/_ref). There is no second checker."""
     from oracle import ref

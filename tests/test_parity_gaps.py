@@ -33,6 +33,21 @@ SCENARIOS = {
     "mixed_types": ("schunk", dict(shield_type="mixed", seed=2106)),
     "mixed_types_panda_reset": ("panda", dict(shield_type="mixed", base_pose="random", reset_period=50,
                                               reset_types=[0, 1, 2], seed=2107)),
+    # (h) configuration values no shipped YAML carries (`cfg`: overrides of the mocap / trajectory file, pu.variant_files):
+    #     measurement delay and errors (SS/src/human_reach.cc:9-24 hands them to reach_lib::System: reach time + delay, radii +
+    #     errors; every shipped mocap file has zeros), PFL parameters (v_safe, alpha_i_max), limits that differ per joint
+    "meas_delay_errors": ("schunk", dict(cfg=dict(mocap=dict(delay=0.05, measurement_error_pos=0.02,
+                                                             measurement_error_vel=0.1)), seed=5401)),
+    "meas_errors_panda_pfl": ("panda", dict(cfg=dict(mocap=dict(delay=0.012, measurement_error_pos=0.005,
+                                                                 measurement_error_vel=0.3)), shield_type=2, seed=5402)),
+    "pfl_parameters": ("schunk", dict(cfg=dict(traj=dict(v_safe=0.25, alpha_i_max=1.0, max_s_stop=0.35)), shield_type=2,
+                                      seed=5403)),
+    "per_joint_limits": ("schunk", dict(cfg=dict(mocap=dict(delay=0.02, measurement_error_pos=0.01),
+                                                 traj=dict(a_max_allowed=[6.0, 10.0, 8.0, 10.0, 5.0, 10.0],
+                                                           j_max_allowed=[150.0, 400.0, 300.0, 400.0, 200.0, 400.0],
+                                                           a_max_ltt=[1.0, 2.0, 1.5, 2.0, 1.0, 2.0],
+                                                           j_max_ltt=[8.0, 15.0, 10.0, 15.0, 8.0, 15.0],
+                                                           v_max_allowed=[0.7, 1.3, 1.0, 0.5, 2.0, 1.0])), seed=5404)),
 }
 
 
@@ -41,7 +56,9 @@ def _run(name, n_envs, ticks, backend, **extra):
     kw = dict(kw, **extra)
     if isinstance(kw.get("shield_type"), str):
         kw["shield_type"] = np.arange(n_envs) % 3          # OFF, SSM, PFL interleaved
-    res = pu.closed_loop_compare(pu.default_files(robot), n_envs=n_envs, ticks=ticks, backend=backend, **kw)
+    cfg = kw.pop("cfg", None)
+    files = pu.variant_files(robot, **cfg) if cfg else pu.default_files(robot)
+    res = pu.closed_loop_compare(files, n_envs=n_envs, ticks=ticks, backend=backend, **kw)
     print(name, backend, res)
     pu.assert_parity(res)
     if kw.get("reset_period"):
