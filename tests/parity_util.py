@@ -114,8 +114,8 @@ class EmulShield:
     def reset(self, base_pose, init_qpos, current_time=0.0, shield_type=1, env_mask=None):
         self.em.reset(base_pose, init_qpos, shield_type, mask=env_mask)
 
-    def humanMeasurement(self, kp, t):
-        self.em.human_measurement(kp, t)
+    def humanMeasurement(self, kp, t, env_mask=None):
+        self.em.human_measurement(kp, np.broadcast_to(np.asarray(t, float), (self.n_envs,)), mask=env_mask)
 
     def newLongTermTrajectory(self, g, env_mask=None):
         self.em.new_goal(g, mask=env_mask)
@@ -141,7 +141,7 @@ class EmulShield:
 def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0", sample_time=0.004, shield_type=1,
                         goal_period=25, stagger=True, ltt_capacity=1024, base_pose=None, collect=None,
                         store_capsules=True, human=None, scenario=None, reset_period=0, reset_types=None,
-                        backend="cuda"):
+                        backend="cuda", meas_every=1, meas_lag=0.0):
     """Drives BatchedSafetyShield (CUDA) and the CPU checker in lockstep on identical synthetic inputs.
 
     Decisions (is_safe, branch) must match exactly; an env whose FIRST mismatch happens on a tick where either side
@@ -162,6 +162,9 @@ def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0"
     (SafetyShield::reset, SS/src/safety_shield.cc:164-201) with a new random base pose, a new init_qpos and - when
     reset_types is a list of ShieldTypes - a new random shield type out of it; the human keypoint history is kept, as
     HumanReach::reset keeps it (SS/src/human_reach.cc:44-50).
+    meas_every > 1: on every tick each env receives a human measurement with probability 1 / meas_every only (masked
+    humanMeasurement; the reach time t_command - last_meas_timestep_ + t_brake of SS/src/human_reach.cc:76-80 then differs
+    from env to env); meas_lag: the measurement's timestamp lies that far behind the cycle time handed to step().
     """
     from human_robot_gym_b200.config import ShieldConfig
     from human_robot_gym_b200.synthetic import SyntheticScenario
@@ -179,6 +182,7 @@ def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0"
     Scen = scenario or SyntheticScenario
     scen = Scen(n_envs, mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, seed)
     rng = np.random.default_rng(seed + 99991)
+    rng_meas = np.random.default_rng(seed + 7)
     if base_pose is None:
         pose = np.zeros((n_envs, 6))
     elif isinstance(base_pose, str) and base_pose == "random":
@@ -216,9 +220,16 @@ def closed_loop_compare(files, n_envs=256, ticks=100, seed=1001, device="cuda:0"
         elif hasattr(scen, "keypoints_adaptive"):
             kp = scen.keypoints_adaptive(k, chk)
         else:
-            kp = scen.keypoints(t)
-        chk.human_measurement(kp, t)
-        gpu.humanMeasurement(to_dev(kp) if human is None else human.device_keypoints(k), t)
+            kp = scen.keypoints(t - meas_lag)
+        mm = None
+        if meas_every > 1:
+            mm = rng_meas.random(n_envs) < 1.0 / meas_every
+            if k == 0:
+                mm[:] = True
+        if mm is None or mm.any():
+            chk.human_measurement(kp, t - meas_lag, mask=mm)
+            gpu.humanMeasurement(to_dev(kp) if human is None else human.device_keypoints(k), t - meas_lag,
+                                 env_mask=None if mm is None else to_dev(mm))
         gmask = scen.goal_mask(k) if hasattr(scen, "goal_mask") else (phase == (k % goal_period))
         if gmask.any():
             g = scen.next_goal(gmask)

@@ -42,6 +42,10 @@ SCENARIOS = {
                                                                  measurement_error_vel=0.3)), shield_type=2, seed=5402)),
     "pfl_parameters": ("schunk", dict(cfg=dict(traj=dict(v_safe=0.25, alpha_i_max=1.0, max_s_stop=0.35)), shield_type=2,
                                       seed=5403)),
+    # (i) measurements that do not arrive on every tick and carry an older timestamp (masked humanMeasurement: the reach
+    #     time of SS/src/human_reach.cc:76-80 then differs from env to env and grows between measurements)
+    "irregular_measurements": ("schunk", dict(meas_every=3, meas_lag=0.002, seed=5501)),
+    "irregular_measurements_panda_pfl": ("panda", dict(meas_every=4, meas_lag=0.0013, shield_type=2, seed=5502)),
     "per_joint_limits": ("schunk", dict(cfg=dict(mocap=dict(delay=0.02, measurement_error_pos=0.01),
                                                  traj=dict(a_max_allowed=[6.0, 10.0, 8.0, 10.0, 5.0, 10.0],
                                                            j_max_allowed=[150.0, 400.0, 300.0, 400.0, 200.0, 400.0],
