@@ -238,3 +238,92 @@ def test_small_ltt_capacity_is_reported_not_silent():
     assert full.check_health()["n_ltt_truncated"] == 0 and float(full.q.abs().max()) > 1e-3
     small.close()
     full.close()
+
+
+# (j) edge inputs, on the host build of the tick logic (CPU only): what a caller can hand over without breaking any rule of the
+# reference's API. Same lockstep comparison as everywhere else; ltt_capacity 2048 because moves from limit to limit are long.
+EDGE_MODES = ["static_human", "collapsed_human", "dup_timestamps", "time_backwards", "human_far", "human_inside_robot",
+              "goals_outside_limits", "goals_at_limits", "init_at_limits", "init_beyond_limits"]
+
+
+@needs_ref
+@pytest.mark.parametrize("robot,shield_type", [("schunk", 1), ("panda", 2)])
+@pytest.mark.parametrize("mode", EDGE_MODES)
+def test_edge_inputs_host_logic_matches_reference(mode, robot, shield_type):
+    """static_human: the same keypoints every tick (zero velocities). collapsed_human: all keypoints in one point (every human
+    capsule a sphere: the exact-equality sphere dispatch of RL/include/intersections.hpp:105-126). dup_timestamps: every second
+    measurement repeats the previous time (the dt < 1e-7 branch of SS/src/human_reach.cc:52-62 keeps the old velocity).
+    time_backwards: some measurements carry an older time than the one before (negative dt, sign-flipped velocities).
+    human_far / human_inside_robot: never / always in collision. goals outside / exactly at the joint limits
+    (LongTermPlanner::checkInputs, LTP/src/long_term_planner.cc:68-77). init_at_limits / init_beyond_limits: the robot starts
+    on / 2 % outside its limits (checkMotionForJointLimits, SS/src/safety_shield.cc:502-509)."""
+    from human_robot_gym_b200.cabi import make_cfg
+    from human_robot_gym_b200.config import ShieldConfig
+    from human_robot_gym_b200.synthetic import SyntheticScenario
+    from tests.host_emul import emul
+    n, ticks, seed = 48, 130, 77
+    files = pu.default_files(robot)
+    sc = ShieldConfig.from_files(0.004, *files)
+    scen = SyntheticScenario(n, pu.mocap_joint_names(files[2]), sc.traj.q_min_allowed, sc.traj.q_max_allowed, seed)
+    qlo, qhi = np.asarray(sc.traj.q_min_allowed), np.asarray(sc.traj.q_max_allowed)
+    rng = np.random.default_rng(seed)
+    init_q = scen.init_q.copy()
+    if mode in ("init_at_limits", "init_beyond_limits"):
+        init_q = np.where(rng.random(init_q.shape) < 0.5, qlo, qhi)
+        if mode == "init_beyond_limits":
+            init_q = init_q * np.where(rng.random(init_q.shape) < 0.3, 1.02, 1.0)
+    pose = np.zeros((n, 6))
+    chk = ref.RefBatch(n, 0.004, *files, pose, init_q, shield_type=shield_type, threads=4)
+    em = emul.EmulBatch(make_cfg(sc, 2048), n, pose, init_q, shield_type)
+    phase = np.arange(n) % 25
+    alive = np.ones(n, bool)
+    mis = near = 0
+    worst = 0.0
+    hist = np.zeros(3, int)
+    kp0 = scen.keypoints(0.0)
+    for k in range(ticks):
+        t = tm = k * 0.004
+        kp = scen.keypoints(t)
+        if mode == "static_human":
+            kp = kp0
+        elif mode == "collapsed_human":
+            kp = np.broadcast_to(kp0[:, :1, :], kp0.shape) + 0.001 * k * np.array([1.0, 0.0, 0.0])
+        elif mode == "dup_timestamps":
+            tm = (k // 2) * 0.008
+        elif mode == "time_backwards":
+            tm = t - (0.02 if k % 7 == 3 else 0.0)
+        elif mode == "human_far":
+            kp = kp + np.array([50.0, 0.0, 0.0])
+        elif mode == "human_inside_robot":
+            kp = kp * 0.05
+        chk.human_measurement(kp, tm)
+        em.human_measurement(kp, np.full(n, tm))
+        g = phase == (k % 25)
+        if g.any():
+            goal = scen.next_goal(g)
+            if mode == "goals_outside_limits":
+                goal = goal + np.where(rng.random(goal.shape) < 0.3, rng.choice([-1.0, 1.0], goal.shape) * (qhi - qlo) * 0.6, 0.0)
+            elif mode == "goals_at_limits":
+                goal = np.where(rng.random(goal.shape) < 0.5, qlo, qhi)
+            chk.new_goal(goal, mask=g)
+            em.new_goal(goal, mask=g)
+        a, b = chk.step(t), em.step(np.full(n, t))
+        assert not (b["status"] & 16).any()                       # HRG_ST_LTT_TRUNCATED: the capacity contract, not this test
+        bad = ((a["is_safe"] != b["is_safe"]) | (a["branch"] != b["branch"])) & alive
+        if bad.any():
+            md = chk.capsules(em.H)[2]
+            nr = ((b["status"] & 32) != 0) | (np.abs(np.where(np.isfinite(md), md, 1.0)).min(axis=1) < 1e-6)
+            near += int((bad & nr).sum())
+            mis += int((bad & ~nr).sum())
+            alive &= ~bad
+        for key in ("q", "dq", "ddq", "dddq"):
+            assert np.isfinite(b[key]).all() and np.isfinite(a[key]).all()
+            worst = max(worst, float(np.abs(a[key][alive] - b[key][alive]).max()))
+        hist += np.bincount(a["branch"][alive], minlength=3)[:3]
+    print(mode, robot, mis, near, worst, hist.tolist())
+    assert mis == 0 and near <= 1, (mis, near)
+    assert worst < 1e-7, worst                                    # north_star: 1e-5
+    if mode == "human_far":
+        assert hist[2] == 0
+    if mode == "human_inside_robot":
+        assert hist[2] > hist[0]
