@@ -271,6 +271,10 @@ def run_reference(args, files, sc, names, rank):
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    fc = reference_flop_count(args)
+    if fc:
+        fc["algorithmic_GFLOPs_host"] = fc["F_step"] * cb["value"] / 1e9      # the same counted operations at the CPU arm's rate
+        line["flop_count_reference"] = fc
     print(json.dumps(line), flush=True)
 
 
